@@ -1,0 +1,1555 @@
+// celeste_b200.cu -- sm_100a kernels + C ABI (include/celeste_b200.h)
+//
+// Hot path of CelestePy re-designed for B200: render point sources / galaxies
+// as PSF-convolved mixtures of Gaussians onto band images, Poisson pixel
+// log-likelihood, batched MH proposal scoring.  Reference citations are
+// relative to the HIPS/DESI-MCMC repository root.
+//
+// Kernel plan:
+//   prepare_kernel   one warp per (source, image) item: WCS, galaxy affine
+//                    transform, PSF (x) profile convolution table, footprint,
+//                    flux -- all in float64, table rounded to fp32 as an
+//                    integer-coordinate quadratic in log2 units.
+//   render_kernel    persistent CTAs pull 1024-pixel strips from a device work
+//                    list; thread = 8 consecutive pixels of a row; per
+//                    component 3 FMA hoisted per row + (2 FMA, 1 MUFU.EX2,
+//                    1 FADD) per pixel.  Epilogues: write patch | Poisson ll
+//                    against nelec/background/mask | conditional photon ll.
+//   field_reduce     gather: 64x16 pixel tiles sum the overlapping patches in
+//                    source order (deterministic), Poisson ll in fp64.
+//   score_finalize   delta / accept per proposal, guard-band list for the
+//                    float64 re-score.
+//
+// Compiled with -fmad=false: every fused multiply-add below is explicit so
+// the float64 preparation follows the reference's (unfused) NumPy arithmetic.
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include <string.h>
+#include <math.h>
+#include <atomic>
+#include <string>
+#include <vector>
+#include <algorithm>
+
+#include "celeste_b200.h"
+
+// ---------------------------------------------------------------------------
+// error plumbing
+// ---------------------------------------------------------------------------
+static thread_local std::string g_err;
+static std::atomic<long long> g_launches{0};
+static int g_device = -1;
+static int g_sm_count = 0;
+
+static int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+#define CUDA_TRY(expr)                                                            \
+  do {                                                                            \
+    cudaError_t _e = (expr);                                                      \
+    if (_e != cudaSuccess)                                                        \
+      return fail(CG_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
+                  __FILE__, __LINE__);                                            \
+  } while (0)
+#define LAUNCH_CHECK()                                                            \
+  do {                                                                            \
+    g_launches.fetch_add(1, std::memory_order_relaxed);                           \
+    cudaError_t _e = cudaGetLastError();                                          \
+    if (_e != cudaSuccess)                                                        \
+      return fail(CG_ECUDA, "kernel launch failed: %s (%s:%d)",                   \
+                  cudaGetErrorString(_e), __FILE__, __LINE__);                    \
+  } while (0)
+#define NEED_INIT()                                                               \
+  do {                                                                            \
+    if (g_device < 0) return fail(CG_ESTATE, "cg_init() has not been called");    \
+  } while (0)
+
+// ---------------------------------------------------------------------------
+// constants
+// ---------------------------------------------------------------------------
+#define LOG2PI_D 1.8378770664093453     /* gmm_like_fast.pyx:29 */
+#define LOG2E_D 1.4426950408889634
+#define LN2_D 0.6931471805599453
+#define PI_D 3.141592653589793
+
+// mixture_profiles.py:9-19 (raw, unnormalised; normalised at cg_init exactly
+// as the reference does: amp /= sum(amp)).
+static const double H_EXP_AMP_RAW[6] = {2.34853813e-03, 3.07995260e-02, 2.23364214e-01,
+                                        1.17949102e+00, 4.33873750e+00, 5.99820770e+00};
+static const double H_EXP_VAR[6] = {1.20078965e-03, 8.84526493e-03, 3.91463084e-02,
+                                    1.39976817e-01, 4.60962500e-01, 1.50159566e+00};
+static const double H_DEV_AMP_RAW[8] = {4.26347652e-02, 2.40127183e-01, 6.85907632e-01,
+                                        1.51937350e+00, 2.83627243e+00, 4.46467501e+00,
+                                        5.72440830e+00, 5.60989349e+00};
+static const double H_DEV_VAR[8] = {2.23759216e-04, 1.00220099e-03, 4.18731126e-03,
+                                    1.69432589e-02, 6.84850479e-02, 2.87207080e-01,
+                                    1.33320254e+00, 8.40215071e+00};
+
+struct ProfileConsts {
+  double exp_amp[6], exp_var[6], dev_amp[8], dev_var[8];
+};
+__constant__ ProfileConsts c_prof;
+
+#define MAX_FILTER_ROWS 1024
+struct FilterTables {
+  int count[CG_NUM_BANDS];
+  int start[CG_NUM_BANDS];
+  int loaded;
+  double wl[MAX_FILTER_ROWS];    // metres, sorted per band
+  double hvec[MAX_FILTER_ROWS];  // planck.py:52-54
+  double sens[MAX_FILTER_ROWS];
+};
+static FilterTables* g_d_filters = nullptr;  // device
+static int g_filters_loaded = 0;
+
+// ---------------------------------------------------------------------------
+// device-side structures
+// ---------------------------------------------------------------------------
+struct DevImage {
+  int H, W, band, n_psf;
+  double epsilon, kappa, calib;
+  double psf_w[CG_MAX_PSF];
+  double psf_mu[CG_MAX_PSF][2];
+  double psf_cov[CG_MAX_PSF][3];
+  double rho_n[2], phi_n[2];
+  double ups[4], ups_inv[4];
+  double R;         // FitsImage.R, fits_image.py:151-155
+  double psf_wsum;  // np.sum(fits_img.weights), sources.py:161,174
+  const float* nelec;
+  const float* mask;
+};
+
+struct CgImage {
+  DevImage h;     // host copy
+  DevImage* d;    // device copy
+};
+
+struct ImgPtrs {
+  const DevImage* p[CG_MAX_IMAGES];
+};
+
+struct ItemHdr {
+  int x0, x1, y0, y1;  // footprint (half-open)
+  int ox, oy;          // local origin (pixel nearest the source centre)
+  int K;               // components (0: renders nothing)
+  int img;
+  int strip_start, n_strips;
+  int aux;
+  int flags;
+  double flux;         // rate multiplier (1 for unit-flux patches)
+  double norm_term;    // band_flux * sum(psf weights), sources.py:174
+};
+
+struct Counters {
+  int total_strips;
+  int work_counter;
+  int guard_count;
+  int err_flag;        // 1: footprint larger than max_patch_px, 2: guard list overflow
+  unsigned long long evals;
+  unsigned long long pad;
+};
+
+#define TAB_STRIDE (CG_MAX_COMP * 6)
+#define STRIP_THREADS 128
+#define PIX_PER_THREAD 8
+#define STRIP_PIX (STRIP_THREADS * PIX_PER_THREAD)
+
+struct PrepArgs {
+  ImgPtrs imgs;
+  int n_img;
+  const CgSource* srcs;
+  int n_src;
+  const CgItem* items;      // NULL: implicit
+  long long n_items;
+  int default_flags;
+  int implicit_mode;        // 0 cross product; 1 per-image fixed boxes + aux=img; 2 indirect list
+  const CgBox* img_boxes;   // device, n_img (implicit_mode >= 1)
+  const int* ind_list;      // device (implicit_mode 2)
+  const int* ind_count;     // device (implicit_mode 2): points at Counters.guard_count of pass 1
+  int aux_per_img;          // implicit_mode >= 1: aux patch index = image index (else -1)
+  double bound_cap;
+  long long max_patch_px;
+  ItemHdr* hdr;
+  void* tab;                // float or double, n_items * TAB_STRIDE
+  int2* worklist;
+  int worklist_cap;
+  Counters* cnt;
+  CgBox* out_boxes;         // optional
+  const FilterTables* filters;
+};
+
+// ---------------------------------------------------------------------------
+// small device helpers
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rexp2(float x) { return ex2_approx(x); }
+__device__ __forceinline__ double rexp2(double x) { return exp2(x); }
+__device__ __forceinline__ float rfma(float a, float b, float c) { return fmaf(a, b, c); }
+__device__ __forceinline__ double rfma(double a, double b, double c) { return fma(a, b, c); }
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// log(lam) for a positive normal float, absolute error ~3e-9: 32-entry table
+// of log(c_i) in float64 + degree-5 log1p of the residual in fp32.
+struct LogTable {
+  double logc[32];
+  float invc[32];
+};
+__device__ __forceinline__ void log_table_init(LogTable* t, int tid, int nthreads) {
+  for (int i = tid; i < 32; i += nthreads) {
+    double c = 1.0 + (2.0 * i + 1.0) / 64.0;
+    t->logc[i] = log(c);
+    t->invc[i] = (float)(1.0 / c);
+  }
+}
+__device__ __forceinline__ double log_accurate(float lam, const LogTable* t) {
+  int bits = __float_as_int(lam);
+  int e = (bits >> 23) - 127;
+  int i = (bits >> 18) & 31;
+  float m = __int_as_float((bits & 0x007fffff) | 0x3f800000);   // [1, 2)
+  float c = __int_as_float(0x3f800000 | (i << 18) | (1 << 17)); // 1 + (2i+1)/64
+  float r = (m - c) * t->invc[i];                               // |r| <= 1/64
+  float p = fmaf(r, 0.2f, -0.25f);
+  p = fmaf(r, p, 0.33333334f);
+  p = fmaf(r, p, -0.5f);
+  p = fmaf(r, p, 1.0f);
+  p = r * p;
+  return fma((double)e, LN2_D, t->logc[i]) + (double)p;
+}
+__device__ __forceinline__ double log_accurate(double lam, const LogTable*) { return log(lam); }
+
+// util/bound/bounding_box.py:13-26 for one component (same operation order).
+__host__ __device__ inline double major_axis(double s00, double s11, double s01, double Rsq) {
+  double sigma1 = sqrt(s00);
+  double sigma2 = sqrt(s11);
+  double rho = s01 / (sigma1 * sigma2);
+  double A11 = sigma1;
+  double A21 = rho * sigma2;
+  double A22 = sigma2 * sqrt(1 - rho * rho);
+  double An = 1. / Rsq * (1 / (A11 * A11) + (A21 * A21) / (A22 * A22));
+  double Bn = 1. / Rsq * (-2 * A21 / (A11 * (A22 * A22)));
+  double Cn = 1. / Rsq * 1. / (A22 * A22);
+  return 1.0 / sqrt(0.5 * (An + Cn - sqrt(Bn * Bn + (An - Cn) * (An - Cn))));
+}
+
+// fits_image.py:176-181
+__device__ inline void pixel2equa(const DevImage& im, double x, double y, double* ra, double* dec) {
+  double phi1rad = im.phi_n[1] / 180. * PI_D;
+  double dx = x - im.rho_n[0], dy = y - im.rho_n[1];
+  double i0 = im.ups[0] * dx + im.ups[1] * dy;
+  double i1 = im.ups[2] * dx + im.ups[3] * dy;
+  *ra = i0 / cos(phi1rad) + im.phi_n[0];
+  *dec = i1 + im.phi_n[1];
+}
+
+// planck.py:82-92,139-140 for one band; the warp strides over wavelengths.
+__device__ double planck_photons_per_joule_warp(const FilterTables* f, double T, int band, int lane) {
+  const double h = 6.6260693e-34, k = 1.3806488e-23, c = 299792458.0;
+  const double hc_k = (h * c) / k;
+  const double hpicc2 = 2 * PI_D * h * c * c;
+  const double pi5 = PI_D * PI_D * PI_D * PI_D * PI_D;
+  const double sigma = 2 * pi5 * (k * k * k * k) / (15 * (c * c) * (h * h * h));
+  if (!(T > 0)) return 0.0;
+  double T4 = T * T * T * T;
+  double total = sigma * T4;
+  int n = f->count[band], s = f->start[band];
+  double acc = 0.0;
+  for (int i = lane; i < n; i += 32) {
+    double w = f->wl[s + i];
+    double w5 = w * w * w * w * w;
+    double rad = hpicc2 / (w5 * (exp(hc_k / (w * T)) - 1));
+    acc += (rad / total) * f->hvec[s + i];
+  }
+  return warp_sum(acc);  // lane 0 holds the sum
+}
+
+// ---------------------------------------------------------------------------
+// prepare: one warp per item
+// ---------------------------------------------------------------------------
+template <typename real>
+__global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
+  const int lane = threadIdx.x & 31;
+  const long long i = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (i >= a.n_items) return;
+
+  CgItem it;
+  if (a.items) {
+    it = a.items[i];
+  } else if (a.implicit_mode == 0) {
+    it.src = (int)(i / a.n_img);
+    it.img = (int)(i % a.n_img);
+    it.flags = a.default_flags;
+    it.aux = -1;
+    it.box[0] = it.box[1] = it.box[2] = it.box[3] = 0;
+  } else {
+    int g = (int)(i / a.n_img);
+    it.img = (int)(i % a.n_img);
+    if (a.implicit_mode == 2) {
+      int cnt = *a.ind_count;
+      if (g > cnt) return;
+      it.src = (g == 0) ? 0 : a.ind_list[g - 1];
+    } else {
+      it.src = g;
+    }
+    it.flags = a.default_flags | CG_ITEM_FIXED_BOX;
+    it.aux = a.aux_per_img ? it.img : -1;
+    CgBox b = a.img_boxes[it.img];
+    it.box[0] = b.x0; it.box[1] = b.x1; it.box[2] = b.y0; it.box[3] = b.y1;
+  }
+
+  const DevImage& im = *a.imgs.p[it.img];
+  const CgSource& s = a.srcs[it.src];
+  const int H = im.H, W = im.W;
+
+  // v_s = image.equa2pixel(u)                       (fits_image.py:166-174)
+  const double phi1rad = im.phi_n[1] / 180. * PI_D;
+  const double iwc0 = (s.u[0] - im.phi_n[0]) * cos(phi1rad);
+  const double iwc1 = (s.u[1] - im.phi_n[1]);
+  const double px = (im.ups_inv[0] * iwc0 + im.ups_inv[1] * iwc1) + im.rho_n[0];
+  const double py = (im.ups_inv[2] * iwc0 + im.ups_inv[3] * iwc1) + im.rho_n[1];
+
+  const int n_psf = im.n_psf;
+  int K = 0;
+  double bound = 0.0;
+  bool trunc_box = true;
+  double Wm[3] = {0, 0, 0};  // W = Tinv Tinv^T : xx, yy, xy
+  const bool star = (s.type == 0);
+  int n_exp = 0, n_dev = 0;
+  double th_exp = 1.0, th_dev = 1.0;
+
+  if (star) {
+    // celeste.py:130-134 overlap test (v_s[0] against both dims, as written)
+    bool off = (px < -50 || px > 2.0 * H || py < -50 || px > 2.0 * W);
+    K = off ? 0 : n_psf;
+    bound = im.R;
+  } else {
+    // cd: FitsImage.cd_at_pixel (fits_image.py:196-216) or header CD
+    double cd[4];
+    if (it.flags & CG_ITEM_HEADER_CD) {
+      cd[0] = im.ups[0]; cd[1] = im.ups[1]; cd[2] = im.ups[2]; cd[3] = im.ups[3];
+    } else {
+      double ra0, dec0, rax, decx, ray, decy;
+      const double step = 10.;
+      pixel2equa(im, px, py, &ra0, &dec0);
+      pixel2equa(im, px + step, py, &rax, &decx);
+      pixel2equa(im, px, py + step, &ray, &decy);
+      double cosd = cos(dec0 * (PI_D / 180.));
+      cd[0] = (rax - ra0) / step * cosd; cd[1] = (ray - ra0) / step * cosd;
+      cd[2] = (decx - dec0) / step;      cd[3] = (decy - dec0) / step;
+    }
+    // celeste_galaxy_conditionals.py:90-125
+    double phi = (90. - s.phi) * PI_D / 180.;
+    double re_deg = fmax(1. / 30, s.sigma) / 3600.;
+    double cp = cos(phi), sp = sin(phi);
+    double G[4] = {re_deg * cp, re_deg * (sp * s.rho), re_deg * (-sp), re_deg * (cp * s.rho)};
+    double detG = G[0] * G[3] - G[1] * G[2];
+    double Gi[4] = {G[3] / detG, -G[1] / detG, -G[2] / detG, G[0] / detG};
+    double T[4] = {Gi[0] * cd[0] + Gi[1] * cd[2], Gi[0] * cd[1] + Gi[1] * cd[3],
+                   Gi[2] * cd[0] + Gi[3] * cd[2], Gi[2] * cd[1] + Gi[3] * cd[3]};
+    double detT = T[0] * T[3] - T[1] * T[2];
+    double Ti[4] = {T[3] / detT, -T[1] / detT, -T[2] / detT, T[0] / detT};
+    Wm[0] = Ti[0] * Ti[0] + Ti[1] * Ti[1];
+    Wm[1] = Ti[2] * Ti[2] + Ti[3] * Ti[3];
+    Wm[2] = Ti[0] * Ti[2] + Ti[1] * Ti[3];
+    if (it.flags & CG_ITEM_PROF_EXP) { n_exp = 6; n_dev = 0; }
+    else if (it.flags & CG_ITEM_PROF_DEV) { n_exp = 0; n_dev = 8; }
+    else { n_exp = 6; n_dev = 8; th_exp = s.theta; th_dev = 1. - s.theta; }
+    K = (n_exp + n_dev) * n_psf;
+    trunc_box = (it.flags & CG_ITEM_TRUNC_BOX) != 0;
+  }
+
+  const int ox = (int)rint(px), oy = (int)rint(py);
+  const double Rsq_gal = 23.025850929940457;  // chi2.ppf(1 - 1e-5, 2)
+  real* tab = reinterpret_cast<real*>(a.tab) + i * TAB_STRIDE;
+
+  double mybound = -1e300;
+  for (int c = lane; c < K; c += 32) {
+    double w, s00, s11, s01, mux, muy;
+    int k;
+    if (star) {
+      k = c;
+      w = im.psf_w[k];
+      s00 = im.psf_cov[k][0]; s11 = im.psf_cov[k][1]; s01 = im.psf_cov[k][2];
+    } else {
+      // profile-major ordering of the live route (mog.py:75-81): c = j*n_psf + k
+      int j = c / n_psf;
+      k = c - j * n_psf;
+      double amp, var;
+      if (j < n_exp) { amp = th_exp * c_prof.exp_amp[j]; var = c_prof.exp_var[j]; }
+      else { amp = th_dev * c_prof.dev_amp[j - n_exp]; var = c_prof.dev_var[j - n_exp]; }
+      w = amp * im.psf_w[k];
+      s00 = var * Wm[0] + im.psf_cov[k][0];
+      s11 = var * Wm[1] + im.psf_cov[k][1];
+      s01 = var * Wm[2] + im.psf_cov[k][2];
+      double dist = sqrt(im.psf_mu[k][0] * im.psf_mu[k][0] + im.psf_mu[k][1] * im.psf_mu[k][1]);
+      mybound = fmax(mybound, major_axis(s00, s11, s01, Rsq_gal) + dist);
+    }
+    mux = px + im.psf_mu[k][0];
+    muy = py + im.psf_mu[k][1];
+    // gmm_like_fast.pyx:165-176 folded into log2 units
+    double det = s00 * s11 - s01 * s01;
+    double i00 = s11 / det, i11 = s00 / det, i01 = -1 * s01 / det;
+    double k2 = (-LOG2PI_D - .5 * log(det) + log(w)) * LOG2E_D;
+    double A = -.5 * LOG2E_D * i00, B = -LOG2E_D * i01, C = -.5 * LOG2E_D * i11;
+    double mx = mux - ox, my = muy - oy;
+    tab[c * 6 + 0] = (real)A;
+    tab[c * 6 + 1] = (real)B;
+    tab[c * 6 + 2] = (real)C;
+    tab[c * 6 + 3] = (real)(-2. * A * mx - B * my);
+    tab[c * 6 + 4] = (real)(-B * mx - 2. * C * my);
+    tab[c * 6 + 5] = (real)(A * mx * mx + B * mx * my + C * my * my + k2);
+  }
+  if (!star) {
+    bound = warp_max(mybound);
+    if (K == 0) bound = 0;
+  }
+  if (a.bound_cap > 0) bound = fmin(bound, a.bound_cap);
+
+  int x0, x1, y0, y1;
+  if (it.flags & CG_ITEM_FIXED_BOX) {
+    x0 = it.box[0]; x1 = it.box[1]; y0 = it.box[2]; y1 = it.box[3];
+    x0 = max(x0, 0); y0 = max(y0, 0); x1 = min(x1, W); y1 = min(y1, H);
+  } else if (trunc_box) {
+    // celeste.py:139-140 / celeste_galaxy_conditionals.py:161-162
+    x0 = max(0, (int)(px - bound)); x1 = min((int)(px + bound + 1), W);
+    y0 = max(0, (int)(py - bound)); y1 = min((int)(py + bound + 1), H);
+  } else {
+    // celeste_galaxy_conditionals.py:208-211
+    x0 = (int)fmax(0., floor(px - bound)); x1 = (int)fmin((double)W, ceil(px + bound));
+    y0 = (int)fmax(0., floor(py - bound)); y1 = (int)fmin((double)H, ceil(py + bound));
+  }
+  if (x1 <= x0 || y1 <= y0 || (K == 0 && !(it.flags & CG_ITEM_FIXED_BOX))) { x1 = x0; y1 = y0; }
+  long long npx = (long long)(x1 - x0) * (y1 - y0);
+  int err = 0;
+  if (npx > a.max_patch_px) { err = 1; x1 = x0; y1 = y0; npx = 0; }
+
+  // flux (celeste.py:38-45,80-81,91-92; planck.py:155-158)
+  double flux;
+  if (it.flags & CG_ITEM_FLUX_UNIT) {
+    flux = 1.0;
+  } else if (star && (s.flags & CG_SRC_PLANCK) && s.t != 0.0) {
+    double ppj = planck_photons_per_joule_warp(a.filters, s.t, im.band, lane);
+    ppj = __shfl_sync(0xffffffffu, ppj, 0);
+    const double c_ = 299792458.0;
+    const double m_per_ly = c_ * 31556952.;
+    const double lens_area = .75 * PI_D * (1.25 * 1.25);
+    double lens_watts = lens_area * s.b * (3.846 * 1e26) / (m_per_ly * m_per_ly);
+    flux = ppj * lens_watts * 54.;
+  } else {
+    flux = (s.flux[im.band] / im.calib) * im.kappa;
+  }
+
+  const int wbox = x1 - x0, hbox = y1 - y0;
+  const int cpr = (wbox + PIX_PER_THREAD - 1) / PIX_PER_THREAD;
+  const int n_strips = (int)(((long long)hbox * cpr + STRIP_THREADS - 1) / STRIP_THREADS);
+  int start = 0;
+  if (lane == 0) {
+    start = n_strips ? atomicAdd(&a.cnt->total_strips, n_strips) : 0;
+    if (npx) atomicAdd(&a.cnt->evals, (unsigned long long)npx * (unsigned long long)K);
+    if (err) atomicExch(&a.cnt->err_flag, 1);
+    if (start + n_strips > a.worklist_cap) { atomicExch(&a.cnt->err_flag, 3); }
+  }
+  start = __shfl_sync(0xffffffffu, start, 0);
+  if (start + n_strips <= a.worklist_cap)
+    for (int j = lane; j < n_strips; j += 32) a.worklist[start + j] = make_int2((int)i, j);
+  if (lane == 0) {
+    ItemHdr h;
+    h.x0 = x0; h.x1 = x1; h.y0 = y0; h.y1 = y1;
+    h.ox = ox; h.oy = oy; h.K = K; h.img = it.img;
+    h.strip_start = start; h.n_strips = n_strips;
+    h.aux = it.aux; h.flags = it.flags;
+    h.flux = flux;
+    h.norm_term = flux * im.psf_wsum;
+    a.hdr[i] = h;
+    if (a.out_boxes) {
+      CgBox b; b.x0 = x0; b.x1 = x1; b.y0 = y0; b.y1 = y1;
+      a.out_boxes[i] = b;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// render: persistent CTAs over the strip work list
+// ---------------------------------------------------------------------------
+#define MODE_PATCH 0
+#define MODE_POISSON 1
+#define MODE_COND 2
+
+
+struct RenderArgs {
+  ImgPtrs imgs;
+  const ItemHdr* hdr;
+  const void* tab;
+  const int2* worklist;
+  Counters* cnt;
+  float* patches;             // MODE_PATCH
+  long long max_patch_px;
+  const float* aux;           // background / photon patches
+  const long long* aux_offsets;
+  double* partials;           // one per strip
+};
+
+template <typename real, int MODE>
+__global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
+  __shared__ __align__(16) real s_tab[TAB_STRIDE];
+  __shared__ int s_work;
+  __shared__ double s_red[STRIP_THREADS / 32];
+  __shared__ LogTable s_log;
+  const int tid = threadIdx.x;
+  if (MODE != MODE_PATCH) log_table_init(&s_log, tid, STRIP_THREADS);
+  const int total = *((volatile int*)&a.cnt->total_strips);
+
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) s_work = atomicAdd(&a.cnt->work_counter, 1);
+    __syncthreads();
+    const int wk = s_work;
+    if (wk >= total) break;
+    const int2 w = a.worklist[wk];
+    const int item = w.x, strip = w.y;
+    const ItemHdr h = a.hdr[item];
+    const real* gtab = reinterpret_cast<const real*>(a.tab) + (long long)item * TAB_STRIDE;
+    for (int t = tid; t < h.K * 6; t += STRIP_THREADS) s_tab[t] = gtab[t];
+    __syncthreads();
+
+    const int wbox = h.x1 - h.x0, hbox = h.y1 - h.y0;
+    const int cpr = (wbox + PIX_PER_THREAD - 1) / PIX_PER_THREAD;
+    const int q = strip * STRIP_THREADS + tid;
+    const int row = q / cpr;
+    const int cx = (q - row * cpr) * PIX_PER_THREAD;
+    const bool active = row < hbox;
+    const int npx = active ? min(PIX_PER_THREAD, wbox - cx) : 0;
+
+    real acc[PIX_PER_THREAD];
+#pragma unroll
+    for (int p = 0; p < PIX_PER_THREAD; ++p) acc[p] = (real)0;
+
+    if (active) {
+      const real yl = (real)(h.y0 + row - h.oy);
+      const real xl0 = (real)(h.x0 + cx - h.ox);
+      real xl[PIX_PER_THREAD];
+#pragma unroll
+      for (int p = 0; p < PIX_PER_THREAD; ++p) xl[p] = xl0 + (real)p;
+      const int K = h.K;
+#pragma unroll 2
+      for (int k = 0; k < K; ++k) {
+        const real A = s_tab[k * 6 + 0], B = s_tab[k * 6 + 1], C = s_tab[k * 6 + 2];
+        const real b10 = s_tab[k * 6 + 3], c01 = s_tab[k * 6 + 4], c00 = s_tab[k * 6 + 5];
+        const real b1 = rfma(B, yl, b10);
+        const real c1 = rfma(rfma(C, yl, c01), yl, c00);
+#pragma unroll
+        for (int p = 0; p < PIX_PER_THREAD; ++p) {
+          const real arg = rfma(rfma(A, xl[p], b1), xl[p], c1);
+          acc[p] += rexp2(arg);
+        }
+      }
+    }
+
+    if (MODE == MODE_PATCH) {
+      if (active) {
+        float* out = a.patches + (long long)item * a.max_patch_px + (long long)row * wbox + cx;
+        const real fl = (real)h.flux;
+#pragma unroll
+        for (int p = 0; p < PIX_PER_THREAD; ++p)
+          if (p < npx) out[p] = (float)(acc[p] * fl);
+      }
+    } else {
+      double s = 0.0;
+      if (active) {
+        const DevImage& im = *a.imgs.p[h.img];
+        const real fl = (real)h.flux;
+        const long long poff = (long long)row * wbox + cx;
+        const float* auxp = (h.aux >= 0) ? a.aux + a.aux_offsets[h.aux] + poff : nullptr;
+        if (MODE == MODE_POISSON) {
+          const float* data = im.nelec + (long long)(h.y0 + row) * im.W + (h.x0 + cx);
+          const float* mask = (im.mask && !(h.flags & CG_ITEM_NO_MASK))
+                                  ? im.mask + (long long)(h.y0 + row) * im.W + (h.x0 + cx) : nullptr;
+          const real eps = (real)im.epsilon;
+#pragma unroll
+          for (int p = 0; p < PIX_PER_THREAD; ++p) {
+            if (p < npx) {
+              const real bg = auxp ? (real)auxp[p] : eps;
+              const real lam = bg + fl * acc[p];
+              const bool good = (lam > (real)0) && (!mask || mask[p] != 0.f);
+              if (good) s += (double)data[p] * log_accurate(lam, &s_log) - (double)lam;
+            }
+          }
+        } else {  // MODE_COND, sources.py:171-174
+#pragma unroll
+          for (int p = 0; p < PIX_PER_THREAD; ++p) {
+            if (p < npx) {
+              const real m = fl * acc[p];
+              if (m >= (real)1.17549435e-38f) s += log_accurate(m, &s_log) * (double)auxp[p];
+            }
+          }
+        }
+      }
+      s = warp_sum(s);
+      if ((tid & 31) == 0) s_red[tid >> 5] = s;
+      __syncthreads();
+      if (tid == 0) {
+        double t = 0;
+#pragma unroll
+        for (int wv = 0; wv < STRIP_THREADS / 32; ++wv) t += s_red[wv];
+        a.partials[h.strip_start + strip] = t;
+      }
+    }
+  }
+}
+
+// per-item sum of strip partials (fixed order -> deterministic)
+__global__ void items_finalize_kernel(const ItemHdr* hdr, const double* partials, long long n_items,
+                                      int mode, double* item_ll, const int* count_limit, int n_img) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_items) return;
+  if (count_limit && (i / n_img) > *count_limit) return;
+  const ItemHdr h = hdr[i];
+  double s = 0;
+  for (int j = 0; j < h.n_strips; ++j) s += partials[h.strip_start + j];
+  if (mode == CG_LL_CONDITIONAL) s -= h.norm_term;
+  item_ll[i] = s;
+}
+
+// ---------------------------------------------------------------------------
+// field reduce (gather) : lambda = eps + sum patches ; ll = sum x log lam - lam
+// ---------------------------------------------------------------------------
+#define TILE_W 64
+#define TILE_H 16
+struct FieldArgs {
+  ImgPtrs imgs;
+  int n_img, n_src;
+  const ItemHdr* hdr;
+  const float* patches;
+  long long max_patch_px;
+  double* tile_partials;   // [n_img][max_tiles]
+  int max_tiles;
+  float* model[CG_MAX_IMAGES > 16 ? 16 : CG_MAX_IMAGES];  // optional outputs (first 16 images)
+  int has_model;
+};
+
+__global__ void __launch_bounds__(256) field_reduce_kernel(FieldArgs a) {
+  const int img = blockIdx.y;
+  const DevImage& im = *a.imgs.p[img];
+  const int H = im.H, W = im.W;
+  const int tiles_x = (W + TILE_W - 1) / TILE_W, tiles_y = (H + TILE_H - 1) / TILE_H;
+  const int tile = blockIdx.x;
+  if (tile >= tiles_x * tiles_y) return;
+  const int tx = tile % tiles_x, ty = tile / tiles_x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int X0 = tx * TILE_W, Y0 = ty * TILE_H;
+  const int x = X0 + (tid & 15) * 4, y = Y0 + (tid >> 4);
+
+  __shared__ int s_wcount[8];
+  __shared__ int4 s_box[256];
+  __shared__ int s_item[256];
+  __shared__ double s_red[8];
+  __shared__ LogTable s_log;
+  log_table_init(&s_log, tid, 256);
+
+  const float eps = (float)im.epsilon;
+  float lam[4] = {eps, eps, eps, eps};
+
+  for (int base = 0; base < a.n_src; base += 256) {
+    const int sidx = base + tid;
+    bool hit = false;
+    int4 bx = make_int4(0, 0, 0, 0);
+    int item = 0;
+    if (sidx < a.n_src) {
+      item = sidx * a.n_img + img;
+      const ItemHdr* hp = a.hdr + item;
+      bx = *reinterpret_cast<const int4*>(hp);   // x0,x1,y0,y1
+      hit = (bx.y > bx.x) && (bx.w > bx.z) && bx.x < X0 + TILE_W && bx.y > X0 &&
+            bx.z < Y0 + TILE_H && bx.w > Y0;
+    }
+    const unsigned bal = __ballot_sync(0xffffffffu, hit);
+    if (lane == 0) s_wcount[warp] = __popc(bal);
+    __syncthreads();
+    int off = 0, nh = 0;
+#pragma unroll
+    for (int wv = 0; wv < 8; ++wv) {
+      int cnt = s_wcount[wv];
+      if (wv < warp) off += cnt;
+      nh += cnt;
+    }
+    if (hit) {
+      int pos = off + __popc(bal & ((1u << lane) - 1));
+      s_box[pos] = bx;
+      s_item[pos] = item;
+    }
+    __syncthreads();
+    for (int j = 0; j < nh; ++j) {
+      const int4 b = s_box[j];
+      if (y >= b.z && y < b.w) {
+        const int wb = b.y - b.x;
+        const float* rowp = a.patches + (long long)s_item[j] * a.max_patch_px +
+                            (long long)(y - b.z) * wb - b.x;
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          int xx = x + p;
+          if (xx >= b.x && xx < b.y) lam[p] += rowp[xx];
+        }
+      }
+    }
+    __syncthreads();
+  }
+
+  double s = 0.0;
+  if (y < H) {
+    const long long rowoff = (long long)y * W;
+    float d[4] = {0, 0, 0, 0};
+    if (im.nelec) {
+      if (x + 3 < W && ((rowoff + x) & 3) == 0 && ((uintptr_t)im.nelec & 15) == 0) {
+        float4 v = *reinterpret_cast<const float4*>(im.nelec + rowoff + x);
+        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+      } else {
+#pragma unroll
+        for (int p = 0; p < 4; ++p)
+          if (x + p < W) d[p] = im.nelec[rowoff + x + p];
+      }
+#pragma unroll
+      for (int p = 0; p < 4; ++p)
+        if (x + p < W) s += (double)d[p] * log_accurate(lam[p], &s_log) - (double)lam[p];
+    }
+    if (a.has_model && img < 16 && a.model[img]) {
+#pragma unroll
+      for (int p = 0; p < 4; ++p)
+        if (x + p < W) a.model[img][rowoff + x + p] = lam[p];
+    }
+  }
+  s = warp_sum(s);
+  if (lane == 0) s_red[warp] = s;
+  __syncthreads();
+  if (tid == 0) {
+    double t = 0;
+#pragma unroll
+    for (int wv = 0; wv < 8; ++wv) t += s_red[wv];
+    a.tile_partials[(long long)img * a.max_tiles + tile] = t;
+  }
+}
+
+// one block per image: fixed-shape tree over the tile partials
+__global__ void __launch_bounds__(256) field_final_kernel(const double* tile_partials, int max_tiles,
+                                                          ImgPtrs imgs, double* ll) {
+  const int img = blockIdx.x;
+  const DevImage& im = *imgs.p[img];
+  const int nt = ((im.W + TILE_W - 1) / TILE_W) * ((im.H + TILE_H - 1) / TILE_H);
+  __shared__ double s_red[256];
+  double s = 0;
+  for (int t = threadIdx.x; t < nt; t += 256) s += tile_partials[(long long)img * max_tiles + t];
+  s_red[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) s_red[threadIdx.x] += s_red[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) ll[img] = s_red[0];
+}
+
+// ---------------------------------------------------------------------------
+// proposal scoring finalize (sources.py:258, :300-306)
+// ---------------------------------------------------------------------------
+__global__ void score_finalize_kernel(const double* item_ll, int n_img, int P,
+                                      const double* log_terms, const double* log_u, double guard,
+                                      double* delta, uint8_t* accept, Counters* cnt,
+                                      int* guard_list, int guard_cap) {
+  int p = blockIdx.x * blockDim.x + threadIdx.x;  // 0..P-1 -> source index p+1
+  if (p >= P) return;
+  double cur = 0, prop = 0;
+  for (int b = 0; b < n_img; ++b) {
+    cur += item_ll[b];
+    prop += item_ll[(long long)(p + 1) * n_img + b];
+  }
+  double d = (prop - cur) + (log_terms ? log_terms[p] : 0.0);
+  delta[p] = d;
+  double lu = log_u[p];
+  accept[p] = (lu < d) ? 1 : 0;
+  if (guard > 0 && fabs(lu - d) < guard) {
+    int pos = atomicAdd(&cnt->guard_count, 1);
+    if (pos < guard_cap) guard_list[pos] = p + 1;
+    else atomicExch(&cnt->err_flag, 2);
+  }
+}
+
+__global__ void score_rescore_kernel(const double* item_ll2, int n_img, const Counters* cnt1,
+                                     const int* guard_list, int guard_cap,
+                                     const double* log_terms, const double* log_u,
+                                     double* delta, uint8_t* accept) {
+  int g = blockIdx.x * blockDim.x + threadIdx.x;
+  int n = min(cnt1->guard_count, guard_cap);
+  if (g >= n) return;
+  int src = guard_list[g];
+  double cur = 0, prop = 0;
+  for (int b = 0; b < n_img; ++b) {
+    cur += item_ll2[b];
+    prop += item_ll2[(long long)(g + 1) * n_img + b];
+  }
+  double d = (prop - cur) + (log_terms ? log_terms[src - 1] : 0.0);
+  delta[src - 1] = d;
+  accept[src - 1] = (log_u[src - 1] < d) ? 1 : 0;
+}
+
+__global__ void clamp_guard_kernel(Counters* c, int cap) {
+  if (c->guard_count > cap) c->guard_count = cap;
+}
+
+// ---------------------------------------------------------------------------
+// A2: gmm_like_2d on an arbitrary point list
+// ---------------------------------------------------------------------------
+// Component constants in float64 (log2 units); the quadratic form is evaluated
+// in float64 because arbitrary covariances can be ill-conditioned (the KAT in
+// CelestePy/test/test_gmm.py draws random 2x2 Wishart matrices); the
+// exponential is the fp32 MUFU.EX2.
+__global__ void gmm_prep_kernel(const double* ws, const double* mus, const double* sigs, int K,
+                                double* tab) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= K) return;
+  double s00 = sigs[k * 4 + 0], s01 = sigs[k * 4 + 1], s10 = sigs[k * 4 + 2], s11 = sigs[k * 4 + 3];
+  double det = s00 * s11 - s01 * s10;
+  double i00 = s11 / det, i11 = s00 / det, i01 = -1 * s01 / det;
+  tab[k * 6 + 0] = mus[k * 2 + 0];
+  tab[k * 6 + 1] = mus[k * 2 + 1];
+  tab[k * 6 + 2] = -.5 * LOG2E_D * i00;
+  tab[k * 6 + 3] = -LOG2E_D * i01;
+  tab[k * 6 + 4] = -.5 * LOG2E_D * i11;
+  tab[k * 6 + 5] = (-LOG2PI_D - .5 * log(det) + log(ws[k])) * LOG2E_D;
+}
+
+__global__ void __launch_bounds__(256) gmm_points_kernel(double* probs, const double* x,
+                                                          const double* tab, long long N, int K) {
+  extern __shared__ double s_gt[];
+  for (int t = threadIdx.x; t < K * 6; t += blockDim.x) s_gt[t] = tab[t];
+  __syncthreads();
+  for (long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x; n < N;
+       n += (long long)gridDim.x * blockDim.x) {
+    const double2 pt = *reinterpret_cast<const double2*>(x + 2 * n);
+    float acc = 0.f;
+    for (int k = 0; k < K; ++k) {
+      const double dx = pt.x - s_gt[k * 6 + 0], dy = pt.y - s_gt[k * 6 + 1];
+      const double arg = fma(dx, fma(s_gt[k * 6 + 2], dx, s_gt[k * 6 + 3] * dy),
+                             fma(s_gt[k * 6 + 4] * dy, dy, s_gt[k * 6 + 5]));
+      acc += ex2_approx((float)arg);
+    }
+    probs[n] = (double)acc;
+  }
+}
+
+// gmm_like_fast.pyx:34-77
+struct MvnArgs { double mean[2], ci[4], logdet; };
+__global__ void mvn2d_logpdf_kernel(double* lls, const double* x, MvnArgs m, long long N) {
+  long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  double x0 = x[2 * n], x1 = x[2 * n + 1];
+  double mean_sig = m.mean[0] * m.mean[0] * m.ci[0] + m.mean[1] * m.mean[1] * m.ci[3] +
+                    2. * m.mean[0] * m.mean[1] * m.ci[1];
+  double xs0 = x0 * m.ci[0] + x1 * m.ci[2];
+  double xs1 = x0 * m.ci[1] + x1 * m.ci[3];
+  double quad = (x0 * xs0 + x1 * xs1) - 2. * (m.mean[0] * xs0 + m.mean[1] * xs1) + mean_sig;
+  lls[n] = -.5 * 2 * LOG2PI_D - .5 * m.logdet - .5 * quad;
+}
+
+// ---------------------------------------------------------------------------
+// A16 / A17
+// ---------------------------------------------------------------------------
+__global__ void planck_kernel(const double* T, const double* b, long long n, double* out,
+                              const FilterTables* f) {
+  long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  int lane = threadIdx.x & 31;
+  if (w >= n * CG_NUM_BANDS) return;
+  long long i = w / CG_NUM_BANDS;
+  int band = (int)(w % CG_NUM_BANDS);
+  double ppj = planck_photons_per_joule_warp(f, T[i], band, lane);
+  if (lane == 0) {
+    const double c_ = 299792458.0;
+    const double m_per_ly = c_ * 31556952.;
+    const double lens_area = .75 * PI_D * (1.25 * 1.25);
+    double lens_watts = lens_area * b[i] * (3.846 * 1e26) / (m_per_ly * m_per_ly);
+    out[w] = ppj * lens_watts * 54.;
+  }
+}
+
+// np.interp semantics (clamped ends)
+__device__ inline double interp_clamped(double xq, const double* xp_m, const double* fp, int n) {
+  // xp = wavelength_lookup*(10**10)   (redshift_utils.py:308)
+  const double sc = 1e10;
+  if (xq <= xp_m[0] * sc) return fp[0];
+  if (xq >= xp_m[n - 1] * sc) return fp[n - 1];
+  int lo = 0, hi = n - 1;
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (xp_m[mid] * sc <= xq) lo = mid; else hi = mid;
+  }
+  double x0 = xp_m[lo] * sc, x1 = xp_m[lo + 1] * sc;
+  double slope = (fp[lo + 1] - fp[lo]) / (x1 - x0);
+  return slope * (xq - x0) + fp[lo];
+}
+
+__global__ void __launch_bounds__(256) eigen_flux_kernel(const double* z, const double* w,
+                                                          const double* m, const double* B,
+                                                          const double* lam0, int K, int V,
+                                                          const double* fluxes, const double* ivar,
+                                                          double* mu, double* ll,
+                                                          const FilterTables* f) {
+  const int c = blockIdx.x, tid = threadIdx.x;
+  const double zz = z[c];
+  double acc[CG_NUM_BANDS], nrm[CG_NUM_BANDS];
+#pragma unroll
+  for (int b = 0; b < CG_NUM_BANDS; ++b) { acc[b] = 0; nrm[b] = 0; }
+  for (int v = tid; v < V; v += 256) {
+    double spec = 0;
+    for (int k = 0; k < K; ++k) spec += w[(long long)c * K + k] * B[(long long)k * V + v];
+    double lam = lam0[v] * (1. + zz);
+    double f2 = lam * lam / 2.99792e18;
+#pragma unroll
+    for (int b = 0; b < CG_NUM_BANDS; ++b) {
+      double sv = interp_clamped(lam, f->wl + f->start[b], f->sens + f->start[b], f->count[b]);
+      nrm[b] += sv;
+      acc[b] += sv * spec * f2;
+    }
+  }
+  __shared__ double s_red[8][2 * CG_NUM_BANDS];
+  const int lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+  for (int b = 0; b < CG_NUM_BANDS; ++b) {
+    double a1 = warp_sum(acc[b]), n1 = warp_sum(nrm[b]);
+    if (lane == 0) { s_red[warp][b] = a1; s_red[warp][CG_NUM_BANDS + b] = n1; }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    double l = 0;
+    for (int b = 0; b < CG_NUM_BANDS; ++b) {
+      double a1 = 0, n1 = 0;
+      for (int wv = 0; wv < 8; ++wv) { a1 += s_red[wv][b]; n1 += s_red[wv][CG_NUM_BANDS + b]; }
+      double fl = (n1 <= 0.) ? 0. : (a1 / n1) * 275422870333.81744384765625;
+      double mub = fl * m[c] / (1. + zz);
+      mu[(long long)c * CG_NUM_BANDS + b] = mub;
+      if (fluxes) {
+        double d = fluxes[(long long)c * CG_NUM_BANDS + b] - mub;
+        l += ivar[(long long)c * CG_NUM_BANDS + b] * d * d;
+      }
+    }
+    if (fluxes && ll) ll[c] = isinf(m[c]) ? -INFINITY : -0.5 * l;
+  }
+}
+
+// ===========================================================================
+// host side
+// ===========================================================================
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct WsLayout {
+  size_t counters, hdr, tab, worklist, partials, item_ll, img_boxes, aux_offsets, tiles, patches;
+  // second pass (float64 re-score)
+  size_t counters2, hdr2, tab2, worklist2, partials2, item_ll2, guard_list;
+  size_t total;
+  int worklist_cap, worklist_cap2, guard_cap;
+  long long n_items2;
+};
+
+#define GUARD_CAP 1024
+#define MAX_TILES_PER_IMG_DEFAULT 0
+
+static WsLayout ws_layout(long long n_items, long long max_patch_px, int with_patches,
+                          int n_img_for_guard, long long n_tiles_total) {
+  WsLayout L;
+  memset(&L, 0, sizeof L);
+  size_t o = 0;
+  auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes, 256); return r; };
+  long long strips_per_item = (max_patch_px + STRIP_PIX - 1) / STRIP_PIX + 64;
+  // rows whose width is not a multiple of 8 waste chunk slots: bound chunks by px/8 + rows
+  long long cap = n_items * strips_per_item;
+  if (cap > 0x7fffffffLL) cap = 0x7fffffffLL;
+  L.worklist_cap = (int)cap;
+  L.counters = take(sizeof(Counters));
+  L.hdr = take(sizeof(ItemHdr) * n_items);
+  L.tab = take(sizeof(float) * TAB_STRIDE * n_items);
+  L.worklist = take(sizeof(int2) * (size_t)L.worklist_cap);
+  L.partials = take(sizeof(double) * (size_t)L.worklist_cap);
+  L.item_ll = take(sizeof(double) * n_items);
+  L.img_boxes = take(sizeof(CgBox) * CG_MAX_IMAGES);
+  L.aux_offsets = take(sizeof(long long) * CG_MAX_IMAGES);
+  L.tiles = take(sizeof(double) * (size_t)n_tiles_total);
+  if (with_patches) L.patches = take(sizeof(float) * (size_t)(n_items * max_patch_px));
+  if (n_img_for_guard > 0) {
+    L.guard_cap = GUARD_CAP;
+    L.n_items2 = (long long)(GUARD_CAP + 1) * n_img_for_guard;
+    long long cap2 = L.n_items2 * strips_per_item;
+    if (cap2 > 0x7fffffffLL) cap2 = 0x7fffffffLL;
+    L.worklist_cap2 = (int)cap2;
+    L.counters2 = take(sizeof(Counters));
+    L.hdr2 = take(sizeof(ItemHdr) * L.n_items2);
+    L.tab2 = take(sizeof(double) * TAB_STRIDE * L.n_items2);
+    L.worklist2 = take(sizeof(int2) * (size_t)L.worklist_cap2);
+    L.partials2 = take(sizeof(double) * (size_t)L.worklist_cap2);
+    L.item_ll2 = take(sizeof(double) * L.n_items2);
+    L.guard_list = take(sizeof(int) * GUARD_CAP);
+  }
+  L.total = o;
+  return L;
+}
+
+static Counters* g_last_counters = nullptr;
+
+extern "C" {
+
+int cg_abi_version(void) { return CG_ABI_VERSION; }
+
+int cg_last_error(char* buf, size_t n) {
+  if (buf && n) {
+    strncpy(buf, g_err.c_str(), n - 1);
+    buf[n - 1] = 0;
+  }
+  return (int)g_err.size();
+}
+
+int cg_init(int device) {
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0)
+    return fail(CG_ECUDA, "no CUDA device available (%s); this library has no CPU fallback",
+                cudaGetErrorString(e));
+  if (device < 0 || device >= count) return fail(CG_EINVAL, "device %d out of range [0,%d)", device, count);
+  CUDA_TRY(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  g_sm_count = prop.multiProcessorCount;
+  ProfileConsts pc;
+  double se = 0, sd = 0;
+  for (int i = 0; i < 6; ++i) se += H_EXP_AMP_RAW[i];
+  for (int i = 0; i < 8; ++i) sd += H_DEV_AMP_RAW[i];
+  for (int i = 0; i < 6; ++i) { pc.exp_amp[i] = H_EXP_AMP_RAW[i] / se; pc.exp_var[i] = H_EXP_VAR[i]; }
+  for (int i = 0; i < 8; ++i) { pc.dev_amp[i] = H_DEV_AMP_RAW[i] / sd; pc.dev_var[i] = H_DEV_VAR[i]; }
+  CUDA_TRY(cudaMemcpyToSymbol(c_prof, &pc, sizeof pc));
+  if (!g_d_filters) {
+    CUDA_TRY(cudaMalloc(&g_d_filters, sizeof(FilterTables)));
+    CUDA_TRY(cudaMemset(g_d_filters, 0, sizeof(FilterTables)));
+  }
+  g_device = device;
+  return CG_OK;
+}
+
+int cg_shutdown(void) {
+  if (g_d_filters) { cudaFree(g_d_filters); g_d_filters = nullptr; }
+  g_filters_loaded = 0;
+  g_device = -1;
+  return CG_OK;
+}
+
+int cg_sm_count(void) { return g_sm_count; }
+
+int64_t cg_launch_count(int reset) {
+  long long v = g_launches.load();
+  if (reset) g_launches.store(0);
+  return v;
+}
+
+int64_t cg_last_eval_count(void* stream) {
+  if (!g_last_counters) return 0;
+  Counters c;
+  if (cudaStreamSynchronize((cudaStream_t)stream) != cudaSuccess) return -1;
+  if (cudaMemcpy(&c, g_last_counters, sizeof c, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+  if (c.err_flag) {
+    fail(CG_ENOMEM, c.err_flag == 1 ? "a footprint exceeded max_patch_px"
+                                    : (c.err_flag == 2 ? "guard list overflow" : "work list overflow"));
+    return -(int64_t)c.err_flag;
+  }
+  return (int64_t)c.evals;
+}
+
+// ---- images ----------------------------------------------------------------
+double cg_calc_bounding_radius(const double* means, const double* covars, int32_t K, double error,
+                               const double* center) {
+  // util/bound/bounding_box.py:9-31 ; chi2.ppf(1-error, 2) = -2 log(error)
+  double Rsq;
+  if (error == 0.001) Rsq = 13.815510557964274;
+  else if (error == 1e-5) Rsq = 23.025850929940457;
+  else Rsq = -2.0 * log(error);
+  double cx = center ? center[0] : 0, cy = center ? center[1] : 0;
+  double best = -INFINITY;
+  for (int i = 0; i < K; ++i) {
+    double maj = major_axis(covars[i * 4 + 0], covars[i * 4 + 3], covars[i * 4 + 1], Rsq);
+    double dx = means[i * 2] - cx, dy = means[i * 2 + 1] - cy;
+    double v = maj + sqrt(dx * dx + dy * dy);
+    if (v > best) best = v;
+  }
+  return best;
+}
+
+int cg_image_create(const CgImageDesc* d, CgImage** out) {
+  NEED_INIT();
+  if (!d || !out) return fail(CG_EINVAL, "null argument");
+  if (d->n_psf < 1 || d->n_psf > CG_MAX_PSF) return fail(CG_EINVAL, "n_psf must be in [1,%d]", CG_MAX_PSF);
+  if (d->H <= 0 || d->W <= 0) return fail(CG_EINVAL, "bad image shape %dx%d", d->H, d->W);
+  if (d->band < 0 || d->band >= CG_NUM_BANDS) return fail(CG_EINVAL, "band must be 0..4");
+  CgImage* im = new CgImage();
+  DevImage& h = im->h;
+  memset(&h, 0, sizeof h);
+  h.H = d->H; h.W = d->W; h.band = d->band; h.n_psf = d->n_psf;
+  h.epsilon = d->epsilon; h.kappa = d->kappa; h.calib = d->calib;
+  double means[CG_MAX_PSF * 2], covs[CG_MAX_PSF * 4];
+  h.psf_wsum = 0;
+  for (int k = 0; k < d->n_psf; ++k) {
+    h.psf_w[k] = d->psf_w[k];
+    h.psf_wsum += d->psf_w[k];
+    for (int j = 0; j < 2; ++j) { h.psf_mu[k][j] = d->psf_mu[k][j]; means[k * 2 + j] = d->psf_mu[k][j]; }
+    for (int j = 0; j < 3; ++j) h.psf_cov[k][j] = d->psf_cov[k][j];
+    covs[k * 4 + 0] = d->psf_cov[k][0]; covs[k * 4 + 3] = d->psf_cov[k][1];
+    covs[k * 4 + 1] = covs[k * 4 + 2] = d->psf_cov[k][2];
+  }
+  for (int j = 0; j < 2; ++j) { h.rho_n[j] = d->rho_n[j]; h.phi_n[j] = d->phi_n[j]; }
+  for (int j = 0; j < 4; ++j) h.ups[j] = d->ups[j];
+  double det = d->ups[0] * d->ups[3] - d->ups[1] * d->ups[2];
+  if (det == 0) { delete im; return fail(CG_EINVAL, "singular CD matrix"); }
+  h.ups_inv[0] = d->ups[3] / det; h.ups_inv[1] = -d->ups[1] / det;
+  h.ups_inv[2] = -d->ups[2] / det; h.ups_inv[3] = d->ups[0] / det;
+  h.R = cg_calc_bounding_radius(means, covs, d->n_psf, 0.001, nullptr);
+  h.nelec = d->d_nelec; h.mask = d->d_mask;
+  cudaError_t e = cudaMalloc(&im->d, sizeof(DevImage));
+  if (e != cudaSuccess) { delete im; return fail(CG_ECUDA, "cudaMalloc: %s", cudaGetErrorString(e)); }
+  e = cudaMemcpy(im->d, &h, sizeof h, cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) { cudaFree(im->d); delete im; return fail(CG_ECUDA, "cudaMemcpy: %s", cudaGetErrorString(e)); }
+  *out = im;
+  return CG_OK;
+}
+
+int cg_image_destroy(CgImage* img) {
+  if (!img) return CG_OK;
+  if (img->d) cudaFree(img->d);
+  delete img;
+  return CG_OK;
+}
+
+int cg_image_set_epsilon(CgImage* img, double epsilon) {
+  NEED_INIT();
+  if (!img) return fail(CG_EINVAL, "null image");
+  img->h.epsilon = epsilon;
+  CUDA_TRY(cudaMemcpy(img->d, &img->h, sizeof(DevImage), cudaMemcpyHostToDevice));
+  return CG_OK;
+}
+
+double cg_image_radius(const CgImage* img) { return img ? img->h.R : NAN; }
+
+int cg_set_filter_curves(const double* wl, const double* hv, const double* sens, const int32_t* counts) {
+  NEED_INIT();
+  FilterTables* f = new FilterTables();
+  memset(f, 0, sizeof *f);
+  int o = 0;
+  for (int b = 0; b < CG_NUM_BANDS; ++b) {
+    if (counts[b] < 2 || o + counts[b] > MAX_FILTER_ROWS) { delete f; return fail(CG_EINVAL, "bad filter table sizes"); }
+    f->count[b] = counts[b];
+    f->start[b] = o;
+    o += counts[b];
+  }
+  memcpy(f->wl, wl, sizeof(double) * o);
+  memcpy(f->hvec, hv, sizeof(double) * o);
+  memcpy(f->sens, sens, sizeof(double) * o);
+  f->loaded = 1;
+  cudaError_t e = cudaMemcpy(g_d_filters, f, sizeof *f, cudaMemcpyHostToDevice);
+  delete f;
+  if (e != cudaSuccess) return fail(CG_ECUDA, "cudaMemcpy: %s", cudaGetErrorString(e));
+  g_filters_loaded = 1;
+  return CG_OK;
+}
+
+// ---- A1 (host) ---------------------------------------------------------------
+int cg_galaxy_prof_psf_mixture_params(const double* W, const double* v_s, const double* image_ws,
+                                      const double* image_means, const double* image_covars,
+                                      int32_t K_psf, const double* prof_amp, const double* prof_sigs,
+                                      int32_t K_prof, double* weights, double* means, double* covars) {
+  // celeste_fast.pyx:123-139 : PSF-major, c = k*K_prof + j
+  int c = 0;
+  for (int k = 0; k < K_psf; ++k)
+    for (int j = 0; j < K_prof; ++j, ++c) {
+      weights[c] = image_ws[k] * prof_amp[j];
+      means[c * 2 + 0] = v_s[0] + image_means[k * 2 + 0];
+      means[c * 2 + 1] = v_s[1] + image_means[k * 2 + 1];
+      for (int e = 0; e < 4; ++e) covars[c * 4 + e] = image_covars[k * 4 + e] + prof_sigs[j] * W[e];
+    }
+  return CG_OK;
+}
+
+int cg_galaxy_psf_mixture_params(const double* thetas, const double* W, const double* v_s,
+                                 const double* image_ws, const double* image_means,
+                                 const double* image_covars, int32_t K_psf, const double* exp_amp,
+                                 const double* exp_sigs, int32_t K_exp, const double* dev_amp,
+                                 const double* dev_sigs, int32_t K_dev, double* weights,
+                                 double* means, double* covars) {
+  // celeste_fast.pyx:62-93
+  int c = 0;
+  for (int k = 0; k < K_psf; ++k)
+    for (int i = 0; i < 2; ++i) {
+      const double* amp = i == 0 ? exp_amp : dev_amp;
+      const double* var = i == 0 ? exp_sigs : dev_sigs;
+      int Ki = i == 0 ? K_exp : K_dev;
+      for (int j = 0; j < Ki; ++j, ++c) {
+        weights[c] = image_ws[k] * thetas[i] * amp[j];
+        means[c * 2 + 0] = v_s[0] + image_means[k * 2 + 0];
+        means[c * 2 + 1] = v_s[1] + image_means[k * 2 + 1];
+        for (int e = 0; e < 4; ++e) covars[c * 4 + e] = image_covars[k * 4 + e] + var[j] * W[e];
+      }
+    }
+  return CG_OK;
+}
+
+// ---- A2 ------------------------------------------------------------------------
+static double* g_gmm_tab = nullptr;  // K_max*6 doubles, lazily allocated
+static int g_gmm_tab_cap = 0;
+
+int cg_gmm_like_2d(double* d_probs, const double* d_x, const double* d_ws, const double* d_mus,
+                   const double* d_sigs, int64_t N, int32_t K, void* stream) {
+  NEED_INIT();
+  if (N < 0 || K < 0) return fail(CG_EINVAL, "negative size");
+  if (K > 4096) return fail(CG_EINVAL, "K=%d exceeds 4096 components", K);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (N == 0) return CG_OK;
+  if (K == 0) { CUDA_TRY(cudaMemsetAsync(d_probs, 0, sizeof(double) * N, st)); return CG_OK; }
+  if (K > g_gmm_tab_cap) {
+    if (g_gmm_tab) cudaFree(g_gmm_tab);
+    g_gmm_tab_cap = std::max(K, 64);
+    CUDA_TRY(cudaMalloc(&g_gmm_tab, sizeof(double) * 6 * g_gmm_tab_cap));
+  }
+  gmm_prep_kernel<<<(K + 63) / 64, 64, 0, st>>>(d_ws, d_mus, d_sigs, K, g_gmm_tab);
+  LAUNCH_CHECK();
+  int blocks = (int)std::min<long long>((N + 255) / 256, (long long)g_sm_count * 8);
+  size_t smem = sizeof(double) * 6 * K;
+  if (smem > 48 * 1024)
+    CUDA_TRY(cudaFuncSetAttribute(gmm_points_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  gmm_points_kernel<<<blocks, 256, smem, st>>>(d_probs, d_x, g_gmm_tab, N, K);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
+int cg_mvn2d_logpdf(double* d_lls, const double* d_x, const double* mean, const double* covinv,
+                    double logdet, int64_t N, void* stream) {
+  NEED_INIT();
+  if (N <= 0) return CG_OK;
+  MvnArgs m;
+  m.mean[0] = mean[0]; m.mean[1] = mean[1];
+  for (int i = 0; i < 4; ++i) m.ci[i] = covinv[i];
+  m.logdet = (double)(float)logdet;  // the reference declares `float logdet` (gmm_like_fast.pyx:39)
+  mvn2d_logpdf_kernel<<<(unsigned)((N + 255) / 256), 256, 0, (cudaStream_t)stream>>>(d_lls, d_x, m, N);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
+// ---- engine --------------------------------------------------------------------
+size_t cg_workspace_bytes(int32_t kind, int64_t n_items, int32_t n_img, int64_t max_patch_px,
+                          int64_t n_tiles) {
+  WsLayout L;
+  switch (kind) {
+    case CG_WS_RENDER: L = ws_layout(n_items, max_patch_px, 0, 0, 0); break;
+    case CG_WS_FIELD: L = ws_layout(std::max<long long>(n_items, 1), max_patch_px, 1, 0, n_tiles); break;
+    case CG_WS_ITEMS: L = ws_layout(n_items * 2, max_patch_px, 0, 0, 0); break;
+    case CG_WS_SCORE: L = ws_layout(n_items, max_patch_px, 0, n_img, 0); break;
+    default: return 0;
+  }
+  return L.total + 256;
+}
+
+int32_t cg_field_tiles(int32_t H, int32_t W) {
+  return ((W + TILE_W - 1) / TILE_W) * ((H + TILE_H - 1) / TILE_H);
+}
+
+static int fill_imgs(CgImage* const* imgs, int n_img, ImgPtrs* out) {
+  if (n_img < 1 || n_img > CG_MAX_IMAGES) return fail(CG_EINVAL, "n_img must be in [1,%d]", CG_MAX_IMAGES);
+  for (int i = 0; i < n_img; ++i) {
+    if (!imgs[i]) return fail(CG_EINVAL, "null image handle");
+    out->p[i] = imgs[i]->d;
+  }
+  return CG_OK;
+}
+
+}  // extern "C"
+
+static int render_grid() { return g_sm_count * 16; }
+
+template <typename real>
+static int run_prepare(const PrepArgs& pa, cudaStream_t st) {
+  if (pa.n_items == 0) return CG_OK;
+  unsigned blocks = (unsigned)((pa.n_items + 3) / 4);
+  prepare_kernel<real><<<blocks, 128, 0, st>>>(pa);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
+template <typename real, int MODE>
+static int run_render(const RenderArgs& ra, long long n_items, cudaStream_t st) {
+  if (n_items == 0) return CG_OK;
+  render_kernel<real, MODE><<<render_grid(), STRIP_THREADS, 0, st>>>(ra);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
+extern "C" {
+
+int cg_render_patches(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs, int32_t n_src,
+                      const CgItem* d_items, int64_t n_items, int32_t default_flags,
+                      double bound_cap, int64_t max_patch_px, float* d_patches, CgBox* d_boxes,
+                      void* d_ws, size_t ws_bytes, void* stream) {
+  NEED_INIT();
+  cudaStream_t st = (cudaStream_t)stream;
+  PrepArgs pa;
+  memset(&pa, 0, sizeof pa);
+  int rc = fill_imgs(imgs, n_img, &pa.imgs);
+  if (rc) return rc;
+  if (!d_items) n_items = (int64_t)n_src * n_img;
+  if (n_items <= 0) return CG_OK;
+  WsLayout L = ws_layout(n_items, max_patch_px, 0, 0, 0);
+  if (L.total > ws_bytes) return fail(CG_ENOMEM, "workspace too small: need %zu bytes, have %zu", L.total, ws_bytes);
+  char* base = (char*)d_ws;
+  Counters* cnt = (Counters*)(base + L.counters);
+  CUDA_TRY(cudaMemsetAsync(cnt, 0, sizeof(Counters), st));
+  pa.n_img = n_img; pa.srcs = d_srcs; pa.n_src = n_src; pa.items = d_items; pa.n_items = n_items;
+  pa.default_flags = default_flags; pa.implicit_mode = 0; pa.bound_cap = bound_cap;
+  pa.max_patch_px = max_patch_px; pa.hdr = (ItemHdr*)(base + L.hdr); pa.tab = base + L.tab;
+  pa.worklist = (int2*)(base + L.worklist); pa.worklist_cap = L.worklist_cap; pa.cnt = cnt;
+  pa.out_boxes = d_boxes; pa.filters = g_d_filters;
+  rc = run_prepare<float>(pa, st);
+  if (rc) return rc;
+  RenderArgs ra;
+  memset(&ra, 0, sizeof ra);
+  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.cnt = cnt;
+  ra.patches = d_patches; ra.max_patch_px = max_patch_px;
+  rc = run_render<float, MODE_PATCH>(ra, n_items, st);
+  g_last_counters = cnt;
+  return rc;
+}
+
+int cg_field_loglik(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs, int32_t n_src,
+                    double bound_cap, int64_t max_patch_px, double* d_ll, float* const* h_d_model,
+                    void* d_ws, size_t ws_bytes, void* stream) {
+  NEED_INIT();
+  cudaStream_t st = (cudaStream_t)stream;
+  PrepArgs pa;
+  memset(&pa, 0, sizeof pa);
+  int rc = fill_imgs(imgs, n_img, &pa.imgs);
+  if (rc) return rc;
+  if (n_src < 0) return fail(CG_EINVAL, "negative n_src");
+  long long n_items = (long long)n_src * n_img;
+  int max_tiles = 0;
+  for (int i = 0; i < n_img; ++i) {
+    int t = ((imgs[i]->h.W + TILE_W - 1) / TILE_W) * ((imgs[i]->h.H + TILE_H - 1) / TILE_H);
+    max_tiles = std::max(max_tiles, t);
+    if (!imgs[i]->h.nelec) return fail(CG_EINVAL, "image %d has no nelec buffer", i);
+  }
+  WsLayout L = ws_layout(std::max<long long>(n_items, 1), max_patch_px, 1, 0, (long long)max_tiles * n_img);
+  if (L.total > ws_bytes) return fail(CG_ENOMEM, "workspace too small: need %zu bytes, have %zu", L.total, ws_bytes);
+  char* base = (char*)d_ws;
+  Counters* cnt = (Counters*)(base + L.counters);
+  CUDA_TRY(cudaMemsetAsync(cnt, 0, sizeof(Counters), st));
+  pa.n_img = n_img; pa.srcs = d_srcs; pa.n_src = n_src; pa.items = nullptr; pa.n_items = n_items;
+  pa.default_flags = CG_ITEM_FLUX_BAND; pa.implicit_mode = 0; pa.bound_cap = bound_cap;
+  pa.max_patch_px = max_patch_px; pa.hdr = (ItemHdr*)(base + L.hdr); pa.tab = base + L.tab;
+  pa.worklist = (int2*)(base + L.worklist); pa.worklist_cap = L.worklist_cap; pa.cnt = cnt;
+  pa.filters = g_d_filters;
+  rc = run_prepare<float>(pa, st);
+  if (rc) return rc;
+  RenderArgs ra;
+  memset(&ra, 0, sizeof ra);
+  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.cnt = cnt;
+  ra.patches = (float*)(base + L.patches); ra.max_patch_px = max_patch_px;
+  rc = run_render<float, MODE_PATCH>(ra, n_items, st);
+  if (rc) return rc;
+  FieldArgs fa;
+  memset(&fa, 0, sizeof fa);
+  fa.imgs = pa.imgs; fa.n_img = n_img; fa.n_src = n_src; fa.hdr = pa.hdr;
+  fa.patches = ra.patches; fa.max_patch_px = max_patch_px;
+  fa.tile_partials = (double*)(base + L.tiles); fa.max_tiles = max_tiles;
+  if (h_d_model) {
+    if (n_img > 16) return fail(CG_EINVAL, "model output supports at most 16 images per call");
+    for (int i = 0; i < n_img; ++i) { fa.model[i] = h_d_model[i]; if (h_d_model[i]) fa.has_model = 1; }
+  }
+  field_reduce_kernel<<<dim3(max_tiles, n_img), 256, 0, st>>>(fa);
+  LAUNCH_CHECK();
+  field_final_kernel<<<n_img, 256, 0, st>>>(fa.tile_partials, max_tiles, pa.imgs, d_ll);
+  LAUNCH_CHECK();
+  g_last_counters = cnt;
+  return CG_OK;
+}
+
+int cg_items_loglik(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs, int32_t n_src,
+                    const CgItem* d_items, int64_t n_items, int32_t mode, double bound_cap,
+                    int64_t max_patch_px, const float* d_aux, const int64_t* d_aux_offsets,
+                    double* d_item_ll, CgBox* d_boxes, int32_t use_fp64, void* d_ws,
+                    size_t ws_bytes, void* stream) {
+  NEED_INIT();
+  cudaStream_t st = (cudaStream_t)stream;
+  if (mode != CG_LL_POISSON_BG && mode != CG_LL_CONDITIONAL) return fail(CG_EINVAL, "unknown mode %d", mode);
+  if (!d_items) return fail(CG_EINVAL, "d_items is required");
+  if (mode == CG_LL_CONDITIONAL && !d_aux) return fail(CG_EINVAL, "conditional mode needs photon patches");
+  PrepArgs pa;
+  memset(&pa, 0, sizeof pa);
+  int rc = fill_imgs(imgs, n_img, &pa.imgs);
+  if (rc) return rc;
+  if (n_items <= 0) return CG_OK;
+  long long max_px = 0;
+  for (int i = 0; i < n_img; ++i) max_px = std::max(max_px, (long long)imgs[i]->h.H * imgs[i]->h.W);
+  if (max_patch_px > 0) max_px = std::min<long long>(max_px, max_patch_px);
+  // tables are sized for double so either precision fits
+  WsLayout L = ws_layout(n_items * 2, max_px, 0, 0, 0);
+  if (L.total > ws_bytes) return fail(CG_ENOMEM, "workspace too small: need %zu bytes, have %zu", L.total, ws_bytes);
+  char* base = (char*)d_ws;
+  Counters* cnt = (Counters*)(base + L.counters);
+  CUDA_TRY(cudaMemsetAsync(cnt, 0, sizeof(Counters), st));
+  pa.n_img = n_img; pa.srcs = d_srcs; pa.n_src = n_src; pa.items = d_items; pa.n_items = n_items;
+  pa.bound_cap = bound_cap; pa.max_patch_px = max_px; pa.hdr = (ItemHdr*)(base + L.hdr);
+  pa.tab = base + L.tab; pa.worklist = (int2*)(base + L.worklist); pa.worklist_cap = L.worklist_cap;
+  pa.cnt = cnt; pa.out_boxes = d_boxes; pa.filters = g_d_filters;
+  RenderArgs ra;
+  memset(&ra, 0, sizeof ra);
+  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.cnt = cnt;
+  ra.aux = d_aux; ra.aux_offsets = (const long long*)d_aux_offsets;
+  ra.partials = (double*)(base + L.partials);
+  if (use_fp64) {
+    rc = run_prepare<double>(pa, st);
+    if (rc) return rc;
+    rc = (mode == CG_LL_POISSON_BG) ? run_render<double, MODE_POISSON>(ra, n_items, st)
+                                    : run_render<double, MODE_COND>(ra, n_items, st);
+  } else {
+    rc = run_prepare<float>(pa, st);
+    if (rc) return rc;
+    rc = (mode == CG_LL_POISSON_BG) ? run_render<float, MODE_POISSON>(ra, n_items, st)
+                                    : run_render<float, MODE_COND>(ra, n_items, st);
+  }
+  if (rc) return rc;
+  items_finalize_kernel<<<(unsigned)((n_items + 255) / 256), 256, 0, st>>>(
+      pa.hdr, ra.partials, n_items, mode, d_item_ll, nullptr, 1);
+  LAUNCH_CHECK();
+  g_last_counters = cnt;
+  return CG_OK;
+}
+
+int cg_score_proposals(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs, int32_t P,
+                       const CgBox* h_boxes, const float* d_bg, const int64_t* h_bg_offsets,
+                       const double* d_log_terms, const double* d_log_u, double guard,
+                       double* d_delta, uint8_t* d_accept, int32_t* d_n_guard, void* d_ws,
+                       size_t ws_bytes, void* stream) {
+  NEED_INIT();
+  cudaStream_t st = (cudaStream_t)stream;
+  PrepArgs pa;
+  memset(&pa, 0, sizeof pa);
+  int rc = fill_imgs(imgs, n_img, &pa.imgs);
+  if (rc) return rc;
+  if (P <= 0) return CG_OK;
+  if (!h_boxes) return fail(CG_EINVAL, "bounding boxes are required");
+  long long max_px = 0;
+  for (int i = 0; i < n_img; ++i) {
+    long long w = std::max(0, std::min(h_boxes[i].x1, imgs[i]->h.W) - std::max(h_boxes[i].x0, 0));
+    long long h = std::max(0, std::min(h_boxes[i].y1, imgs[i]->h.H) - std::max(h_boxes[i].y0, 0));
+    max_px = std::max(max_px, w * h);
+    if (!imgs[i]->h.nelec) return fail(CG_EINVAL, "image %d has no nelec buffer", i);
+  }
+  const long long n_items = (long long)(P + 1) * n_img;
+  WsLayout L = ws_layout(n_items, max_px, 0, guard > 0 ? n_img : 0, 0);
+  if (L.total > ws_bytes) return fail(CG_ENOMEM, "workspace too small: need %zu bytes, have %zu", L.total, ws_bytes);
+  char* base = (char*)d_ws;
+  Counters* cnt = (Counters*)(base + L.counters);
+  CUDA_TRY(cudaMemsetAsync(cnt, 0, sizeof(Counters), st));
+  CgBox* d_boxes = (CgBox*)(base + L.img_boxes);
+  long long* d_off = (long long*)(base + L.aux_offsets);
+  CUDA_TRY(cudaMemcpyAsync(d_boxes, h_boxes, sizeof(CgBox) * n_img, cudaMemcpyHostToDevice, st));
+  if (d_bg) {
+    if (!h_bg_offsets) return fail(CG_EINVAL, "background offsets are required with d_bg");
+    CUDA_TRY(cudaMemcpyAsync(d_off, h_bg_offsets, sizeof(long long) * n_img, cudaMemcpyHostToDevice, st));
+  }
+  pa.n_img = n_img; pa.srcs = d_srcs; pa.n_src = P + 1; pa.items = nullptr; pa.n_items = n_items;
+  pa.default_flags = CG_ITEM_FLUX_BAND; pa.implicit_mode = 1; pa.img_boxes = d_boxes;
+  pa.aux_per_img = d_bg ? 1 : 0;
+  pa.bound_cap = 0; pa.max_patch_px = max_px; pa.hdr = (ItemHdr*)(base + L.hdr);
+  pa.tab = base + L.tab; pa.worklist = (int2*)(base + L.worklist); pa.worklist_cap = L.worklist_cap;
+  pa.cnt = cnt; pa.filters = g_d_filters;
+  rc = run_prepare<float>(pa, st);
+  if (rc) return rc;
+  RenderArgs ra;
+  memset(&ra, 0, sizeof ra);
+  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.cnt = cnt;
+  ra.aux = d_bg; ra.aux_offsets = d_off; ra.partials = (double*)(base + L.partials);
+  rc = run_render<float, MODE_POISSON>(ra, n_items, st);
+  if (rc) return rc;
+  double* item_ll = (double*)(base + L.item_ll);
+  items_finalize_kernel<<<(unsigned)((n_items + 255) / 256), 256, 0, st>>>(
+      pa.hdr, ra.partials, n_items, CG_LL_POISSON_BG, item_ll, nullptr, 1);
+  LAUNCH_CHECK();
+  int* guard_list = guard > 0 ? (int*)(base + L.guard_list) : nullptr;
+  score_finalize_kernel<<<(P + 255) / 256, 256, 0, st>>>(item_ll, n_img, P, d_log_terms, d_log_u, guard,
+                                                        d_delta, d_accept, cnt, guard_list, L.guard_cap);
+  LAUNCH_CHECK();
+  if (guard > 0) {
+    // float64 re-score of the guard-band proposals (+ the current state)
+    Counters* cnt2 = (Counters*)(base + L.counters2);
+    CUDA_TRY(cudaMemsetAsync(cnt2, 0, sizeof(Counters), st));
+    clamp_guard_kernel<<<1, 1, 0, st>>>(cnt, L.guard_cap);
+    LAUNCH_CHECK();
+    PrepArgs p2 = pa;
+    p2.implicit_mode = 2; p2.ind_list = guard_list; p2.ind_count = &cnt->guard_count;
+    p2.n_items = L.n_items2; p2.hdr = (ItemHdr*)(base + L.hdr2); p2.tab = base + L.tab2;
+    p2.worklist = (int2*)(base + L.worklist2); p2.worklist_cap = L.worklist_cap2; p2.cnt = cnt2;
+    rc = run_prepare<double>(p2, st);
+    if (rc) return rc;
+    RenderArgs r2 = ra;
+    r2.hdr = p2.hdr; r2.tab = p2.tab; r2.worklist = p2.worklist; r2.cnt = cnt2;
+    r2.partials = (double*)(base + L.partials2);
+    rc = run_render<double, MODE_POISSON>(r2, L.n_items2, st);
+    if (rc) return rc;
+    double* item_ll2 = (double*)(base + L.item_ll2);
+    items_finalize_kernel<<<(unsigned)((L.n_items2 + 255) / 256), 256, 0, st>>>(
+        p2.hdr, r2.partials, L.n_items2, CG_LL_POISSON_BG, item_ll2, &cnt->guard_count, n_img);
+    LAUNCH_CHECK();
+    score_rescore_kernel<<<(L.guard_cap + 255) / 256, 256, 0, st>>>(
+        item_ll2, n_img, cnt, guard_list, L.guard_cap, d_log_terms, d_log_u, d_delta, d_accept);
+    LAUNCH_CHECK();
+  }
+  if (d_n_guard)
+    CUDA_TRY(cudaMemcpyAsync(d_n_guard, &cnt->guard_count, sizeof(int), cudaMemcpyDeviceToDevice, st));
+  g_last_counters = cnt;
+  return CG_OK;
+}
+
+// ---- A16 / A17 -----------------------------------------------------------------
+int cg_planck_fluxes(const double* d_T, const double* d_b, int64_t n, double* d_out, void* stream) {
+  NEED_INIT();
+  if (!g_filters_loaded) return fail(CG_ESTATE, "cg_set_filter_curves() has not been called");
+  if (n <= 0) return CG_OK;
+  long long threads = n * CG_NUM_BANDS * 32;
+  planck_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(d_T, d_b, n, d_out,
+                                                                                     g_d_filters);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
+int cg_eigen_fluxes(const double* d_z, const double* d_w, const double* d_m, const double* d_B,
+                    const double* d_lam0, int32_t n_chain, int32_t K, int32_t V,
+                    const double* d_fluxes, const double* d_fluxes_ivar, double* d_mu, double* d_ll,
+                    void* stream) {
+  NEED_INIT();
+  if (!g_filters_loaded) return fail(CG_ESTATE, "cg_set_filter_curves() has not been called");
+  if (n_chain <= 0) return CG_OK;
+  if (d_fluxes && !d_fluxes_ivar) return fail(CG_EINVAL, "fluxes_ivar required with fluxes");
+  eigen_flux_kernel<<<n_chain, 256, 0, (cudaStream_t)stream>>>(d_z, d_w, d_m, d_B, d_lam0, K, V, d_fluxes,
+                                                               d_fluxes_ivar, d_mu, d_ll, g_d_filters);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
+}  // extern "C"

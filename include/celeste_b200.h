@@ -1,0 +1,259 @@
+/*
+ * celeste_b200.h -- C ABI of libceleste_b200.so
+ *
+ * B200-native (sm_100a) implementation of the CelestePy per-proposal image
+ * log-likelihood: mixture-of-Gaussians rendering of stars / galaxies onto
+ * SDSS-style band images, the Poisson pixel log-likelihood, and batched
+ * Metropolis-Hastings proposal scoring with on-device accept/reject.
+ *
+ * The reference (HIPS/DESI-MCMC) has no FFI registry; its boundary is the
+ * Python call surface of its Cython modules and the numpy functions around
+ * them.  Each entry point below names the reference interface it replaces
+ * (paths relative to the reference repository root).  The reference-side
+ * binding (a ctypes stub) is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative CG_E* code on failure;
+ *     cg_last_error() returns the message of the calling thread's last failure.
+ *   - pointers named d_* are DEVICE pointers (owned by the caller, normally
+ *     torch tensors); pointers named h_* are HOST pointers; `stream` is a
+ *     cudaStream_t passed as void* (NULL = legacy default stream).
+ *   - all work is enqueued on `stream`; nothing synchronises unless stated.
+ *   - no exceptions cross this boundary; no persistent device allocation is
+ *     made by the library except the small CgImage descriptor copy.
+ */
+#ifndef CELESTE_B200_H
+#define CELESTE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CG_ABI_VERSION 1
+
+#define CG_MAX_PSF 4      /* PSF mixture components per image (reference: 3, fits_image.py:130-133) */
+#define CG_NUM_BANDS 5    /* u g r i z */
+#define CG_MAX_COMP 48    /* components per (source, image): (6 exp + 8 dev) x 3 PSF = 42 */
+#define CG_MAX_IMAGES 64  /* images per call */
+
+enum {
+  CG_OK = 0,
+  CG_EINVAL = -1,   /* bad argument (the Python shim raises ValueError) */
+  CG_ECUDA = -2,    /* CUDA runtime error (sticky; RuntimeError)        */
+  CG_ENOMEM = -3,   /* workspace too small                              */
+  CG_ESTATE = -4    /* library not initialised                          */
+};
+
+/* ---- data contract ------------------------------------------------------ */
+
+/* What the hot path reads from FitsImage (CelestePy/fits_image.py:16-155). */
+typedef struct CgImageDesc {
+  int32_t H, W;                 /* nelec.shape                         (:90-92)  */
+  int32_t band;                 /* 0..4 = u g r i z                              */
+  int32_t n_psf;                /* PSF components, <= CG_MAX_PSF        (:130)   */
+  double epsilon;               /* sky rate, electrons / pixel          (:113)   */
+  double kappa;                 /* gain                                 (:112)   */
+  double calib;                 /* nanomaggies per count                (:116)   */
+  double psf_w[CG_MAX_PSF];     /* weights                              (:130)   */
+  double psf_mu[CG_MAX_PSF][2]; /* means (x, y)                         (:131)   */
+  double psf_cov[CG_MAX_PSF][3];/* var_x, var_y, cov_xy                 (:132-138) */
+  double rho_n[2];              /* pixel reference point (0-based)      (:99)    */
+  double phi_n[2];              /* equatorial reference point           (:100)   */
+  double ups[4];                /* Ups_n, row-major CD matrix           (:101-102) */
+  const float* d_nelec;         /* H*W electrons, row-major [y][x]; may be NULL for render-only */
+  const float* d_mask;          /* H*W invvar-style mask (0 = bad) or NULL = all good */
+} CgImageDesc;
+
+typedef struct CgImage CgImage;   /* opaque handle */
+
+/* What the hot path reads from SrcParams (CelestePy/celeste_src.py:12-157). */
+typedef struct CgSource {
+  int32_t type;        /* a: 0 = star, 1 = galaxy                         */
+  int32_t flags;       /* CG_SRC_* */
+  double u[2];         /* RA, Dec (degrees)                               */
+  double flux[CG_NUM_BANDS]; /* nanomaggies, u g r i z                    */
+  double theta;        /* exp-profile weight                              */
+  double sigma;        /* effective radius, arcsec                        */
+  double phi;          /* position angle                                  */
+  double rho;          /* axis ratio                                      */
+  double t;            /* star temperature (K), used with CG_SRC_PLANCK   */
+  double b;            /* star brightness ell/d^2, used with CG_SRC_PLANCK*/
+} CgSource;
+
+#define CG_SRC_PLANCK 1   /* star flux from black-body route (celeste.py:38-40, planck.py:155) */
+
+/* One unit of render work: a (source, image) pair. */
+typedef struct CgItem {
+  int32_t src;         /* index into the source array */
+  int32_t img;         /* index into the image array  */
+  int32_t flags;       /* CG_ITEM_* */
+  int32_t box[4];      /* x0, x1, y0, y1 (half-open) when CG_ITEM_FIXED_BOX */
+  int32_t aux;         /* index of the per-item auxiliary patch (background / photons), or -1 */
+} CgItem;
+
+#define CG_ITEM_FLUX_BAND   0x00  /* rate = unit patch * flux/calib*kappa (celeste.py:80-81,91-92) */
+#define CG_ITEM_FLUX_UNIT   0x01  /* unit-flux patch (celeste.py:114, celeste_galaxy_conditionals.py:185) */
+#define CG_ITEM_FIXED_BOX   0x04  /* use box[] (the xlim/ylim arguments of the reference) */
+#define CG_ITEM_TRUNC_BOX   0x08  /* galaxy footprint by int() truncation (celeste_galaxy_conditionals.py:161-162) */
+#define CG_ITEM_PROF_EXP    0x10  /* exponential profile only, no theta weight (gen_galaxy_prof_psf_image 'exp') */
+#define CG_ITEM_PROF_DEV    0x20  /* de Vaucouleurs profile only ('dev') */
+#define CG_ITEM_HEADER_CD   0x40  /* galaxy transformation from Ups_n instead of cd_at_pixel (:33) */
+#define CG_ITEM_NO_MASK     0x80  /* ignore the image mask (sources.py:188-237 has none) */
+
+/* Box of an item after preparation, readable by the host. */
+typedef struct CgBox { int32_t x0, x1, y0, y1; } CgBox;
+
+/* ---- life cycle --------------------------------------------------------- */
+
+int cg_abi_version(void);
+int cg_init(int device);                     /* select device, query SM count */
+int cg_shutdown(void);
+int cg_last_error(char* buf, size_t n);      /* copies the message, returns its length */
+int cg_sm_count(void);
+
+/* FitsImage constructor replacement (fits_image.py:48-155): copies the
+ * descriptor, derives invcovars/logdets (:141-145), R at err=.001 (:151-155). */
+int cg_image_create(const CgImageDesc* desc, CgImage** out);
+int cg_image_destroy(CgImage* img);
+int cg_image_set_epsilon(CgImage* img, double epsilon);    /* models.py:159 resamples epsilon */
+double cg_image_radius(const CgImage* img);                /* FitsImage.R */
+
+/* Filter curves for the black-body route (planck.py:31-55): per band,
+ * wavelengths (m, sorted) and h_vec = S*lambda/(hc)*dLambda, concatenated. */
+int cg_set_filter_curves(const double* h_wavelengths, const double* h_hvecs,
+                         const double* h_sens, const int32_t* h_counts /* [5] */);
+
+/* ---- A2: util/like/gmm_like_fast.pyx:130-176 ---------------------------- */
+/* probs[n] = sum_k ws[k] N(x[n]; mus[k], sigs[k]).  All device pointers,
+ * float64 as in the reference; arithmetic is fp32 in centred coordinates. */
+int cg_gmm_like_2d(double* d_probs, const double* d_x, const double* d_ws,
+                   const double* d_mus, const double* d_sigs,
+                   int64_t N, int32_t K, void* stream);
+
+/* gmm_like_fast.pyx:34-77 */
+int cg_mvn2d_logpdf(double* d_lls, const double* d_x, const double* h_mean,
+                    const double* h_covinv, double logdet, int64_t N, void* stream);
+
+/* ---- A1: celeste_fast.pyx:29-94, :100-140 (host arrays, tiny) ----------- */
+int cg_galaxy_prof_psf_mixture_params(const double* W, const double* v_s,
+                                      const double* image_ws, const double* image_means,
+                                      const double* image_covars, int32_t K_psf,
+                                      const double* prof_amp, const double* prof_sigs,
+                                      int32_t K_prof,
+                                      double* weights, double* means, double* covars);
+int cg_galaxy_psf_mixture_params(const double* thetas, const double* W, const double* v_s,
+                                 const double* image_ws, const double* image_means,
+                                 const double* image_covars, int32_t K_psf,
+                                 const double* exp_amp, const double* exp_sigs, int32_t K_exp,
+                                 const double* dev_amp, const double* dev_sigs, int32_t K_dev,
+                                 double* weights, double* means, double* covars);
+
+/* A12: util/bound/bounding_box.py:9-31 (host) */
+double cg_calc_bounding_radius(const double* means, const double* covars, int32_t K,
+                               double error, const double* center);
+
+/* ---- render + likelihood engine ----------------------------------------- */
+
+/* Workspace size (bytes) the caller must provide (a device buffer, e.g. a
+ * torch uint8 tensor).  kind selects the entry point; n_items = number of
+ * (source, image) items (CG_WS_SCORE: (P+1)*n_img); max_patch_px bounds the
+ * pixels of one footprint; n_tiles (CG_WS_FIELD) = n_img * max_i
+ * cg_field_tiles(H_i, W_i). */
+#define CG_WS_RENDER 0
+#define CG_WS_FIELD 1
+#define CG_WS_ITEMS 2
+#define CG_WS_SCORE 3
+size_t cg_workspace_bytes(int32_t kind, int64_t n_items, int32_t n_img, int64_t max_patch_px,
+                          int64_t n_tiles);
+int32_t cg_field_tiles(int32_t H, int32_t W);
+
+/* A5/A6/A10: render patches.  For item i the rate patch (row-major,
+ * (y1-y0) x (x1-x0)) is written to d_patches + i*max_patch_px and its box to
+ * d_boxes[i].  h_items may be NULL: items are then the cross product
+ * source-major (item = src*n_img + img) with flags = default_flags.
+ * Replaces celeste.py:114-176 (star), celeste_galaxy_conditionals.py:185-214
+ * (galaxy, live route) and :134-182 (Cython route) and the flux scaling of
+ * celeste.py:72-96.  bound_cap > 0 caps the automatic footprint radius. */
+int cg_render_patches(CgImage* const* imgs, int32_t n_img,
+                      const CgSource* d_srcs, int32_t n_src,
+                      const CgItem* d_items, int64_t n_items, int32_t default_flags,
+                      double bound_cap, int64_t max_patch_px,
+                      float* d_patches, CgBox* d_boxes,
+                      void* d_workspace, size_t workspace_bytes, void* stream);
+
+/* A7/A8: celeste.py:203-252, models.py:88-108.  Full-frame model
+ * lambda = epsilon + sum_s patch_s and ll_img = sum(nelec*log(lambda) - lambda)
+ * for every image; d_ll[n_img] (double).  d_model[i] (device float*, H*W) may
+ * be NULL; pass d_model = NULL to skip all model output. */
+int cg_field_loglik(CgImage* const* imgs, int32_t n_img,
+                    const CgSource* d_srcs, int32_t n_src,
+                    double bound_cap, int64_t max_patch_px,
+                    double* d_ll, float* const* h_d_model,
+                    void* d_workspace, size_t workspace_bytes, void* stream);
+
+/* Likelihood modes of cg_items_loglik */
+#define CG_LL_POISSON_BG 0  /* sources.py:6-12 with model = aux + rate, data = nelec crop, mask = image mask
+                               (aux < 0: background = epsilon; sources.py:188-237) */
+#define CG_LL_CONDITIONAL 1 /* sources.py:134-183: sum_{rate>0} log(rate)*z - band_flux*sum(psf_w); z = aux patch */
+
+/* A13/A14/A15 building block: per-item log-likelihood over its box.  The aux
+ * patch of item i (background or photon counts, float, box-shaped row-major)
+ * is d_aux + aux_offsets[item.aux].  Output d_item_ll[n_items] (double). */
+int cg_items_loglik(CgImage* const* imgs, int32_t n_img,
+                    const CgSource* d_srcs, int32_t n_src,
+                    const CgItem* d_items, int64_t n_items,
+                    int32_t mode, double bound_cap, int64_t max_patch_px,
+                    const float* d_aux, const int64_t* d_aux_offsets,
+                    double* d_item_ll, CgBox* d_boxes, int32_t use_fp64,
+                    void* d_workspace, size_t workspace_bytes, void* stream);
+
+/* A15: Source.calculate_acceptance_logprob + the accept test
+ * (sources.py:258, :275-306) for P proposals of one source.
+ *   delta[p] = sum_img ll(prop_p) - sum_img ll(cur) + d_log_terms[p]
+ *   accept[p] = d_log_u[p] < delta[p]
+ * d_srcs[0] is the current state, d_srcs[1..P] the proposals.  h_boxes[n_img]
+ * are the cached bounding boxes, d_bg + bg_offsets[img] the cached background
+ * patches (sources.py:279-282).  Proposals whose margin |log_u - delta| is
+ * below `guard` are re-scored in float64 on device (guard <= 0 disables).
+ * d_n_guard (int32, may be NULL) receives the number of re-scored proposals.
+ * d_bg may be NULL: the background is then epsilon. */
+int cg_score_proposals(CgImage* const* imgs, int32_t n_img,
+                       const CgSource* d_srcs, int32_t P,
+                       const CgBox* h_boxes,
+                       const float* d_bg, const int64_t* h_bg_offsets,
+                       const double* d_log_terms, const double* d_log_u,
+                       double guard,
+                       double* d_delta, uint8_t* d_accept, int32_t* d_n_guard,
+                       void* d_workspace, size_t workspace_bytes, void* stream);
+
+/* ---- A16: planck.py:94-158 ----------------------------------------------- */
+/* out[i*5+band] = photons_expected_brightness(T[i], b[i], band); float64. */
+int cg_planck_fluxes(const double* d_T, const double* d_b, int64_t n,
+                     double* d_out, void* stream);
+
+/* ---- A17: experiments/redshift/redshift_utils.py:304-323,
+ *           quasar_infer_photometry.py:31-46 ------------------------------- */
+/* For chain c: spec = w[c] . B (K x V), lam_obs = lam0*(1+z[c]),
+ * mu[c] = project_to_bands(spec, lam_obs)*m[c]/(1+z[c]) -> d_mu[c*5+band];
+ * if d_fluxes != NULL also ll[c] = -0.5*sum(ivar*(fluxes-mu)^2). */
+int cg_eigen_fluxes(const double* d_z, const double* d_w, const double* d_m,
+                    const double* d_B, const double* d_lam0,
+                    int32_t n_chain, int32_t K, int32_t V,
+                    const double* d_fluxes, const double* d_fluxes_ivar,
+                    double* d_mu, double* d_ll, void* stream);
+
+/* ---- instrumentation ------------------------------------------------------ */
+/* Number of kernels launched by this library since cg_init (or last reset). */
+int64_t cg_launch_count(int reset);
+/* Component evaluations (pixel x component) of the last cg_field_loglik /
+ * cg_render_patches / cg_items_loglik / cg_score_proposals call: reads a
+ * device counter, synchronises `stream`. */
+int64_t cg_last_eval_count(void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CELESTE_B200_H */
