@@ -1,0 +1,322 @@
+#!/usr/bin/env python
+"""bench.py -- throughput of the B200 render + Poisson log-likelihood path.
+
+Step = one full-field log-likelihood pass (BASELINE.json config 2: synthetic
+Stripe-82 frame 2048x1489 x 5 bands, 500 mixed sources, footprints capped at
+101x101) over every field this rank owns.  Fields are independent, so ranks
+shard them with no pixel traffic (weak scaling, F fields per GPU; 8 GPUs x 8 =
+the 64 fields of config 5) and exchange one small float64 all-reduce per step
+(global log-likelihood + prior sufficient statistics).
+
+  value  component evaluations/s, source parameters already in HBM
+  e2e    the same through the host API: packed source parameters copied
+         pinned-host -> device every step, per-image log-likelihoods copied
+         back.  Image pixels stay resident (uploaded once when the Image is
+         constructed, as FitsImage reads its frame once).
+
+`--impl reference` times the reference's own CPU route (compiled Cython
+gmm_like_2d from oracle/_ref, all host threads) on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+H, W, N_SRC, STAR_FRAC, BOUND_CAP = 1489, 2048, 500, .6, 50.0
+MAX_PATCH_PX = 103 * 103
+METRIC = "source-pixel-component evals/s"
+WORKLOAD = ("C2 full-field log-likelihood: synthetic Stripe-82 frame 2048x1489 x 5 bands, 500 mixed "
+            "star/galaxy sources (60% stars), footprints capped at 101x101")
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._stop_ev = index, [], threading.Event()
+
+    def run(self):
+        while not self._stop_ev.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True,
+                                     text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            self._stop_ev.wait(0.1)
+
+    def stop(self):
+        self._stop_ev.set()
+        self.join(timeout=6)
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            for nm, v in zip(names, r[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_baseline(field, budget_s):
+    """The reference's CPU route on a bounded sample of field 0 (rank 0 only)."""
+    from desi_mcmc_b200 import synth
+    from oracle import cpu_path, ref_cpu as ref
+    be = cpu_path.backend()
+    rng = np.random.RandomState(field["seed"])
+    imgs = [ref.SyntheticImage(nelec=rng.poisson(430., size=(H, W)).astype(np.float64),
+                               **synth.image_kwargs(m)) for m in field["images"]]
+    srcs = [ref.SrcParams(u=s["u"], a=s["a"], b=s["b"], t=s["t"], theta=s["theta"], phi=s["phi"],
+                          sigma=s["sigma"], rho=s["rho"], fluxes=s["fluxes"]) for s in field["sources"]]
+    r = cpu_path.timed_sample(imgs, srcs, BOUND_CAP, budget_s=budget_s, be=be)
+    return {"value": r["evals"] / r["seconds"], "unit": "evals/s", "cores": cpu_path.threads_used(be[0]),
+            "host_cores": os.cpu_count(), "kind": be[0],
+            "sample": "field 0: first %d of %d sources x %d bands rendered with %s gmm_like_2d "
+                      "(float64) + full-frame Poisson log-likelihood; %.3g evals in %.1f s"
+                      % (r["n_src"], len(srcs), r["n_img"],
+                         "the compiled reference (oracle/_ref, OpenMP)" if be[0] == "reference"
+                         else "the NumPy port", r["evals"], r["seconds"]),
+            "evals": r["evals"], "seconds": r["seconds"]}
+
+
+def run_reference(args, rank):
+    """--impl reference: CPU arm, rank 0 only."""
+    if rank != 0:
+        return
+    from desi_mcmc_b200 import synth
+    field = synth.make_field(1005, H, W, N_SRC, STAR_FRAC)
+    per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
+    for _ in range(args.warmup):
+        cpu_baseline(field, per_step)
+    ev, sec, last = 0, 0.0, None
+    for _ in range(args.steps):
+        last = cpu_baseline(field, per_step)
+        ev += last["evals"]
+        sec += last["seconds"]
+    val = ev / sec
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "evals/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sec / max(1, args.steps),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": {"workload": WORKLOAD, "sample_per_step": last["sample"]},
+            "cpu_baseline": {"value": val, "unit": "evals/s", "cores": last["cores"], "kind": last["kind"],
+                             "sample": last["sample"]},
+            "e2e": {"value": val, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--fields-per-gpu", type=int, default=8)
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-proposals", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from desi_mcmc_b200 import engine, synth, _ffi
+
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    engine.init(local)
+    dev = engine.device()
+    F = args.fields_per_gpu
+
+    # ---- synthetic fields of this rank (config 5 seeds 1005+f), pixels drawn on device
+    fields, images, srcs_host, srcs_dev = [], [], [], []
+    gen = torch.Generator(device=dev)
+    for f in range(F):
+        fid = rank * F + f
+        fld = synth.make_field(1005 + fid, H, W, N_SRC, STAR_FRAC)
+        imgs = [engine.Image(nelec=torch.zeros((H, W), dtype=torch.float32, device=dev),
+                             **synth.image_kwargs(m)) for m in fld["images"]]
+        packed = engine.pack_sources([engine.SrcParams(u=s["u"], a=s["a"], theta=s["theta"], phi=s["phi"],
+                                                       sigma=s["sigma"], rho=s["rho"], fluxes=s["fluxes"])
+                                      for s in fld["sources"]])
+        d_src = engine.to_device(packed)
+        _, models = engine.field_loglik(imgs, d_src, bound_cap=BOUND_CAP, max_patch_px=MAX_PATCH_PX,
+                                        return_model=True)
+        gen.manual_seed(1005 + fid)
+        for im, lam in zip(imgs, models):
+            im.set_nelec(torch.poisson(lam, generator=gen))
+        del models
+        fields.append(fld)
+        images.append(imgs)
+        srcs_host.append(packed)
+        srcs_dev.append(d_src)
+    torch.cuda.synchronize()
+
+    ws = engine.field_workspace(images[0], N_SRC, MAX_PATCH_PX)
+    L = engine.lib()
+    import ctypes as C
+    harrs = [(C.c_void_p * 5)(*[im._h for im in imgs]) for imgs in images]
+    ll_dev = torch.zeros((F, 5), dtype=torch.float64, device=dev)
+    stats = torch.zeros(64, dtype=torch.float64, device=dev)     # [sum ll, n_star, n_gal, flux moments ...]
+    n_star = float(sum(1 for fld in fields for s in fld["sources"] if s["a"] == 0))
+
+    def step_device(d_srcs_list):
+        st = engine.stream_ptr()
+        for f in range(F):
+            _ffi.check(L.cg_field_loglik(harrs[f], 5, d_srcs_list[f].data_ptr(), N_SRC, BOUND_CAP,
+                                         MAX_PATCH_PX, ll_dev[f].data_ptr(), None, ws.data_ptr(),
+                                         ws.numel(), st))
+        if world > 1:
+            stats.zero_()
+            stats[0] = ll_dev.sum()
+            stats[1] = n_star
+            dist.all_reduce(stats)
+
+    # evaluations per step (constant): count once per field
+    evals_step = 0
+    for f in range(F):
+        _ffi.check(L.cg_field_loglik(harrs[f], 5, srcs_dev[f].data_ptr(), N_SRC, BOUND_CAP, MAX_PATCH_PX,
+                                     ll_dev[f].data_ptr(), None, ws.data_ptr(), ws.numel(),
+                                     engine.stream_ptr()))
+        evals_step += engine.last_eval_count()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident leg
+    for _ in range(args.warmup):
+        step_device(srcs_dev)
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    engine.launch_count(reset=True)
+    engine.profile_render(True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step_device(srcs_dev)
+    e1.record()
+    barrier()
+    dev_ms = max_over_ranks(e0.elapsed_time(e1))
+    launches = engine.launch_count()
+    render_ms, render_n = engine.profile_render_read()
+    engine.profile_render(False)
+    clocks = sampler.stop()
+    ll_ref = ll_dev.cpu().numpy().copy()
+
+    # ---- end-to-end leg: host source arrays -> pinned -> device, ll -> host
+    stages = [engine.PinnedStage(N_SRC * _ffi.SRC_DTYPE.itemsize) for _ in range(F)]
+    ll_host = torch.zeros((F, 5), dtype=torch.float64).pin_memory()
+
+    def step_e2e():
+        d = [stages[f].upload(srcs_host[f]) for f in range(F)]
+        step_device(d)
+        ll_host.copy_(ll_dev, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(ll_host.sum())
+
+    for _ in range(args.warmup):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        total_ll = step_e2e()
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    assert np.array_equal(ll_host.numpy(), ll_ref), "e2e and device-resident results differ"
+
+    total_evals = evals_step * world          # every rank holds the same shapes, different seeds
+    if world > 1:
+        t = torch.tensor([float(evals_step)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t)
+        total_evals = float(t.item())
+    value = total_evals * args.steps / (dev_ms * 1e-3)
+    e2e_value = total_evals * args.steps / e2e_s
+
+    if rank == 0:
+        xu_peak = engine.pipe_probe(0)
+        fma_peak = engine.pipe_probe(1)
+        achieved = evals_step * args.steps / (render_ms * 1e-3) if render_ms > 0 else None
+        sm = engine.sm_count()
+        nominal = sm * 16 * (clocks["sm_mhz"] or 0) * 1e6
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        line = {
+            "metric": METRIC, "value": value, "unit": "evals/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32 rates, f64 log-likelihood accumulation",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "fields_per_gpu": F, "fields_total": F * world,
+                       "evals_per_step_per_gpu": evals_step, "pixels_per_step_per_gpu": F * 5 * H * W,
+                       "l2": "inputs larger than L2 (%d MB of pixel data per GPU per step)" % (F * 5 * H * W * 4 >> 20),
+                       "e2e_inputs": "packed source parameters (host) per step; image pixels resident",
+                       "parallelism": "fields sharded over ranks; one float64 all-reduce per step" if world > 1 else "single GPU"},
+            "e2e": {"value": e2e_value, "unit": "evals/s", "ms_per_step": 1e3 * e2e_s / args.steps,
+                    "h2d_bytes_per_step": F * N_SRC * _ffi.SRC_DTYPE.itemsize, "d2h_bytes_per_step": F * 5 * 8},
+            "gpu_launches": launches,
+            "roofline": {"kernel": "render_kernel<float, MODE_PATCH>", "bound": "xu",
+                         "achieved": achieved, "peak": xu_peak, "unit": "evals/s (1 eval = 1 MUFU.EX2 + 3 FP32)",
+                         "frac": (achieved / xu_peak) if achieved else None,
+                         "peak_source": "measured live: MUFU.EX2 probe kernel on this GPU (cg_pipe_probe); "
+                                        "nominal %d SMs x 16/clk x %.0f MHz = %.3g" % (sm, clocks["sm_mhz"] or 0, nominal),
+                         "fp32_fma_peak": fma_peak, "kernel_ms_total": render_ms, "kernel_launches": render_n,
+                         "kernel_share_of_step": render_ms / dev_ms if dev_ms else None,
+                         "traffic": None,
+                         "hbm_peak_gbs": peaks.get("hbm_gbs")},
+            "clocks": clocks,
+            "total_loglik": total_ll,
+        }
+        if not args.no_cpu_baseline and world == 1:
+            line["cpu_baseline"] = {k: v for k, v in cpu_baseline(fields[0], args.cpu_seconds).items()
+                                    if k not in ("evals", "seconds")}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

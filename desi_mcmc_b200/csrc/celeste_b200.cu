@@ -953,6 +953,46 @@ __global__ void __launch_bounds__(256) eigen_flux_kernel(const double* z, const 
   }
 }
 
+// ---------------------------------------------------------------------------
+// XU (MUFU.EX2) throughput probe: the roofline denominator of render_kernel,
+// measured on the device it runs on.  8 independent ex2 chains per thread.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) xu_probe_kernel(float* out, int iters) {
+  float v[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v[j] = -1.0f - 0.001f * (float)(threadIdx.x + j);
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = ex2_approx(v[j]) - 1.5f;
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s += v[j];
+  if (s == 123.456f) out[blockIdx.x * blockDim.x + threadIdx.x] = s;   // never true; keeps the chains live
+}
+
+// FP32 FMA throughput probe (secondary pipe of render_kernel).
+__global__ void __launch_bounds__(256) fma_probe_kernel(float* out, int iters) {
+  float v[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v[j] = 0.5f + 0.001f * (float)(threadIdx.x + j);
+  const float a = 0.999f, b = 0.0007f;
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = fmaf(v[j], a, b);
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s += v[j];
+  if (s == 123.456f) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+// per-launch CUDA-event timing of render_kernel (bench.py's roofline leg)
+#define PROF_MAX 8192
+static bool g_prof_on = false;
+static std::vector<cudaEvent_t> g_prof_ev;   // 2 per launch
+static int g_prof_n = 0;
+
 // ===========================================================================
 // host side
 // ===========================================================================
@@ -1296,7 +1336,10 @@ static int run_prepare(const PrepArgs& pa, cudaStream_t st) {
 template <typename real, int MODE>
 static int run_render(const RenderArgs& ra, long long n_items, cudaStream_t st) {
   if (n_items == 0) return CG_OK;
+  const bool prof = g_prof_on && g_prof_n < PROF_MAX;
+  if (prof) cudaEventRecord(g_prof_ev[2 * g_prof_n], st);
   render_kernel<real, MODE><<<render_grid(), STRIP_THREADS, 0, st>>>(ra);
+  if (prof) { cudaEventRecord(g_prof_ev[2 * g_prof_n + 1], st); ++g_prof_n; }
   LAUNCH_CHECK();
   return CG_OK;
 }
@@ -1549,6 +1592,60 @@ int cg_eigen_fluxes(const double* d_z, const double* d_w, const double* d_m, con
   eigen_flux_kernel<<<n_chain, 256, 0, (cudaStream_t)stream>>>(d_z, d_w, d_m, d_B, d_lam0, K, V, d_fluxes,
                                                                d_fluxes_ivar, d_mu, d_ll, g_d_filters);
   LAUNCH_CHECK();
+  return CG_OK;
+}
+
+// ---- instrumentation -------------------------------------------------------------
+int cg_profile_render(int enable) {
+  NEED_INIT();
+  if (enable && g_prof_ev.empty()) {
+    g_prof_ev.resize(2 * PROF_MAX);
+    for (auto& e : g_prof_ev) CUDA_TRY(cudaEventCreate(&e));
+  }
+  g_prof_on = enable != 0;
+  g_prof_n = 0;
+  return CG_OK;
+}
+
+int cg_profile_render_read(double* total_ms, int64_t* launches) {
+  NEED_INIT();
+  double t = 0;
+  for (int i = 0; i < g_prof_n; ++i) {
+    CUDA_TRY(cudaEventSynchronize(g_prof_ev[2 * i + 1]));
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, g_prof_ev[2 * i], g_prof_ev[2 * i + 1]));
+    t += ms;
+  }
+  if (total_ms) *total_ms = t;
+  if (launches) *launches = g_prof_n;
+  return CG_OK;
+}
+
+int cg_pipe_probe(int which, double* ops_per_s, void* stream) {
+  NEED_INIT();
+  cudaStream_t st = (cudaStream_t)stream;
+  const int iters = 4096, blocks = g_sm_count * 8, threads = 256;
+  float* d_out = nullptr;
+  CUDA_TRY(cudaMalloc(&d_out, sizeof(float) * blocks * threads));
+  cudaEvent_t e0, e1;
+  CUDA_TRY(cudaEventCreate(&e0));
+  CUDA_TRY(cudaEventCreate(&e1));
+  float best = 1e30f;
+  for (int rep = 0; rep < 6; ++rep) {
+    CUDA_TRY(cudaEventRecord(e0, st));
+    if (which == 0) xu_probe_kernel<<<blocks, threads, 0, st>>>(d_out, iters);
+    else fma_probe_kernel<<<blocks, threads, 0, st>>>(d_out, iters);
+    CUDA_TRY(cudaEventRecord(e1, st));
+    LAUNCH_CHECK();
+    CUDA_TRY(cudaEventSynchronize(e1));
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+    if (rep > 0 && ms < best) best = ms;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(d_out);
+  if (ops_per_s) *ops_per_s = (double)blocks * threads * 8.0 * iters / (best * 1e-3);
   return CG_OK;
 }
 

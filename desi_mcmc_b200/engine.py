@@ -1,0 +1,641 @@
+"""Host side of the B200 render + likelihood engine.
+
+torch owns every device buffer (images, source arrays, patches, workspaces)
+and supplies the stream; all arithmetic happens in libceleste_b200.so through
+the C ABI (``_ffi``).  Nothing here computes a likelihood on the host.
+
+Data contract mirrors
+  * ``Image``     <- CelestePy/fits_image.py:16-155 (FitsImage fields the hot
+                     path reads; no FITS I/O)
+  * ``SrcParams`` <- CelestePy/celeste_src.py:12-157
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Iterable, Sequence
+
+import numpy as np
+import torch
+
+from . import _ffi
+from ._ffi import (BOX_DTYPE, CG_ITEM_FIXED_BOX, CG_ITEM_FLUX_BAND, CG_ITEM_FLUX_UNIT,
+                   CG_LL_CONDITIONAL, CG_LL_POISSON_BG, CG_MAX_IMAGES, CG_NUM_BANDS,
+                   CG_SRC_PLANCK, ITEM_DTYPE, SRC_DTYPE, check)
+
+BANDS = ["u", "g", "r", "i", "z"]
+
+_state = {"device": None, "lib": None, "ws": {}, "filters": False}
+
+
+# ---------------------------------------------------------------------------
+# life cycle
+# ---------------------------------------------------------------------------
+def init(device: int | None = None):
+    """Load the library and bind it to one GPU (one process per GPU)."""
+    lib = _ffi.load()
+    if not torch.cuda.is_available():
+        raise RuntimeError("desi_mcmc_b200 needs a CUDA device: the render/likelihood path "
+                           "has no CPU fallback")
+    if device is None:
+        device = int(os.environ.get("LOCAL_RANK", "0"))
+    if _state["device"] == device:
+        return lib
+    torch.cuda.set_device(device)
+    torch.zeros(1, device="cuda:%d" % device)      # create the primary context torch shares
+    check(lib.cg_init(device))
+    _state.update(device=device, lib=lib, ws={}, filters=False)
+    return lib
+
+
+def lib():
+    if _state["lib"] is None:
+        return init()
+    return _state["lib"]
+
+
+def device() -> torch.device:
+    lib()
+    return torch.device("cuda", _state["device"])
+
+
+def stream_ptr() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def sm_count() -> int:
+    return lib().cg_sm_count()
+
+
+def launch_count(reset: bool = False) -> int:
+    return int(lib().cg_launch_count(1 if reset else 0))
+
+
+def last_eval_count() -> int:
+    """pixel x component evaluations of the last engine call (synchronises)."""
+    n = int(lib().cg_last_eval_count(stream_ptr()))
+    if n < 0:
+        raise MemoryError(_ffi.last_error())
+    return n
+
+
+def profile_render(enable: bool) -> None:
+    """Start (and reset) / stop per-launch CUDA-event timing of render_kernel."""
+    check(lib().cg_profile_render(1 if enable else 0))
+
+
+def profile_render_read():
+    """-> (total milliseconds, launches) of the render_kernel launches recorded."""
+    ms, n = C.c_double(0), C.c_int64(0)
+    check(lib().cg_profile_render_read(C.byref(ms), C.byref(n)))
+    return ms.value, n.value
+
+
+def pipe_probe(which: int = 0) -> float:
+    """Measured MUFU.EX2 (0) or FP32-FMA (1) instructions*lanes per second."""
+    v = C.c_double(0)
+    check(lib().cg_pipe_probe(which, C.byref(v), stream_ptr()))
+    return v.value
+
+
+def _workspace(kind: int, n_items: int, n_img: int, max_patch_px: int, n_tiles: int = 0):
+    need = int(lib().cg_workspace_bytes(kind, int(n_items), int(n_img), int(max_patch_px), int(n_tiles)))
+    key = kind
+    ws = _state["ws"].get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.empty(max(need, 1 << 20), dtype=torch.uint8, device=device())
+        _state["ws"][key] = ws
+    return ws
+
+
+def to_device(a: np.ndarray) -> torch.Tensor:
+    """Host POD array -> device bytes (pageable host memory; see PinnedStage
+    for the steady-state path)."""
+    a = np.ascontiguousarray(a)
+    t = torch.from_numpy(a.view(np.uint8).reshape(-1))
+    return t.to(device(), non_blocking=False)
+
+
+class PinnedStage(object):
+    """A pinned host buffer + device twin for per-step H2D of POD arrays."""
+
+    def __init__(self, nbytes: int):
+        self.host = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+        self.dev = torch.empty(nbytes, dtype=torch.uint8, device=device())
+        self.np = self.host.numpy()
+
+    def upload(self, a: np.ndarray) -> torch.Tensor:
+        raw = a.view(np.uint8).reshape(-1)
+        n = raw.size
+        self.np[:n] = raw
+        self.dev[:n].copy_(self.host[:n], non_blocking=True)
+        return self.dev
+
+
+# ---------------------------------------------------------------------------
+# data contract
+# ---------------------------------------------------------------------------
+class SrcParams(object):
+    """celeste_src.py:12-157.  ``fluxes`` may be a length-5 array (ugriz) or a
+    band->value dict, as the reference accepts both."""
+
+    def __init__(self, u, a=None, b=None, t=None, v=None, theta=None, phi=None,
+                 sigma=None, rho=None, fluxes=None, ell=None, d=None, header=None):
+        self.a = a
+        self.u = np.asarray(u, dtype=np.float64)
+        self.b, self.t = b, t
+        self.v = v
+        self.theta, self.phi, self.sigma, self.rho = theta, phi, sigma, rho
+        if isinstance(fluxes, dict):
+            fluxes = [fluxes[c] for c in BANDS]
+        self.fluxes = None if fluxes is None else np.asarray(fluxes, dtype=np.float64)
+        self.ell, self.d, self.header = ell, d, header
+
+    @property
+    def flux_dict(self):
+        return {c: v for c, v in zip(BANDS, self.fluxes)}
+
+    @property
+    def shape(self):
+        return np.array([self.theta, self.sigma, self.phi, self.rho])
+
+    def is_star(self):
+        return self.a == 0
+
+    def is_galaxy(self):
+        return self.a == 1
+
+
+def pack_sources(srcs: Sequence, out: np.ndarray | None = None) -> np.ndarray:
+    """SrcParams-like objects -> CgSource array (include/celeste_b200.h).
+    A star with a truthy temperature takes the black-body route, exactly the
+    reference's test ``if src.t`` (celeste.py:38)."""
+    n = len(srcs)
+    arr = np.zeros(n, dtype=SRC_DTYPE) if out is None else out[:n]
+    for i, s in enumerate(srcs):
+        r = arr[i]
+        if s.a not in (0, 1):
+            raise ValueError("source type unknown")
+        r["type"] = int(s.a)
+        r["u"] = s.u
+        flags = 0
+        if s.fluxes is not None:
+            r["flux"] = s.fluxes
+        if s.a == 0 and s.t:
+            flags |= CG_SRC_PLANCK
+            r["t"] = s.t
+            r["b"] = s.b
+        if s.a == 1:
+            r["theta"], r["sigma"], r["phi"], r["rho"] = s.theta, s.sigma, s.phi, s.rho
+        r["flags"] = flags
+    return arr
+
+
+def pack_source_fields(type_, u, flux, theta=None, sigma=None, phi=None, rho=None,
+                       t=None, b=None) -> np.ndarray:
+    """Vectorised packer for arrays of parameters (proposal batches)."""
+    u = np.asarray(u, dtype=np.float64)
+    n = u.shape[0]
+    arr = np.zeros(n, dtype=SRC_DTYPE)
+    arr["type"] = type_
+    arr["u"] = u
+    arr["flux"] = flux
+    for name, val in (("theta", theta), ("sigma", sigma), ("phi", phi), ("rho", rho)):
+        if val is not None:
+            arr[name] = val
+    if t is not None:
+        arr["t"] = t
+        arr["b"] = b
+        arr["flags"] = np.where((np.asarray(type_) == 0) & (np.asarray(t) != 0), CG_SRC_PLANCK, 0)
+    return arr
+
+
+class Image(object):
+    """Device-resident mirror of FitsImage (fits_image.py:16-155): the caller
+    passes what the FITS header/frames would hold.  ``nelec`` is uploaded once
+    (float32: photo-electron counts are integers below 2**24) and stays in HBM."""
+
+    def __init__(self, band, nelec, calib, gain, rho_n, phi_n, Ups_n, psf_weights, psf_means,
+                 psf_covars, sky=None, epsilon=None, invvar=None):
+        L = lib()
+        self.band = band if isinstance(band, str) else BANDS[band]
+        self.band_index = BANDS.index(self.band)
+        if isinstance(nelec, torch.Tensor):
+            self.d_nelec = nelec.to(device(), dtype=torch.float32).contiguous()
+        else:
+            self.d_nelec = torch.from_numpy(np.ascontiguousarray(nelec, dtype=np.float32)).to(device())
+        self.shape = tuple(self.d_nelec.shape)
+        if len(self.shape) != 2:
+            raise ValueError("nelec must be 2-d")
+        self.d_mask = None
+        if invvar is not None:
+            if isinstance(invvar, torch.Tensor):
+                self.d_mask = invvar.to(device(), dtype=torch.float32).contiguous()
+            else:
+                self.d_mask = torch.from_numpy(np.ascontiguousarray(invvar, dtype=np.float32)).to(device())
+            if tuple(self.d_mask.shape) != self.shape:
+                raise ValueError("invvar shape must equal nelec shape")
+        self.rho_n = np.asarray(rho_n, dtype=np.float64)
+        self.phi_n = np.asarray(phi_n, dtype=np.float64)
+        self.Ups_n = np.asarray(Ups_n, dtype=np.float64).reshape(2, 2)
+        self.Ups_n_inv = np.linalg.inv(self.Ups_n)
+        self.kappa = float(gain)
+        if epsilon is None:
+            if sky is None:
+                raise ValueError("pass sky or epsilon")
+            epsilon = float(sky) * self.kappa            # fits_image.py:113,119
+        self.epsilon = float(epsilon)
+        self.calib = float(calib)
+        self.weights = np.asarray(psf_weights, dtype=np.float64)
+        self.means = np.asarray(psf_means, dtype=np.float64).reshape(-1, 2)
+        self.covars = np.asarray(psf_covars, dtype=np.float64).reshape(-1, 2, 2)
+        K = self.weights.shape[0]
+        if not (self.means.shape[0] == K == self.covars.shape[0]):
+            raise ValueError("PSF weights, means and covariances must have same first dimension")
+        if K > _ffi.CG_MAX_PSF:
+            raise ValueError("at most %d PSF components" % _ffi.CG_MAX_PSF)
+        d = _ffi.CgImageDesc()
+        d.H, d.W = self.shape
+        d.band, d.n_psf = self.band_index, K
+        d.epsilon, d.kappa, d.calib = self.epsilon, self.kappa, self.calib
+        for k in range(K):
+            d.psf_w[k] = self.weights[k]
+            d.psf_mu[k][0], d.psf_mu[k][1] = self.means[k]
+            d.psf_cov[k][0] = self.covars[k, 0, 0]
+            d.psf_cov[k][1] = self.covars[k, 1, 1]
+            d.psf_cov[k][2] = self.covars[k, 0, 1]
+        d.rho_n[0], d.rho_n[1] = self.rho_n
+        d.phi_n[0], d.phi_n[1] = self.phi_n
+        for j, v in enumerate(self.Ups_n.ravel()):
+            d.ups[j] = v
+        d.d_nelec = self.d_nelec.data_ptr()
+        d.d_mask = self.d_mask.data_ptr() if self.d_mask is not None else None
+        h = C.c_void_p()
+        check(L.cg_image_create(C.byref(d), C.byref(h)))
+        self._h = h
+        self.R = float(L.cg_image_radius(h))             # fits_image.py:151-155
+
+    # host conveniences (float64, a handful of flops; fits_image.py:166-216)
+    def equa2pixel(self, s_equa):
+        phi1rad = self.phi_n[1] / 180. * np.pi
+        s_iwc = np.array([(s_equa[0] - self.phi_n[0]) * np.cos(phi1rad), (s_equa[1] - self.phi_n[1])])
+        return np.dot(self.Ups_n_inv, s_iwc) + self.rho_n
+
+    def pixel2equa(self, s_pixel):
+        phi1rad = self.phi_n[1] / 180. * np.pi
+        s_iwc = np.dot(self.Ups_n, np.asarray(s_pixel, dtype=np.float64) - self.rho_n)
+        return np.array([s_iwc[0] / np.cos(phi1rad) + self.phi_n[0], s_iwc[1] + self.phi_n[1]])
+
+    def nmgy2counts(self, flux):
+        return (flux / self.calib) * self.kappa
+
+    def set_epsilon(self, epsilon: float):
+        """Field.resample_photons re-draws epsilon every sweep (models.py:156-160)."""
+        check(lib().cg_image_set_epsilon(self._h, float(epsilon)))
+        self.epsilon = float(epsilon)
+
+    @property
+    def nelec(self) -> torch.Tensor:
+        return self.d_nelec
+
+    def set_nelec(self, nelec):
+        """Overwrite the resident pixel counts in place (same device buffer)."""
+        if not isinstance(nelec, torch.Tensor):
+            nelec = torch.from_numpy(np.ascontiguousarray(nelec, dtype=np.float32))
+        self.d_nelec.copy_(nelec.to(dtype=torch.float32).reshape(self.shape))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and _state["lib"] is not None:
+            _state["lib"].cg_image_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def _handles(images: Sequence[Image]):
+    n = len(images)
+    if n < 1 or n > CG_MAX_IMAGES:
+        raise ValueError("between 1 and %d images per call" % CG_MAX_IMAGES)
+    arr = (C.c_void_p * n)(*[im._h for im in images])
+    return arr, n
+
+
+def _srcs_dev(srcs):
+    """Accepts a packed CgSource array (numpy), a device byte tensor, or a
+    sequence of SrcParams; returns (device tensor, count)."""
+    if isinstance(srcs, torch.Tensor):
+        return srcs, srcs.numel() // SRC_DTYPE.itemsize
+    if isinstance(srcs, np.ndarray) and srcs.dtype == SRC_DTYPE:
+        return to_device(srcs), srcs.shape[0]
+    arr = pack_sources(list(srcs))
+    return to_device(arr), arr.shape[0]
+
+
+def read_filter_table(path: str | None = None):
+    """planck.py:31-55: per band, wavelengths (m, ascending), sensitivities and
+    h_vec = S/(hc/lambda)*dLambda.  Default table: the SDSS ugriz response
+    curves packed in desi_mcmc_b200/data/filter_curves.npz (Angstrom); a path
+    to a text file in the reference's "band<TAB>angstrom<TAB>sens" layout is
+    also accepted."""
+    h, c = 6.6260693e-34, 299792458
+    wl, sens = {}, {}
+    if path is None:
+        z = np.load(os.path.join(_ffi.PKG, "data", "filter_curves.npz"))
+        for b in BANDS:
+            wl[b] = z["wl_" + b] * 1e-4 * 1e-6
+            sens[b] = z["sens_" + b]
+    else:
+        acc_w = {b: [] for b in BANDS}
+        acc_s = {b: [] for b in BANDS}
+        with open(path) as f:
+            for line in f:
+                band, wavelength, sensitivity = line.strip().split("\t")
+                acc_w[band].append(float(wavelength) * 1e-4 * 1e-6)
+                acc_s[band].append(float(sensitivity))
+        for b in BANDS:
+            wl[b], sens[b] = np.array(acc_w[b]), np.array(acc_s[b])
+    hv = {}
+    for b in BANDS:
+        order = wl[b].argsort()
+        wl[b], sens[b] = wl[b][order], sens[b][order]
+        dLam = np.abs(wl[b][2] - wl[b][1])
+        hv[b] = sens[b] / (h * c / wl[b]) * dLam
+    return wl, sens, hv
+
+
+def load_filter_curves(path: str | None = None):
+    """Hand the filter tables to the device (cg_set_filter_curves)."""
+    wl, sens, hv = read_filter_table(path)
+    wl_all = np.ascontiguousarray(np.concatenate([wl[b] for b in BANDS]))
+    hv_all = np.ascontiguousarray(np.concatenate([hv[b] for b in BANDS]))
+    s_all = np.ascontiguousarray(np.concatenate([sens[b] for b in BANDS]))
+    cnt = np.asarray([wl[b].size for b in BANDS], dtype=np.int32)
+    check(lib().cg_set_filter_curves(wl_all.ctypes.data, hv_all.ctypes.data, s_all.ctypes.data,
+                                     cnt.ctypes.data))
+    _state["filters"] = True
+
+
+def _need_filters(arr_or_srcs):
+    if _state["filters"]:
+        return
+    need = False
+    if isinstance(arr_or_srcs, np.ndarray):
+        need = bool(np.any(arr_or_srcs["flags"] & CG_SRC_PLANCK))
+    if need:
+        load_filter_curves()
+
+
+# ---------------------------------------------------------------------------
+# engine calls
+# ---------------------------------------------------------------------------
+def make_items(src, img, flags=0, box=None, aux=-1) -> np.ndarray:
+    """Build a CgItem array from broadcastable columns; box = (x0, x1, y0, y1)."""
+    src = np.atleast_1d(np.asarray(src, dtype=np.int32))
+    n = src.shape[0]
+    it = np.zeros(n, dtype=ITEM_DTYPE)
+    it["src"] = src
+    it["img"] = img
+    it["flags"] = flags
+    it["aux"] = aux
+    if box is not None:
+        it["box"] = np.asarray(box, dtype=np.int32).reshape(-1, 4)
+        it["flags"] |= CG_ITEM_FIXED_BOX
+    return it
+
+
+def render_patches(images: Sequence[Image], srcs, items: np.ndarray | None = None,
+                   default_flags: int = CG_ITEM_FLUX_BAND, bound_cap: float = 0.0,
+                   max_patch_px: int | None = None):
+    """A5/A6/A10: rate (or unit-flux) patches for (source, image) items.
+    Returns (patches [n_items, max_patch_px] float32 device tensor,
+    boxes [n_items] BOX_DTYPE host array).  items=None renders the cross
+    product, item = src*n_img + img."""
+    L = lib()
+    harr, n_img = _handles(images)
+    if isinstance(srcs, np.ndarray):
+        _need_filters(srcs)
+    d_srcs, n_src = _srcs_dev(srcs)
+    if items is None:
+        n_items = n_src * n_img
+        d_items = None
+    else:
+        n_items = items.shape[0]
+        d_items = to_device(items)
+    if max_patch_px is None:
+        max_patch_px = max(im.shape[0] * im.shape[1] for im in images)
+        if bound_cap > 0:
+            side = int(2 * bound_cap + 3)
+            max_patch_px = min(max_patch_px, side * side)
+    if n_items == 0:
+        return (torch.zeros((0, max_patch_px), dtype=torch.float32, device=device()),
+                np.zeros(0, dtype=BOX_DTYPE))
+    patches = torch.zeros((n_items, max_patch_px), dtype=torch.float32, device=device())
+    boxes = torch.zeros(n_items * BOX_DTYPE.itemsize, dtype=torch.uint8, device=device())
+    ws = _workspace(_ffi.CG_WS_RENDER, n_items, n_img, max_patch_px)
+    check(L.cg_render_patches(harr, n_img, d_srcs.data_ptr(), n_src,
+                              d_items.data_ptr() if d_items is not None else None, n_items,
+                              default_flags, float(bound_cap), max_patch_px,
+                              patches.data_ptr(), boxes.data_ptr(), ws.data_ptr(), ws.numel(),
+                              stream_ptr()))
+    last_eval_count()          # surfaces footprint/work-list overflow as an exception
+    return patches, boxes.cpu().numpy().view(BOX_DTYPE)
+
+
+def field_workspace(images: Sequence[Image], n_src: int, max_patch_px: int):
+    n_img = len(images)
+    tiles = n_img * max(int(lib().cg_field_tiles(im.shape[0], im.shape[1])) for im in images)
+    return _workspace(_ffi.CG_WS_FIELD, max(n_src, 1) * n_img, n_img, max_patch_px, tiles)
+
+
+def field_loglik(images: Sequence[Image], srcs, bound_cap: float = 0.0,
+                 max_patch_px: int | None = None, return_model: bool = False,
+                 out: torch.Tensor | None = None, sync: bool = True):
+    """A7/A8 (celeste.py:203-252): per-image Poisson log-likelihood of the full
+    frames under lambda = epsilon + sum_s patch_s.  Returns a float64 device
+    tensor [n_img] (and the model images when return_model)."""
+    L = lib()
+    harr, n_img = _handles(images)
+    if isinstance(srcs, np.ndarray):
+        _need_filters(srcs)
+    d_srcs, n_src = _srcs_dev(srcs)
+    if max_patch_px is None:
+        side = int(2 * bound_cap + 3) if bound_cap > 0 else 203
+        max_patch_px = side * side
+    ws = field_workspace(images, n_src, max_patch_px)
+    ll = out if out is not None else torch.zeros(n_img, dtype=torch.float64, device=device())
+    models, mptr = None, None
+    if return_model:
+        models = [torch.zeros(im.shape, dtype=torch.float32, device=device()) for im in images]
+        mptr = (C.c_void_p * n_img)(*[m.data_ptr() for m in models])
+    check(L.cg_field_loglik(harr, n_img, d_srcs.data_ptr(), n_src, float(bound_cap), max_patch_px,
+                            ll.data_ptr(), mptr, ws.data_ptr(), ws.numel(), stream_ptr()))
+    if sync:
+        last_eval_count()
+    return (ll, models) if return_model else ll
+
+
+def items_loglik(images: Sequence[Image], srcs, items: np.ndarray, mode: int = CG_LL_POISSON_BG,
+                 aux: torch.Tensor | None = None, aux_offsets: np.ndarray | None = None,
+                 bound_cap: float = 0.0, max_patch_px: int = 0, use_fp64: bool = False):
+    """A13/A14/A15 building block: per-item log-likelihood over its box.
+    Returns (item_ll float64 device tensor, boxes host array)."""
+    L = lib()
+    harr, n_img = _handles(images)
+    d_srcs, n_src = _srcs_dev(srcs)
+    n_items = items.shape[0]
+    d_items = to_device(items)
+    if max_patch_px <= 0:
+        max_patch_px = max(im.shape[0] * im.shape[1] for im in images)
+    ws = _workspace(_ffi.CG_WS_ITEMS, n_items, n_img, max_patch_px)
+    ll = torch.zeros(n_items, dtype=torch.float64, device=device())
+    boxes = torch.zeros(n_items * BOX_DTYPE.itemsize, dtype=torch.uint8, device=device())
+    d_off = None
+    if aux is not None:
+        if aux_offsets is None:
+            raise ValueError("aux_offsets required with aux")
+        d_off = to_device(np.ascontiguousarray(aux_offsets, dtype=np.int64))
+    check(L.cg_items_loglik(harr, n_img, d_srcs.data_ptr(), n_src, d_items.data_ptr(), n_items,
+                            mode, float(bound_cap), max_patch_px,
+                            aux.data_ptr() if aux is not None else None,
+                            d_off.data_ptr() if d_off is not None else None,
+                            ll.data_ptr(), boxes.data_ptr(), 1 if use_fp64 else 0,
+                            ws.data_ptr(), ws.numel(), stream_ptr()))
+    last_eval_count()
+    return ll, boxes.cpu().numpy().view(BOX_DTYPE)
+
+
+class ProposalScorer(object):
+    """A15: batched Source.calculate_acceptance_logprob + accept test
+    (sources.py:258,275-306) for P proposals of one source over its cached
+    bounding boxes / background patches.  Buffers are allocated once; score()
+    takes HOST arrays (packed proposals, log-terms, log-uniforms) and returns
+    host arrays -- the per-step H2D/D2H the end-to-end numbers include."""
+
+    def __init__(self, images: Sequence[Image], boxes, backgrounds=None, max_proposals: int = 4096,
+                 guard: float = 1e-2):
+        self.L = lib()
+        self.images = list(images)
+        self.harr, self.n_img = _handles(self.images)
+        self.P_max = int(max_proposals)
+        self.guard = float(guard)
+        b = np.zeros(self.n_img, dtype=BOX_DTYPE)
+        for i, bx in enumerate(boxes):          # (x0, x1, y0, y1)
+            b[i] = tuple(int(v) for v in bx)
+        self.boxes = b
+        max_px = int(max((bb["x1"] - bb["x0"]) * (bb["y1"] - bb["y0"]) for bb in b))
+        self.max_px = max_px
+        self.d_bg, self.bg_off = None, None
+        if backgrounds is not None:
+            offs, flat, o = [], [], 0
+            for i, bg in enumerate(backgrounds):
+                bg = np.ascontiguousarray(bg, dtype=np.float32)
+                bb = b[i]
+                if bg.shape != (bb["y1"] - bb["y0"], bb["x1"] - bb["x0"]):
+                    raise ValueError("background %d shape %s does not match its box" % (i, bg.shape))
+                offs.append(o)
+                flat.append(bg.ravel())
+                o += bg.size
+            self.bg_off = np.asarray(offs, dtype=np.int64)
+            self.d_bg = torch.from_numpy(np.concatenate(flat)).to(device())
+        n_items = (self.P_max + 1) * self.n_img
+        need = int(self.L.cg_workspace_bytes(_ffi.CG_WS_SCORE, n_items, self.n_img, max_px, 0))
+        self.ws = torch.empty(need, dtype=torch.uint8, device=device())
+        self.stage_src = PinnedStage((self.P_max + 1) * SRC_DTYPE.itemsize)
+        self.stage_terms = PinnedStage(self.P_max * 8)
+        self.stage_u = PinnedStage(self.P_max * 8)
+        self.d_delta = torch.zeros(self.P_max, dtype=torch.float64, device=device())
+        self.d_accept = torch.zeros(self.P_max, dtype=torch.uint8, device=device())
+        self.d_nguard = torch.zeros(1, dtype=torch.int32, device=device())
+        self.h_delta = torch.zeros(self.P_max, dtype=torch.float64).pin_memory()
+        self.h_accept = torch.zeros(self.P_max, dtype=torch.uint8).pin_memory()
+        self.h_nguard = torch.zeros(1, dtype=torch.int32).pin_memory()
+
+    def score_device(self, d_srcs: torch.Tensor, P: int, d_terms, d_log_u):
+        """All inputs already in HBM; nothing synchronises."""
+        check(self.L.cg_score_proposals(
+            self.harr, self.n_img, d_srcs.data_ptr(), int(P), self.boxes.ctypes.data,
+            self.d_bg.data_ptr() if self.d_bg is not None else None,
+            self.bg_off.ctypes.data if self.bg_off is not None else None,
+            d_terms.data_ptr() if d_terms is not None else None, d_log_u.data_ptr(),
+            self.guard, self.d_delta.data_ptr(), self.d_accept.data_ptr(),
+            self.d_nguard.data_ptr(), self.ws.data_ptr(), self.ws.numel(), stream_ptr()))
+
+    def score(self, cur_and_props: np.ndarray, log_u: np.ndarray, log_terms: np.ndarray | None = None):
+        """cur_and_props: CgSource array, [0] = current state, [1:] = proposals.
+        Returns (delta [P] float64, accept [P] bool, n_guard)."""
+        P = cur_and_props.shape[0] - 1
+        if P > self.P_max:
+            raise ValueError("more proposals than max_proposals")
+        if log_u.shape[0] != P:
+            raise ValueError("log_u must have one entry per proposal")
+        d_srcs = self.stage_src.upload(cur_and_props)
+        d_u = self.stage_u.upload(np.ascontiguousarray(log_u, dtype=np.float64))
+        d_t = None
+        if log_terms is not None:
+            d_t = self.stage_terms.upload(np.ascontiguousarray(log_terms, dtype=np.float64))
+        self.score_device(d_srcs, P, d_t, d_u)
+        self.h_delta[:P].copy_(self.d_delta[:P], non_blocking=True)
+        self.h_accept[:P].copy_(self.d_accept[:P], non_blocking=True)
+        self.h_nguard.copy_(self.d_nguard, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return (self.h_delta[:P].numpy().copy(), self.h_accept[:P].numpy().astype(bool),
+                int(self.h_nguard[0]))
+
+
+def gmm_like_2d_device(d_x, d_ws, d_mus, d_sigs, d_probs=None):
+    """A2 on device tensors (float64)."""
+    N, K = d_x.shape[0], d_ws.shape[0]
+    if d_probs is None:
+        d_probs = torch.empty(N, dtype=torch.float64, device=device())
+    check(lib().cg_gmm_like_2d(d_probs.data_ptr(), d_x.data_ptr(), d_ws.data_ptr(), d_mus.data_ptr(),
+                               d_sigs.data_ptr(), N, K, stream_ptr()))
+    return d_probs
+
+
+def planck_fluxes(T, b) -> np.ndarray:
+    """A16: photons_expected_brightness(T[i], b[i], band) for all 5 bands
+    (planck.py:155-158) -> [n, 5] float64."""
+    if not _state["filters"]:
+        load_filter_curves()
+    T = np.atleast_1d(np.asarray(T, dtype=np.float64))
+    b = np.broadcast_to(np.asarray(b, dtype=np.float64), T.shape).copy()
+    d_T = torch.from_numpy(T).to(device())
+    d_b = torch.from_numpy(b).to(device())
+    out = torch.zeros((T.shape[0], CG_NUM_BANDS), dtype=torch.float64, device=device())
+    check(lib().cg_planck_fluxes(d_T.data_ptr(), d_b.data_ptr(), T.shape[0], out.data_ptr(), stream_ptr()))
+    return out.cpu().numpy()
+
+
+def eigen_fluxes(z, w, m, B, lam0, fluxes=None, fluxes_ivar=None):
+    """A17: batched project_to_bands / pixel_likelihood
+    (experiments/redshift/redshift_utils.py:304-323,
+    quasar_infer_photometry.py:31-46).  Returns (mu [C,5], ll [C] or None)."""
+    if not _state["filters"]:
+        load_filter_curves()
+    z = np.atleast_1d(np.asarray(z, dtype=np.float64))
+    Cn = z.shape[0]
+    w = np.ascontiguousarray(np.asarray(w, dtype=np.float64).reshape(Cn, -1))
+    m = np.broadcast_to(np.asarray(m, dtype=np.float64), z.shape).copy()
+    B = np.ascontiguousarray(B, dtype=np.float64)
+    K, V = B.shape
+    if w.shape[1] != K:
+        raise ValueError("weights and basis disagree on K")
+    dev = device()
+    d = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(dev)
+    d_z, d_w, d_m, d_B, d_l = d(z), d(w), d(m), d(B), d(lam0)
+    mu = torch.zeros((Cn, CG_NUM_BANDS), dtype=torch.float64, device=dev)
+    ll, d_f, d_iv = None, None, None
+    if fluxes is not None:
+        d_f = d(np.broadcast_to(np.asarray(fluxes, dtype=np.float64), (Cn, CG_NUM_BANDS)))
+        d_iv = d(np.broadcast_to(np.asarray(fluxes_ivar, dtype=np.float64), (Cn, CG_NUM_BANDS)))
+        ll = torch.zeros(Cn, dtype=torch.float64, device=dev)
+    check(lib().cg_eigen_fluxes(d_z.data_ptr(), d_w.data_ptr(), d_m.data_ptr(), d_B.data_ptr(),
+                                d_l.data_ptr(), Cn, K, V,
+                                d_f.data_ptr() if d_f is not None else None,
+                                d_iv.data_ptr() if d_iv is not None else None,
+                                mu.data_ptr(), ll.data_ptr() if ll is not None else None, stream_ptr()))
+    return mu.cpu().numpy(), (ll.cpu().numpy() if ll is not None else None)

@@ -1,0 +1,125 @@
+"""Seeded synthetic inputs of the BASELINE.json configurations.
+
+Pure input generation (NumPy ``RandomState`` so the legacy stream is
+reproducible); no rendering or likelihood arithmetic lives here.  Image
+parameters follow the header of the r-band stamp the reference ships
+(data/stamps/stamp-r-253.1147-11.6072.fits: CALIB .00521, SKY 94, GAIN 4.6, PSF
+weights .60/.32/.08 with variances 1.9/7.0/29.8 px^2, CD +-1.1e-4 deg/px); the
+galaxy-shape draws follow experiments/galaxy/sample_stamp.py:119-125.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+BANDS = ["u", "g", "r", "i", "z"]
+PIX_DEG = 1.1e-4
+
+
+def make_psf(rng):
+    w = np.array([.60, .32, .08]) * rng.uniform(.9, 1.1, size=3)
+    w = w / w.sum()
+    means = rng.normal(0., .2, size=(3, 2))
+    covs = np.zeros((3, 2, 2))
+    for k, v in enumerate((1.9, 7.0, 30.0)):
+        vx, vy = v * rng.uniform(.8, 1.25, size=2)
+        c = rng.uniform(-.15, .15) * np.sqrt(vx * vy)
+        covs[k] = [[vx, c], [c, vy]]
+    return w, means, covs
+
+
+def make_image_meta(rng, band, H, W, center=(253.1147, 11.6072), rotate=True):
+    """What FitsImage would read from a frame header (fits_image.py:85-147)."""
+    w, means, covs = make_psf(rng)
+    ang = rng.uniform(-.02, .02) if rotate else 0.
+    ca, sa = np.cos(ang), np.sin(ang)
+    ups = PIX_DEG * np.array([[-ca, sa], [sa, ca]])
+    return dict(band=band,
+                calib=.005 * rng.uniform(.9, 1.1),
+                gain=4.6 * rng.uniform(.95, 1.05),
+                sky=94. * rng.uniform(.8, 1.2),
+                rho_n=np.array([W / 2., H / 2.]) + rng.uniform(-.5, .5, size=2),
+                phi_n=np.array(center, dtype=np.float64),
+                Ups_n=ups,
+                psf_weights=w, psf_means=means, psf_covars=covs,
+                shape=(H, W))
+
+
+def pixel2equa(meta, p):
+    """fits_image.py:176-181 on a meta dict (for placing synthetic sources)."""
+    phi1rad = meta["phi_n"][1] / 180. * np.pi
+    iwc = np.dot(meta["Ups_n"], np.asarray(p, dtype=np.float64) - meta["rho_n"])
+    return np.array([iwc[0] / np.cos(phi1rad) + meta["phi_n"][0], iwc[1] + meta["phi_n"][1]])
+
+
+def make_source(rng, meta, is_star, pix=None, planck=False, margin=0.):
+    H, W = meta["shape"]
+    if pix is None:
+        pix = np.array([rng.uniform(margin, W - margin), rng.uniform(margin, H - margin)])
+    u = pixel2equa(meta, pix)
+    colors = np.exp(rng.normal(0., .3, size=5))
+    if is_star:
+        flux = 10. * np.exp(rng.normal(0., .7)) * colors
+        s = dict(a=0, u=u, fluxes=flux, t=None, b=None,
+                 theta=None, sigma=None, phi=None, rho=None)
+        if planck:
+            s["t"] = rng.uniform(3000., 10000.)
+            s["b"] = np.exp(rng.normal(np.log(5e-11), .5))   # ~7e3 photo-electrons
+        return s
+    flux = 30. * np.exp(rng.normal(0., .7)) * colors
+    return dict(a=1, u=u, fluxes=flux, t=None, b=None,
+                theta=float(np.clip(rng.beta(.4, .4), .01, .99)),
+                sigma=float(np.exp(rng.normal(np.log(1.5), .5))),
+                phi=float(rng.uniform(0., 180.)),   # degrees: celeste_galaxy_conditionals.py:97
+                rho=float(rng.uniform(.2, 1.)))
+
+
+def make_field(seed, H=1489, W=2048, n_src=500, star_frac=.6, planck_frac=0., margin=0.):
+    """C2 / C5: one 5-band field with n_src mixed sources."""
+    rng = np.random.RandomState(seed)
+    metas = [make_image_meta(rng, b, H, W) for b in BANDS]
+    srcs = []
+    for _ in range(n_src):
+        star = rng.uniform() < star_frac
+        srcs.append(make_source(rng, metas[2], star, planck=star and rng.uniform() < planck_frac,
+                                margin=margin))
+    return dict(seed=seed, images=metas, sources=srcs)
+
+
+def make_stamp(seed, size=25, n_star=1, n_gal=1):
+    """C1: 1 star + 1 galaxy on a 5-band 25x25 stamp."""
+    rng = np.random.RandomState(seed)
+    metas = [make_image_meta(rng, b, size, size) for b in BANDS]
+    c = np.array([size / 2., size / 2.])
+    srcs = []
+    for i in range(n_star):
+        srcs.append(make_source(rng, metas[2], True, pix=c + rng.uniform(-.5, .5, size=2) + 3. * i))
+    for i in range(n_gal):
+        ang = rng.uniform(0, 2 * np.pi)
+        srcs.append(make_source(rng, metas[2], False,
+                                pix=c + 4. * np.array([np.cos(ang), np.sin(ang)]) * (i + 1)))
+    return dict(seed=seed, images=metas, sources=srcs)
+
+
+def make_proposals(seed, cur, P):
+    """C3: P Gaussian perturbations of a galaxy's state (u in pixels .05, flux
+    2 %, theta/rho .02, phi 3 deg, sigma 3 %) + log-uniforms from the same
+    legacy stream."""
+    rng = np.random.RandomState(seed)
+    props = []
+    for _ in range(P):
+        p = dict(cur)
+        p["u"] = cur["u"] + rng.normal(0., .05, size=2) * PIX_DEG
+        p["fluxes"] = cur["fluxes"] * (1. + rng.normal(0., .02, size=5))
+        if cur["a"] == 1:
+            p["theta"] = float(np.clip(cur["theta"] + rng.normal(0., .02), .01, .99))
+            p["rho"] = float(np.clip(cur["rho"] + rng.normal(0., .02), .05, 1.))
+            p["phi"] = float(cur["phi"] + rng.normal(0., 3.))
+            p["sigma"] = float(cur["sigma"] * (1. + rng.normal(0., .03)))
+        props.append(p)
+    log_u = np.log(rng.uniform(size=P))
+    return props, log_u
+
+
+def image_kwargs(meta):
+    return {k: meta[k] for k in ("band", "calib", "gain", "sky", "rho_n", "phi_n", "Ups_n",
+                                 "psf_weights", "psf_means", "psf_covars")}

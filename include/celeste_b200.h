@@ -253,6 +253,14 @@ int64_t cg_launch_count(int reset);
  * device counter, synchronises `stream`. */
 int64_t cg_last_eval_count(void* stream);
 
+/* CUDA-event timing of every render_kernel launch (bench.py's roofline leg):
+ * enable resets the record; read synchronises on the recorded events. */
+int cg_profile_render(int enable);
+int cg_profile_render_read(double* h_total_ms, int64_t* h_launches);
+/* Measured pipe throughput on this device: which = 0 MUFU.EX2 results/s (the
+ * XU roofline of render_kernel), 1 = FP32 FMA instructions/s.  Synchronises. */
+int cg_pipe_probe(int which, double* h_ops_per_s, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -744,3 +744,22 @@ def softmax(x):
     """experiments/redshift/redshift_utils.py:394-397."""
     x_tilde = np.exp(x - x.max())
     return x_tilde / x_tilde.sum()
+
+
+def set_filter_tables_npz(npz_path):
+    """Same tables as load_filter_curves (planck.py:31-55) from the packed copy
+    of the reference's data file (desi_mcmc_b200/data/filter_curves.npz, made by
+    tools/make_filter_table.py); /root/reference is absent on the GPU box."""
+    global _FILTERS
+    z = np.load(npz_path)
+    wl, sens, h_vecs = {}, {}, {}
+    for b in BANDS:
+        wl[b] = z["wl_" + b] * 1e-4 * 1e-6
+        sens[b] = z["sens_" + b]
+        order = wl[b].argsort()
+        wl[b] = wl[b][order]
+        sens[b] = sens[b][order]
+        dLam = np.abs(wl[b][2] - wl[b][1])
+        h_vecs[b] = sens[b] / (h * c / wl[b]) * dLam
+    _FILTERS = (wl, sens, h_vecs)
+    return _FILTERS

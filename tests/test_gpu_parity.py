@@ -1,0 +1,253 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle on the
+same seeded inputs.  Tolerances are BASELINE.json's: rendered rates 1e-5
+relative, per-image log-likelihood 1e-6 relative, accept/reject identical."""
+import os
+
+import numpy as np
+import pytest
+
+from desi_mcmc_b200 import synth
+from tests import helpers as hp
+
+pytestmark = pytest.mark.gpu
+
+RATE_RTOL = 1e-5
+LL_RTOL = 1e-6
+# a rate below RATE_FLOOR x (patch peak) is compared absolutely: fp32 flushes
+# below 2^-126 and the float64 oracle does not
+RATE_FLOOR = 1e-12
+
+
+def kat_inputs(K=42, n=200):
+    """CelestePy/test/test_gmm.py:63-85, same seed and draw order."""
+    np.random.seed(41)
+    means = 2 * np.random.randn(K * 2).reshape(K, 2)
+    covs = np.zeros((K, 2, 2))
+    for i in range(K):
+        covs[i] = np.random.randn(2, 2)
+        covs[i] = covs[i].dot(covs[i].T)
+        np.linalg.inv(covs[i])
+        np.linalg.slogdet(covs[i])
+    ws = np.random.rand(K)
+    ws /= np.sum(ws)
+    xx, yy = np.meshgrid(np.linspace(-3, 3, n), np.linspace(-5, 5, n))
+    X = np.column_stack((xx.ravel(), yy.ravel()))
+    return X, ws, means, covs
+
+
+def test_gmm_like_2d_kat(engine, oracle):
+    from desi_mcmc_b200.compat import gmm_like_fast
+    X, ws, means, covs = kat_inputs()
+    want = oracle.gmm_like_2d(X, ws, means, covs)
+    got = np.zeros(X.shape[0])
+    assert gmm_like_fast.gmm_like_2d(got, X, ws, means, covs) is None
+    assert np.allclose(got, want)                       # the reference test's own criterion
+    assert hp.rel_err(got, want, RATE_FLOOR * want.max()) < RATE_RTOL
+
+
+def test_gmm_like_2d_errors(engine):
+    from desi_mcmc_b200.compat import gmm_like_fast
+    X, ws, means, covs = kat_inputs(K=3, n=4)
+    with pytest.raises(ValueError):
+        gmm_like_fast.gmm_like_2d(np.zeros(16), X, ws[:2], means, covs)
+    with pytest.raises(ValueError):
+        gmm_like_fast.gmm_like_2d(np.zeros(16), X.astype(np.float32), ws, means, covs)
+    p = np.ones(0)
+    gmm_like_fast.gmm_like_2d(p, X[:0], ws, means, covs)    # empty input is a no-op
+
+
+def test_mvn2d_logpdf(engine, oracle):
+    from desi_mcmc_b200.compat import gmm_like_fast
+    X, ws, means, covs = kat_inputs(K=3, n=100)
+    ci = np.linalg.inv(covs[2])
+    _, logdet = np.linalg.slogdet(covs[2])
+    want = oracle.multivariate_normal_2d_covinv_logdet_logpdf(np.zeros(X.shape[0]), X, means[2], ci, logdet)
+    got = gmm_like_fast.multivariate_normal_2d_covinv_logdet_logpdf(np.zeros(X.shape[0]), X, means[2], ci, logdet)
+    assert np.allclose(got, want, rtol=1e-12, atol=1e-9)
+
+
+def _check_patches(eng, ref, field, flags, unit):
+    H, W = field["images"][0]["shape"]
+    zeros = [np.zeros((H, W))] * 5
+    gimgs = hp.gpu_images(eng, field, zeros)
+    oimgs = hp.oracle_images(ref, field, zeros)
+    gs, os_ = hp.gpu_sources(eng, field), hp.oracle_sources(ref, field)
+    patches, boxes = eng.render_patches(gimgs, gs, default_flags=flags)
+    patches = patches.cpu().numpy()
+    worst = 0.0
+    for si, s in enumerate(os_):
+        for bi, img in enumerate(oimgs):
+            it = si * 5 + bi
+            if s.a == 0:
+                want, ylim, xlim = ref.gen_point_source_psf_image(s.u, img)
+            else:
+                want, ylim, xlim = ref.gen_galaxy_psf_image(s.shape, s.u, img)
+            if not unit:
+                want = want * img.nmgy2counts(s.flux_dict[img.band])
+            b = boxes[it]
+            assert (b["x0"], b["x1"], b["y0"], b["y1"]) == (int(xlim[0]), int(xlim[1]), int(ylim[0]), int(ylim[1]))
+            h, w = b["y1"] - b["y0"], b["x1"] - b["x0"]
+            got = patches[it, :h * w].reshape(h, w)
+            assert got.shape == want.shape
+            worst = max(worst, hp.rel_err(got, want, RATE_FLOOR * want.max()))
+    return worst
+
+
+def test_unit_patches_stamp_c1(engine, oracle):
+    from desi_mcmc_b200 import _ffi
+    field = synth.make_stamp(1001)
+    assert _check_patches(engine, oracle, field, _ffi.CG_ITEM_FLUX_UNIT, True) < RATE_RTOL
+
+
+def test_rate_patches_small_field(engine, oracle):
+    from desi_mcmc_b200 import _ffi
+    field = synth.make_field(77, H=160, W=192, n_src=14, star_frac=.5)
+    assert _check_patches(engine, oracle, field, _ffi.CG_ITEM_FLUX_BAND, False) < RATE_RTOL
+
+
+def test_field_loglik_small(engine, oracle):
+    field = synth.make_field(78, H=150, W=170, n_src=10, star_frac=.5)
+    nelec = hp.simulate_nelec(oracle, field, 5)
+    gimgs = hp.gpu_images(engine, field, nelec)
+    oimgs = hp.oracle_images(oracle, field, nelec)
+    ll, models = engine.field_loglik(gimgs, hp.gpu_sources(engine, field), return_model=True)
+    ll = ll.cpu().numpy()
+    osrcs = hp.oracle_sources(oracle, field)
+    for i, img in enumerate(oimgs):
+        lam = oracle.gen_model_image(osrcs, img)
+        assert hp.rel_err(models[i].cpu().numpy(), lam, 1.0) < RATE_RTOL
+        want = oracle.celeste_likelihood(osrcs, img)
+        assert abs(ll[i] - want) <= LL_RTOL * abs(want)
+    total = oracle.celeste_likelihood_multi_image(osrcs, oimgs)
+    assert abs(ll.sum() - total) <= LL_RTOL * abs(total)
+
+
+def test_field_loglik_no_sources(engine, oracle):
+    field = synth.make_field(79, H=64, W=100, n_src=0)
+    rng = np.random.RandomState(3)
+    nelec = [rng.poisson(400., size=(64, 100)).astype(np.float64) for _ in range(5)]
+    gimgs = hp.gpu_images(engine, field, nelec)
+    oimgs = hp.oracle_images(oracle, field, nelec)
+    from desi_mcmc_b200 import _ffi
+    ll = engine.field_loglik(gimgs, np.zeros(0, dtype=_ffi.SRC_DTYPE)).cpu().numpy()
+    for i, img in enumerate(oimgs):
+        want = oracle.celeste_likelihood([], img)
+        assert abs(ll[i] - want) <= LL_RTOL * abs(want)
+
+
+def _stamp_problem(eng, ref, seed, size, P, with_mask=True):
+    rng = np.random.RandomState(seed)
+    field = synth.make_stamp(seed, size=size, n_star=1, n_gal=1)
+    nelec = hp.simulate_nelec(ref, field, seed + 1)
+    invvar = None
+    if with_mask:
+        invvar = [(rng.uniform(size=(size, size)) > .03).astype(np.float64) for _ in range(5)]
+    gimgs = hp.gpu_images(eng, field, nelec, invvar)
+    oimgs = hp.oracle_images(ref, field, nelec, invvar)
+    cur = field["sources"][1]            # the galaxy
+    other = field["sources"][0]
+    props, log_u = synth.make_proposals(seed + 2, cur, P)
+    return field, gimgs, oimgs, cur, other, props, log_u
+
+
+def test_score_proposals_parity(engine, oracle):
+    """A15 (sources.py:275-306, :258): delta and accept decisions for the seed."""
+    P, size = 96, 32
+    field, gimgs, oimgs, cur, other, props, log_u = _stamp_problem(engine, oracle, 1003, size, P)
+    ocur = hp.oracle_sources(oracle, [cur])[0]
+    oother = hp.oracle_sources(oracle, [other])
+    oprops = hp.oracle_sources(oracle, props)
+    boxes, bgs, gboxes = [], [], []
+    for img in oimgs:
+        xlim, ylim = oracle.make_bbox(ocur, img, pixel_radius=12)
+        boxes.append((xlim, ylim))
+        bgs.append(oracle.generate_background_patch(ocur, oother, img, xlim, ylim))
+        gboxes.append((xlim[0], xlim[1], ylim[0], ylim[1]))
+    log_terms = np.random.RandomState(9).normal(0, .1, size=P)
+    want = np.array([oracle.calculate_acceptance_logprob(ocur, p, oimgs, boxes, bgs, logdet=lt)
+                     for p, lt in zip(oprops, log_terms)])
+    scorer = engine.ProposalScorer(gimgs, gboxes, bgs, max_proposals=P, guard=1e-2)
+    packed = engine.pack_sources(hp.gpu_sources(engine, [cur] + props))
+    delta, accept, n_guard = scorer.score(packed, log_u, log_terms)
+    print("max |delta - oracle| = %.3g, guard re-scored %d of %d" % (np.max(np.abs(delta - want)), n_guard, P))
+    assert np.array_equal(accept, log_u < want)
+    # fp32 rates: |delta error| is bounded well inside the guard band
+    assert np.max(np.abs(delta - want)) < 2e-3
+    # guard-band proposals were re-scored in float64
+    near = np.abs(log_u - want) < 5e-3
+    assert n_guard >= near.sum()
+    if near.any():
+        assert np.max(np.abs(delta[near] - want[near])) < 1e-5
+
+
+def test_items_loglik_modes(engine, oracle):
+    """A13 (conditional, sources.py:134-183) and A14 (isolated, :188-237)."""
+    from desi_mcmc_b200 import _ffi
+    field = synth.make_stamp(1001, size=25)
+    nelec = hp.simulate_nelec(oracle, field, 4)
+    gimgs = hp.gpu_images(engine, field, nelec)
+    oimgs = hp.oracle_images(oracle, field, nelec)
+    osrcs = hp.oracle_sources(oracle, field)
+    gsrcs = engine.pack_sources(hp.gpu_sources(engine, field))
+    rng = np.random.RandomState(12)
+    import torch
+    for si, s in enumerate(osrcs):
+        xl, yl = (3, 24), (2, 23)
+        # isolated: data = nelec crop, background epsilon, no mask
+        items = engine.make_items([si] * 5, np.arange(5), flags=_ffi.CG_ITEM_NO_MASK,
+                                  box=[(xl[0], xl[1], yl[0], yl[1])] * 5)
+        ll, _ = engine.items_loglik(gimgs, gsrcs, items, mode=_ffi.CG_LL_POISSON_BG)
+        want = oracle.source_log_likelihood_isolated(s, [(yl, xl)] * 5, oimgs)
+        assert abs(ll.sum().item() - want) <= LL_RTOL * abs(want)
+        # conditional on allocated photons z
+        zs = [rng.poisson(3., size=(yl[1] - yl[0], xl[1] - xl[0])).astype(np.float64) for _ in range(5)]
+        want = oracle.source_log_likelihood(s, [(z, yl, xl, img) for z, img in zip(zs, oimgs)])
+        aux = torch.from_numpy(np.concatenate([z.ravel() for z in zs]).astype(np.float32)).to(engine.device())
+        offs = np.arange(5, dtype=np.int64) * zs[0].size
+        items["aux"] = np.arange(5)
+        ll, _ = engine.items_loglik(gimgs, gsrcs, items, mode=_ffi.CG_LL_CONDITIONAL, aux=aux, aux_offsets=offs)
+        assert abs(ll.sum().item() - want) <= LL_RTOL * abs(want)
+
+
+def test_planck_and_eigen_fluxes(engine, oracle):
+    from desi_mcmc_b200 import _ffi
+    oracle.set_filter_tables_npz(os.path.join(_ffi.PKG, "data", "filter_curves.npz"))
+    T = np.array([3000., 5777., 8395., 12000., 0.])
+    b = np.array([1e-10, 2e-10, 1., 3e-11, 1.])
+    got = engine.planck_fluxes(T, b)
+    for i in range(T.size):
+        for j, band in enumerate(oracle.BANDS):
+            want = oracle.photons_expected_brightness(T[i], b[i], band)
+            assert abs(got[i, j] - want) <= 1e-12 * abs(want)
+    rng = np.random.RandomState(6)
+    K, V, Cn = 4, 1364, 7
+    lam0 = np.linspace(600., 12000., V)
+    B = np.abs(rng.normal(size=(K, V))) + .1
+    B /= B.sum(axis=1, keepdims=True)
+    z = rng.uniform(.5, 5., size=Cn)
+    w = rng.dirichlet(np.ones(K), size=Cn)
+    m = np.exp(rng.normal(10., 1., size=Cn))
+    fl = np.abs(rng.normal(5., 2., size=(Cn, 5)))
+    iv = rng.uniform(.5, 2., size=(Cn, 5))
+    mu, ll = engine.eigen_fluxes(z, w, m, B, lam0, fl, iv)
+    for c in range(Cn):
+        spec = np.dot(w[c], B)
+        want_mu = oracle.project_to_bands(spec, lam0 * (1 + z[c])) * m[c] / (1 + z[c])
+        assert np.allclose(mu[c], want_mu, rtol=1e-11, atol=0)
+        want_ll = oracle.pixel_likelihood(z[c], w[c], m[c], fl[c], iv[c], lam0, B)
+        assert abs(ll[c] - want_ll) <= 1e-10 * abs(want_ll)
+
+
+def test_planck_star_render(engine, oracle):
+    """celeste.py:38-45: a star with a temperature takes the black-body flux."""
+    from desi_mcmc_b200 import _ffi
+    oracle.set_filter_tables_npz(os.path.join(_ffi.PKG, "data", "filter_curves.npz"))
+    field = synth.make_field(80, H=96, W=96, n_src=6, star_frac=1.0, planck_frac=1.0, margin=20)
+    nelec = hp.simulate_nelec(oracle, field, 2)
+    gimgs = hp.gpu_images(engine, field, nelec)
+    oimgs = hp.oracle_images(oracle, field, nelec)
+    ll = engine.field_loglik(gimgs, hp.gpu_sources(engine, field)).cpu().numpy()
+    osrcs = hp.oracle_sources(oracle, field)
+    for i, img in enumerate(oimgs):
+        want = oracle.celeste_likelihood(osrcs, img)
+        assert abs(ll[i] - want) <= LL_RTOL * abs(want)
