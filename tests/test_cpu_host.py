@@ -135,7 +135,7 @@ m = D.max_over_ranks(float(rank) + .5)
 assert m == 1.5
 dist.barrier()
 dist.destroy_process_group()
-open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "ok_%d" % rank), "w").write("ok")
+open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "ok_" + str(rank)), "w").write("ok")
 """
 
 
