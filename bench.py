@@ -100,6 +100,50 @@ def cpu_baseline(field, budget_s):
             "evals": r["evals"], "seconds": r["seconds"]}
 
 
+def bench_proposals(engine, synth, steps):
+    """Second half of BASELINE.json's metric: MCMC proposals/s (config 3: 4096
+    proposals of one galaxy on a 5-band 64x64 stamp, K = 42), device-resident and
+    end to end (host proposal arrays in, accept decisions out)."""
+    import torch
+    P, size = 4096, 64
+    field = synth.make_stamp(1003, size=size, n_star=1, n_gal=1)
+    rng = np.random.RandomState(1003)
+    dev = engine.device()
+    imgs = [engine.Image(nelec=torch.from_numpy(rng.poisson(450., size=(size, size)).astype(np.float32)),
+                         **synth.image_kwargs(m)) for m in field["images"]]
+    cur = field["sources"][1]
+    props, log_u = synth.make_proposals(1005, cur, P)
+    packed = engine.pack_sources([engine.SrcParams(**{k: s[k] for k in
+                                  ("u", "a", "b", "t", "theta", "phi", "sigma", "rho", "fluxes")})
+                                  for s in [cur] + props])
+    boxes = [(0, size, 0, size)] * 5
+    bgs = [np.full((size, size), im.epsilon, dtype=np.float32) for im in imgs]
+    sc = engine.ProposalScorer(imgs, boxes, bgs, max_proposals=P, guard=1e-2)
+    for _ in range(3):
+        delta, acc, ng = sc.score(packed, log_u)
+    evals = engine.last_eval_count()
+    d_src = engine.to_device(packed)
+    d_u = torch.from_numpy(log_u).to(dev)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        sc.score_device(d_src, P, None, d_u)
+    e1.record()
+    torch.cuda.synchronize()
+    dev_s = e0.elapsed_time(e1) * 1e-3
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        sc.score(packed, log_u)
+    e2e_s = time.perf_counter() - t0
+    return {"metric": "MCMC proposals/s per field", "workload": "C3: 4096 proposals x 5-band 64x64 galaxy stamp, "
+            "K=42 (dev 8 + exp 6 x 3-comp PSF), accept/reject on device from host log-uniforms",
+            "value": P * steps / dev_s, "unit": "proposals/s", "evals_per_s": evals * steps / dev_s,
+            "e2e": {"value": P * steps / e2e_s, "unit": "proposals/s",
+                    "h2d_bytes_per_step": int(packed.nbytes + log_u.nbytes), "d2h_bytes_per_step": P * 9 + 4},
+            "steps": steps, "accepted": int(acc.sum()), "guard_rescored": int(ng)}
+
+
 def run_reference(args, rank):
     """--impl reference: CPU arm, rank 0 only."""
     if rank != 0:
@@ -133,6 +177,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--fields-per-gpu", type=int, default=8)
+    ap.add_argument("--fields-per-call", type=int, default=2,
+                    help="fields batched into one cg_fields_loglik call (patches of a call stay in L2)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-proposals", action="store_true")
@@ -160,7 +206,7 @@ def main():
     F = args.fields_per_gpu
 
     # ---- synthetic fields of this rank (config 5 seeds 1005+f), pixels drawn on device
-    fields, images, srcs_host, srcs_dev = [], [], [], []
+    fields, images, srcs_host = [], [], []
     gen = torch.Generator(device=dev)
     for f in range(F):
         fid = rank * F + f
@@ -170,8 +216,7 @@ def main():
         packed = engine.pack_sources([engine.SrcParams(u=s["u"], a=s["a"], theta=s["theta"], phi=s["phi"],
                                                        sigma=s["sigma"], rho=s["rho"], fluxes=s["fluxes"])
                                       for s in fld["sources"]])
-        d_src = engine.to_device(packed)
-        _, models = engine.field_loglik(imgs, d_src, bound_cap=BOUND_CAP, max_patch_px=MAX_PATCH_PX,
+        _, models = engine.field_loglik(imgs, packed, bound_cap=BOUND_CAP, max_patch_px=MAX_PATCH_PX,
                                         return_model=True)
         gen.manual_seed(1005 + fid)
         for im, lam in zip(imgs, models):
@@ -180,36 +225,34 @@ def main():
         fields.append(fld)
         images.append(imgs)
         srcs_host.append(packed)
-        srcs_dev.append(d_src)
+    engine._state["ws"].clear()
     torch.cuda.synchronize()
 
-    ws = engine.field_workspace(images[0], N_SRC, MAX_PATCH_PX)
-    L = engine.lib()
-    import ctypes as C
-    harrs = [(C.c_void_p * 5)(*[im._h for im in imgs]) for imgs in images]
-    ll_dev = torch.zeros((F, 5), dtype=torch.float64, device=dev)
-    stats = torch.zeros(64, dtype=torch.float64, device=dev)     # [sum ll, n_star, n_gal, flux moments ...]
+    # field sets: FPC fields per cg_fields_loglik call (one prepare/render/gather launch each)
+    FPC = max(1, min(args.fields_per_call, F, _ffi.CG_MAX_FIELDS))
+    groups = [list(range(g, min(g + FPC, F))) for g in range(0, F, FPC)]
+    sets = [engine.FieldSet([images[f] for f in g], [N_SRC] * len(g), bound_cap=BOUND_CAP,
+                            max_patch_px=MAX_PATCH_PX) for g in groups]
+    for fs, g in zip(sets, groups):
+        fs.set_sources([srcs_host[f] for f in g])
+    stats = torch.zeros(64, dtype=torch.float64, device=dev)     # [sum ll, n_star, ...]
     n_star = float(sum(1 for fld in fields for s in fld["sources"] if s["a"] == 0))
 
-    def step_device(d_srcs_list):
-        st = engine.stream_ptr()
-        for f in range(F):
-            _ffi.check(L.cg_field_loglik(harrs[f], 5, d_srcs_list[f].data_ptr(), N_SRC, BOUND_CAP,
-                                         MAX_PATCH_PX, ll_dev[f].data_ptr(), None, ws.data_ptr(),
-                                         ws.numel(), st))
+    def step_device():
+        for fs in sets:
+            fs.loglik_device()
         if world > 1:
             stats.zero_()
-            stats[0] = ll_dev.sum()
+            stats[0] = sum(fs.ll.sum() for fs in sets)
             stats[1] = n_star
             dist.all_reduce(stats)
 
-    # evaluations per step (constant): count once per field
-    evals_step = 0
-    for f in range(F):
-        _ffi.check(L.cg_field_loglik(harrs[f], 5, srcs_dev[f].data_ptr(), N_SRC, BOUND_CAP, MAX_PATCH_PX,
-                                     ll_dev[f].data_ptr(), None, ws.data_ptr(), ws.numel(),
-                                     engine.stream_ptr()))
+    # evaluations per step (constant): count once per set
+    evals_step, issued_step = 0, 0
+    for fs in sets:
+        fs.loglik_device()
         evals_step += engine.last_eval_count()
+        issued_step += engine.last_issued_count()
 
     def barrier():
         if world > 1:
@@ -225,7 +268,7 @@ def main():
 
     # ---- device-resident leg
     for _ in range(args.warmup):
-        step_device(srcs_dev)
+        step_device()
     barrier()
     sampler = ClockSampler(local)
     sampler.start()
@@ -234,26 +277,28 @@ def main():
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
-        step_device(srcs_dev)
+        step_device()
     e1.record()
     barrier()
     dev_ms = max_over_ranks(e0.elapsed_time(e1))
     launches = engine.launch_count()
     render_ms, render_n = engine.profile_render_read()
     engine.profile_render(False)
-    clocks = sampler.stop()
-    ll_ref = ll_dev.cpu().numpy().copy()
+    ll_ref = np.concatenate([fs.ll.cpu().numpy() for fs in sets])
 
     # ---- end-to-end leg: host source arrays -> pinned -> device, ll -> host
-    stages = [engine.PinnedStage(N_SRC * _ffi.SRC_DTYPE.itemsize) for _ in range(F)]
-    ll_host = torch.zeros((F, 5), dtype=torch.float64).pin_memory()
-
     def step_e2e():
-        d = [stages[f].upload(srcs_host[f]) for f in range(F)]
-        step_device(d)
-        ll_host.copy_(ll_dev, non_blocking=True)
+        for fs, g in zip(sets, groups):
+            fs.set_sources([srcs_host[f] for f in g])
+            fs.loglik_device()
+            fs.h_ll.copy_(fs.ll, non_blocking=True)
+        if world > 1:
+            stats.zero_()
+            stats[0] = sum(fs.ll.sum() for fs in sets)
+            stats[1] = n_star
+            dist.all_reduce(stats)
         torch.cuda.current_stream().synchronize()
-        return float(ll_host.sum())
+        return float(sum(fs.h_ll.sum() for fs in sets))
 
     for _ in range(args.warmup):
         step_e2e()
@@ -264,7 +309,13 @@ def main():
     torch.cuda.synchronize()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     barrier()
-    assert np.array_equal(ll_host.numpy(), ll_ref), "e2e and device-resident results differ"
+    clocks = sampler.stop()
+    ll_e2e = np.concatenate([fs.h_ll.numpy() for fs in sets])
+    assert np.array_equal(ll_e2e, ll_ref), "e2e and device-resident results differ"
+
+    prop = None
+    if rank == 0 and not args.no_proposals:
+        prop = bench_proposals(engine, synth, max(3, min(args.steps, 10)))
 
     total_evals = evals_step * world          # every rank holds the same shapes, different seeds
     if world > 1:
@@ -291,7 +342,9 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": "f32 rates, f64 log-likelihood accumulation",
             "data": "synthetic",
             "config": {"workload": WORKLOAD, "fields_per_gpu": F, "fields_total": F * world,
-                       "evals_per_step_per_gpu": evals_step, "pixels_per_step_per_gpu": F * 5 * H * W,
+                       "fields_per_call": FPC,
+                       "evals_per_step_per_gpu": evals_step, "issued_lane_evals_per_step_per_gpu": issued_step,
+                       "pixels_per_step_per_gpu": F * 5 * H * W,
                        "l2": "inputs larger than L2 (%d MB of pixel data per GPU per step)" % (F * 5 * H * W * 4 >> 20),
                        "e2e_inputs": "packed source parameters (host) per step; image pixels resident",
                        "parallelism": "fields sharded over ranks; one float64 all-reduce per step" if world > 1 else "single GPU"},
@@ -303,6 +356,10 @@ def main():
                          "frac": (achieved / xu_peak) if achieved else None,
                          "peak_source": "measured live: MUFU.EX2 probe kernel on this GPU (cg_pipe_probe); "
                                         "nominal %d SMs x 16/clk x %.0f MHz = %.3g" % (sm, clocks["sm_mhz"] or 0, nominal),
+                         "issued": (issued_step * args.steps / (render_ms * 1e-3)) if render_ms > 0 else None,
+                         "issued_frac": (issued_step * args.steps / (render_ms * 1e-3) / xu_peak) if render_ms > 0 else None,
+                         "note": "achieved = algorithmic evals (footprint pixels x components, SURVEY 8d) / kernel time; "
+                                 "issued = MUFU.EX2 lane-operations actually executed after per-warp component culling",
                          "fp32_fma_peak": fma_peak, "kernel_ms_total": render_ms, "kernel_launches": render_n,
                          "kernel_share_of_step": render_ms / dev_ms if dev_ms else None,
                          "traffic": None,
@@ -310,6 +367,8 @@ def main():
             "clocks": clocks,
             "total_loglik": total_ll,
         }
+        if prop is not None:
+            line["proposals"] = prop
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = {k: v for k, v in cpu_baseline(fields[0], args.cpu_seconds).items()
                                     if k not in ("evals", "seconds")}

@@ -58,6 +58,9 @@ class CgBox(C.Structure):
     _fields_ = [("x0", C.c_int32), ("x1", C.c_int32), ("y0", C.c_int32), ("y1", C.c_int32)]
 
 
+CG_OPT_CULL = 1
+CG_MAX_FIELDS = 16
+
 # numpy mirrors of the POD arrays that cross the boundary in bulk
 SRC_DTYPE = np.dtype([("type", "<i4"), ("flags", "<i4"), ("u", "<f8", (2,)),
                       ("flux", "<f8", (CG_NUM_BANDS,)), ("theta", "<f8"), ("sigma", "<f8"),
@@ -94,6 +97,8 @@ PROTOTYPES = {
     "cg_render_patches": (C.c_int, [_vp, _i32, _vp, _i32, _vp, _i64, _i32, _dbl, _i64, _vp, _vp,
                                     _vp, _sz, _vp]),
     "cg_field_loglik": (C.c_int, [_vp, _i32, _vp, _i32, _dbl, _i64, _vp, _vp, _vp, _sz, _vp]),
+    "cg_fields_loglik": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _dbl, _i64, _vp, _vp, _vp, _sz, _vp]),
+    "cg_set_option": (C.c_int, [_i32, _i32]),
     "cg_items_loglik": (C.c_int, [_vp, _i32, _vp, _i32, _vp, _i64, _i32, _dbl, _i64, _vp, _vp,
                                   _vp, _vp, _i32, _vp, _sz, _vp]),
     "cg_score_proposals": (C.c_int, [_vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _dbl,
@@ -102,6 +107,7 @@ PROTOTYPES = {
     "cg_eigen_fluxes": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp]),
     "cg_launch_count": (_i64, [C.c_int]),
     "cg_last_eval_count": (_i64, [_vp]),
+    "cg_last_issued_count": (_i64, [_vp]),
     "cg_profile_render": (C.c_int, [C.c_int]),
     "cg_profile_render_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "cg_pipe_probe": (C.c_int, [C.c_int, C.POINTER(C.c_double), _vp]),

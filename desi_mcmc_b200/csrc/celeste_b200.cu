@@ -109,6 +109,8 @@ struct FilterTables {
   double sens[MAX_FILTER_ROWS];
 };
 static FilterTables* g_d_filters = nullptr;  // device
+struct LogTable;
+static LogTable* g_d_logtab = nullptr;       // device, filled at cg_init
 static int g_filters_loaded = 0;
 
 // ---------------------------------------------------------------------------
@@ -150,28 +152,60 @@ struct ItemHdr {
 };
 
 struct Counters {
-  int total_strips;
+  int total_strips;    // partial-sum slots handed out
   int work_counter;
   int guard_count;
-  int err_flag;        // 1: footprint larger than max_patch_px, 2: guard list overflow
-  unsigned long long evals;
-  unsigned long long pad;
+  int err_flag;        // 1: footprint larger than max_patch_px, 2: guard list overflow, 3: work list overflow
+  unsigned long long evals;    // algorithmic: footprint pixels x components
+  unsigned long long issued;   // lane-evaluations actually issued after culling (warp granular)
+  int heavy_strips;    // work units of galaxies, listed from the front of the work list
+  int light_strips;    // work units of stars (K <= 4), listed from the back
+  int pad[2];
 };
 
-#define TAB_STRIDE (CG_MAX_COMP * 6)
-#define STRIP_THREADS 128
-#define PIX_PER_THREAD 8
+// Component table: 12 values per component (three 16-byte loads):
+//   A, B, C, b10 | c01, c00, mx, my | qs, kx, ky, sl
+//   the quadratic A x^2 + B x y + C y^2 + b10 x + c01 y + c00 in log2 units,
+//   footprint-local integer coordinates, followed by the culling record: mean
+//   (mx, my), peak value qs, kx = 2 Sxx / log2(e), ky = 2 Syy / log2(e)
+//   (half-widths^2 of the level-set bounding box per unit of log2 drop) and
+//   sl = log2(e) / (2 lambda_min(Sigma)) (steepest log2 drop per squared pixel).
+#define TAB_W 12
+#define TAB_STRIDE (CG_MAX_COMP * TAB_W)
+// the render kernel takes work in units of up to UNIT_STRIPS strips of one item
+#define UNIT_STRIPS 4
+#define STRIP_THREADS 256
+#define PIX_PER_THREAD 4
 #define STRIP_PIX (STRIP_THREADS * PIX_PER_THREAD)
+// A strip is 256 consecutive 4-pixel chunks of a footprint in TILE-MAJOR order
+// (tiles of TILE_CW chunks x TILE_R rows), so that the 32 chunks of a warp
+// form a compact block of pixels and whole components can be culled per warp.
+#define TILE_CW 4
+#define TILE_R 8
+// a component is skipped for a warp when its largest value over the warp's
+// pixels is below 2^-CULL_T of a lower bound of the mixture there
+#define CULL_T 27.0f
+// full-field gather: image tiles of 64 x 16 pixels, per-tile source lists
+#define TILE_W 64
+#define TILE_H 16
+#define TILE_LIST_CAP 64
+
+#define CG_MAX_FIELDS 16
+struct FieldBatch {   // implicit_mode 3: independent fields, each a cross product of its sources x images
+  int n_fields;
+  int item_off[CG_MAX_FIELDS + 1], src_off[CG_MAX_FIELDS + 1], img_off[CG_MAX_FIELDS + 1];
+};
 
 struct PrepArgs {
   ImgPtrs imgs;
+  FieldBatch fb;
   int n_img;
   const CgSource* srcs;
   int n_src;
   const CgItem* items;      // NULL: implicit
   long long n_items;
   int default_flags;
-  int implicit_mode;        // 0 cross product; 1 per-image fixed boxes + aux=img; 2 indirect list
+  int implicit_mode;        // 0 cross product; 1 per-image fixed boxes + aux=img; 2 indirect list; 3 field batch
   const CgBox* img_boxes;   // device, n_img (implicit_mode >= 1)
   const int* ind_list;      // device (implicit_mode 2)
   const int* ind_count;     // device (implicit_mode 2): points at Counters.guard_count of pass 1
@@ -185,6 +219,10 @@ struct PrepArgs {
   Counters* cnt;
   CgBox* out_boxes;         // optional
   const FilterTables* filters;
+  // full-field path: per (image, 64x16 tile) list of the items that overlap it
+  int* tile_count;          // [n_img][max_tiles] (NULL: no binning)
+  int* tile_list;           // [n_img][max_tiles][TILE_LIST_CAP]
+  int max_tiles;
 };
 
 // ---------------------------------------------------------------------------
@@ -211,32 +249,32 @@ __device__ __forceinline__ double warp_max(double v) {
   return v;
 }
 
-// log(lam) for a positive normal float, absolute error ~3e-9: 32-entry table
-// of log(c_i) in float64 + degree-5 log1p of the residual in fp32.
+// log(lam) for a positive normal float, absolute error ~3e-9: a float64 table
+// t[idx] = (e - 127) ln 2 + log(c_i), idx = the float's exponent and top five
+// mantissa bits (c_i = centre of the mantissa bin), built once at cg_init and
+// L1-resident (a workload touches a few dozen entries), plus a degree-5 log1p
+// of the residual r = (m - c_i) / c_i, |r| <= 1/64, in fp32.
 struct LogTable {
-  double logc[32];
-  float invc[32];
+  double t[8192];
 };
-__device__ __forceinline__ void log_table_init(LogTable* t, int tid, int nthreads) {
-  for (int i = tid; i < 32; i += nthreads) {
-    double c = 1.0 + (2.0 * i + 1.0) / 64.0;
-    t->logc[i] = log(c);
-    t->invc[i] = (float)(1.0 / c);
-  }
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
 }
-__device__ __forceinline__ double log_accurate(float lam, const LogTable* t) {
-  int bits = __float_as_int(lam);
-  int e = (bits >> 23) - 127;
-  int i = (bits >> 18) & 31;
-  float m = __int_as_float((bits & 0x007fffff) | 0x3f800000);   // [1, 2)
-  float c = __int_as_float(0x3f800000 | (i << 18) | (1 << 17)); // 1 + (2i+1)/64
-  float r = (m - c) * t->invc[i];                               // |r| <= 1/64
+__device__ __forceinline__ float log_residual(float lam) {
+  const int bits = __float_as_int(lam);
+  const float m = __int_as_float((bits & 0x007fffff) | 0x3f800000);   // [1, 2)
+  const float c = __int_as_float((bits & 0x007c0000) | 0x3f820000);   // 1 + (2i+1)/64
+  const float r = (m - c) * rcp_approx(c);
   float p = fmaf(r, 0.2f, -0.25f);
   p = fmaf(r, p, 0.33333334f);
   p = fmaf(r, p, -0.5f);
   p = fmaf(r, p, 1.0f);
-  p = r * p;
-  return fma((double)e, LN2_D, t->logc[i]) + (double)p;
+  return r * p;
+}
+__device__ __forceinline__ double log_accurate(float lam, const LogTable* t) {
+  return __ldg(&t->t[(__float_as_int(lam) >> 18) & 8191]) + (double)log_residual(lam);
 }
 __device__ __forceinline__ double log_accurate(double lam, const LogTable*) { return log(lam); }
 
@@ -300,6 +338,16 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
   } else if (a.implicit_mode == 0) {
     it.src = (int)(i / a.n_img);
     it.img = (int)(i % a.n_img);
+    it.flags = a.default_flags;
+    it.aux = -1;
+    it.box[0] = it.box[1] = it.box[2] = it.box[3] = 0;
+  } else if (a.implicit_mode == 3) {
+    int f = 0;
+    while (f + 1 < a.fb.n_fields && i >= a.fb.item_off[f + 1]) ++f;
+    const int local = (int)i - a.fb.item_off[f];
+    const int ni = a.fb.img_off[f + 1] - a.fb.img_off[f];
+    it.src = a.fb.src_off[f] + local / ni;
+    it.img = a.fb.img_off[f] + local % ni;
     it.flags = a.default_flags;
     it.aux = -1;
     it.box[0] = it.box[1] = it.box[2] = it.box[3] = 0;
@@ -414,12 +462,23 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
     double k2 = (-LOG2PI_D - .5 * log(det) + log(w)) * LOG2E_D;
     double A = -.5 * LOG2E_D * i00, B = -LOG2E_D * i01, C = -.5 * LOG2E_D * i11;
     double mx = mux - ox, my = muy - oy;
-    tab[c * 6 + 0] = (real)A;
-    tab[c * 6 + 1] = (real)B;
-    tab[c * 6 + 2] = (real)C;
-    tab[c * 6 + 3] = (real)(-2. * A * mx - B * my);
-    tab[c * 6 + 4] = (real)(-B * mx - 2. * C * my);
-    tab[c * 6 + 5] = (real)(A * mx * mx + B * mx * my + C * my * my + k2);
+    real* t = tab + c * TAB_W;
+    t[0] = (real)A;
+    t[1] = (real)B;
+    t[2] = (real)C;
+    t[3] = (real)(-2. * A * mx - B * my);
+    t[4] = (real)(-B * mx - 2. * C * my);
+    t[5] = (real)(A * mx * mx + B * mx * my + C * my * my + k2);
+    t[6] = (real)mx;
+    t[7] = (real)my;
+    t[8] = (real)k2;
+    t[9] = (real)(2. * s00 / LOG2E_D);
+    t[10] = (real)(2. * s11 / LOG2E_D);
+    {
+      const double dd = s00 - s11;
+      const double lmin = .5 * ((s00 + s11) - sqrt(dd * dd + 4. * s01 * s01));
+      t[11] = (real)(.5 * LOG2E_D / fmax(lmin, 1e-300));
+    }
   }
   if (!star) {
     bound = warp_max(mybound);
@@ -464,16 +523,40 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
   const int wbox = x1 - x0, hbox = y1 - y0;
   const int cpr = (wbox + PIX_PER_THREAD - 1) / PIX_PER_THREAD;
   const int n_strips = (int)(((long long)hbox * cpr + STRIP_THREADS - 1) / STRIP_THREADS);
-  int start = 0;
+  const int n_units = (n_strips + UNIT_STRIPS - 1) / UNIT_STRIPS;
+  const bool heavy = K > 4;
+  int start = 0, wpos = 0;
   if (lane == 0) {
-    start = n_strips ? atomicAdd(&a.cnt->total_strips, n_strips) : 0;
+    if (n_strips) {
+      start = atomicAdd(&a.cnt->total_strips, n_strips);
+      wpos = atomicAdd(heavy ? &a.cnt->heavy_strips : &a.cnt->light_strips, n_units);
+    }
     if (npx) atomicAdd(&a.cnt->evals, (unsigned long long)npx * (unsigned long long)K);
     if (err) atomicExch(&a.cnt->err_flag, 1);
     if (start + n_strips > a.worklist_cap) { atomicExch(&a.cnt->err_flag, 3); }
   }
   start = __shfl_sync(0xffffffffu, start, 0);
+  wpos = __shfl_sync(0xffffffffu, wpos, 0);
+  // heavy strips fill the list from the front, light ones from the back: the
+  // render kernel drains the front first (longest-processing-time-first)
   if (start + n_strips <= a.worklist_cap)
-    for (int j = lane; j < n_strips; j += 32) a.worklist[start + j] = make_int2((int)i, j);
+    for (int j = lane; j < n_units; j += 32) {
+      const int slot = heavy ? (wpos + j) : (a.worklist_cap - 1 - (wpos + j));
+      a.worklist[slot] = make_int2((int)i, j * UNIT_STRIPS);   // (item, first strip of the unit)
+    }
+  // bin the footprint into the image tiles it overlaps (full-field gather)
+  if (a.tile_count && npx > 0 && K > 0) {
+    const int tiles_x = (W + TILE_W - 1) / TILE_W;
+    const int txa = x0 / TILE_W, txb = (x1 - 1) / TILE_W;
+    const int tya = y0 / TILE_H, tyb = (y1 - 1) / TILE_H;
+    const int nx = txb - txa + 1, nt = nx * (tyb - tya + 1);
+    for (int j = lane; j < nt; j += 32) {
+      const int t = (tya + j / nx) * tiles_x + txa + (j % nx);
+      const long long slot = (long long)it.img * a.max_tiles + t;
+      const int pos = atomicAdd(&a.tile_count[slot], 1);
+      if (pos < TILE_LIST_CAP) a.tile_list[slot * TILE_LIST_CAP + pos] = (int)i;
+    }
+  }
   if (lane == 0) {
     ItemHdr h;
     h.x0 = x0; h.x1 = x1; h.y0 = y0; h.y1 = y1;
@@ -497,126 +580,246 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
 #define MODE_POISSON 1
 #define MODE_COND 2
 
-
 struct RenderArgs {
   ImgPtrs imgs;
   const ItemHdr* hdr;
   const void* tab;
   const int2* worklist;
+  int worklist_cap;
   Counters* cnt;
   float* patches;             // MODE_PATCH
   long long max_patch_px;
   const float* aux;           // background / photon patches
   const long long* aux_offsets;
   double* partials;           // one per strip
+  int cull;                   // 0 disables component culling
+  const LogTable* logtab;
 };
+
+// q / d for 0 <= q < 2^22, d >= 1 through the fp32 reciprocal (+ one correction step)
+__device__ __forceinline__ int fast_div(int q, int d, float rd) {
+  int t = (int)((float)q * rd);
+  int r = q - t * d;
+  if (r < 0) { --t; r += d; }
+  if (r >= d) { ++t; }
+  return t;
+}
+
+// Chunk q of a (w x h) footprint in tile-major order -> (row, first column).
+// Tiles are TILE_CW chunks x TILE_R rows; edge tiles are narrower / shorter
+// and simply hold fewer chunks, so no lane is spent on padding tiles.
+__device__ __forceinline__ void chunk_decode(int q, int cpr, int hbox, float r_trow, int* row, int* cx) {
+  const int trow_chunks = cpr * TILE_R;
+  const int tr = fast_div(q, trow_chunks, r_trow);
+  const int rem = q - tr * trow_chunks;
+  const int R = min(TILE_R, hbox - tr * TILE_R);
+  const int ft = TILE_CW * R;
+  const int tc = fast_div(rem, ft, __frcp_rn((float)ft));
+  const int rem2 = rem - tc * ft;
+  const int tw = min(TILE_CW, cpr - tc * TILE_CW);
+  const int r = (tw == TILE_CW) ? (rem2 / TILE_CW) : fast_div(rem2, tw, __frcp_rn((float)tw));
+  const int c = rem2 - r * tw;
+  *row = tr * TILE_R + r;
+  *cx = (tc * TILE_CW + c) * PIX_PER_THREAD;
+}
+
+// Per-warp component culling over the warp's pixel rectangle [xa,xb] x [ya,yb]
+// (footprint-local coordinates).  Each lane owns components lane and lane+32.
+//   lower bound of the mixture  lb = max_k ( qs_k - sl_k * dfar_k^2 ), dfar = distance from the
+//                               mean to the farthest corner (Mahalanobis^2 <= d^2 / lambda_min);
+//   component k is dropped when even the bounding box of its level set
+//   { q_k >= lb - CULL_T } misses the rectangle, i.e. its largest value over
+//   the rectangle is below 2^-CULL_T of the mixture everywhere in it.
+// Survivors are compacted (component order preserved) into the warp's table
+// of 8-float entries; returns their number.
+__device__ __forceinline__ int cull_components(const float* s_tab, int K, int lane, float xa,
+                                               float xb, float ya, float yb, float* wtab) {
+  float lb = -INFINITY;
+  float4 e0[2], e1[2];
+  float qs[2], kx[2], ky[2], dx2[2], dy2[2];
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    const int k = lane + 32 * r;
+    qs[r] = -INFINITY; kx[r] = ky[r] = 0.f; dx2[r] = dy2[r] = 0.f;
+    if (k < K) {
+      e0[r] = *reinterpret_cast<const float4*>(s_tab + k * TAB_W);
+      e1[r] = *reinterpret_cast<const float4*>(s_tab + k * TAB_W + 4);
+      const float4 e2 = *reinterpret_cast<const float4*>(s_tab + k * TAB_W + 8);
+      const float mx = e1[r].z, my = e1[r].w;
+      qs[r] = e2.x; kx[r] = e2.y; ky[r] = e2.z;
+      const float fx = fmaxf(fabsf(xa - mx), fabsf(xb - mx)), fy = fmaxf(fabsf(ya - my), fabsf(yb - my));
+      const float l = qs[r] - e2.w * (fx * fx + fy * fy);
+      if (l == l) lb = fmaxf(lb, l);
+      const float dx = fmaxf(0.f, fmaxf(xa - mx, mx - xb)), dy = fmaxf(0.f, fmaxf(ya - my, my - yb));
+      dx2[r] = dx * dx; dy2[r] = dy * dy;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) lb = fmaxf(lb, __shfl_xor_sync(0xffffffffu, lb, o));
+  const float thr = lb - (CULL_T + 0.5f);       // 0.5: fp32 slack of the bounds
+  bool keep[2];
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    const float rho = (qs[r] - thr) * 1.0001f;
+    // !(a > b) keeps the component when a bound is NaN (degenerate component)
+    keep[r] = (lane + 32 * r < K) && !(rho < 0.f) && !(dx2[r] > rho * kx[r]) && !(dy2[r] > rho * ky[r]);
+  }
+  const unsigned m0 = __ballot_sync(0xffffffffu, keep[0]);
+  const unsigned m1 = __ballot_sync(0xffffffffu, keep[1]);
+  const unsigned lt = (1u << lane) - 1u;
+  if (keep[0]) {
+    float* d = wtab + __popc(m0 & lt) * 8;
+    *reinterpret_cast<float4*>(d) = e0[0];
+    *reinterpret_cast<float2*>(d + 4) = make_float2(e1[0].x, e1[0].y);
+  }
+  if (keep[1]) {
+    float* d = wtab + (__popc(m0) + __popc(m1 & lt)) * 8;
+    *reinterpret_cast<float4*>(d) = e0[1];
+    *reinterpret_cast<float2*>(d + 4) = make_float2(e1[1].x, e1[1].y);
+  }
+  __syncwarp();
+  return __popc(m0) + __popc(m1);
+}
 
 template <typename real, int MODE>
 __global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
   __shared__ __align__(16) real s_tab[TAB_STRIDE];
+  __shared__ __align__(16) float s_wtab[(sizeof(real) == 4) ? (STRIP_THREADS / 32) * CG_MAX_COMP * 8 : 4];
   __shared__ int s_work;
   __shared__ double s_red[STRIP_THREADS / 32];
-  __shared__ LogTable s_log;
-  const int tid = threadIdx.x;
-  if (MODE != MODE_PATCH) log_table_init(&s_log, tid, STRIP_THREADS);
-  const int total = *((volatile int*)&a.cnt->total_strips);
+  const LogTable* const logt = a.logtab;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int n_heavy = *((volatile int*)&a.cnt->heavy_strips);
+  const int total = n_heavy + *((volatile int*)&a.cnt->light_strips);
+  unsigned long long issued = 0;
 
+  if (tid == 0) s_work = atomicAdd(&a.cnt->work_counter, 1);
+  __syncthreads();
   for (;;) {
-    __syncthreads();
-    if (tid == 0) s_work = atomicAdd(&a.cnt->work_counter, 1);
-    __syncthreads();
     const int wk = s_work;
     if (wk >= total) break;
-    const int2 w = a.worklist[wk];
-    const int item = w.x, strip = w.y;
+    const int slot = (wk < n_heavy) ? wk : (a.worklist_cap - 1 - (wk - n_heavy));
+    const int2 w = a.worklist[slot];
+    const int item = w.x, strip0 = w.y;
     const ItemHdr h = a.hdr[item];
-    const real* gtab = reinterpret_cast<const real*>(a.tab) + (long long)item * TAB_STRIDE;
-    for (int t = tid; t < h.K * 6; t += STRIP_THREADS) s_tab[t] = gtab[t];
-    __syncthreads();
+    {
+      const real* gtab = reinterpret_cast<const real*>(a.tab) + (long long)item * TAB_STRIDE;
+      for (int t = tid; t < h.K * TAB_W; t += STRIP_THREADS) s_tab[t] = gtab[t];
+    }
+    __syncthreads();              // table staged; every thread has read s_work
+    int nxt = 0;
+    if (tid == 0) nxt = atomicAdd(&a.cnt->work_counter, 1);   // in flight during the unit
 
     const int wbox = h.x1 - h.x0, hbox = h.y1 - h.y0;
     const int cpr = (wbox + PIX_PER_THREAD - 1) / PIX_PER_THREAD;
-    const int q = strip * STRIP_THREADS + tid;
-    const int row = q / cpr;
-    const int cx = (q - row * cpr) * PIX_PER_THREAD;
-    const bool active = row < hbox;
-    const int npx = active ? min(PIX_PER_THREAD, wbox - cx) : 0;
+    const int n_chunks = cpr * hbox;
+    const float r_trow = __frcp_rn((float)(cpr * TILE_R));
+    const int strip_end = min(strip0 + UNIT_STRIPS, h.n_strips);
+    const DevImage* imp = (MODE != MODE_PATCH) ? a.imgs.p[h.img] : nullptr;
+    const real fl = (real)h.flux;
 
-    real acc[PIX_PER_THREAD];
-#pragma unroll
-    for (int p = 0; p < PIX_PER_THREAD; ++p) acc[p] = (real)0;
+#pragma unroll 1
+    for (int strip = strip0; strip < strip_end; ++strip) {
+      const int q = strip * STRIP_THREADS + tid;
+      const bool active = q < n_chunks;
+      int row = 0, cx = 0;
+      if (active) chunk_decode(q, cpr, hbox, r_trow, &row, &cx);
+      const int npx = active ? min(PIX_PER_THREAD, wbox - cx) : 0;
 
-    if (active) {
-      const real yl = (real)(h.y0 + row - h.oy);
-      const real xl0 = (real)(h.x0 + cx - h.ox);
-      real xl[PIX_PER_THREAD];
+      real acc[PIX_PER_THREAD];
 #pragma unroll
-      for (int p = 0; p < PIX_PER_THREAD; ++p) xl[p] = xl0 + (real)p;
-      const int K = h.K;
+      for (int p = 0; p < PIX_PER_THREAD; ++p) acc[p] = (real)0;
+
+      const unsigned act = __ballot_sync(0xffffffffu, active);
+      if (act) {                    // warp-uniform
+        int n = h.K;
+        const real* tb = s_tab;
+        int stride = TAB_W;
+        if (sizeof(real) == 4 && a.cull && n > 1) {
+          const int rmin = __reduce_min_sync(0xffffffffu, active ? row : 0x7fffffff);
+          const int rmax = __reduce_max_sync(0xffffffffu, active ? row : -1);
+          const int cmin = __reduce_min_sync(0xffffffffu, active ? cx : 0x7fffffff);
+          const int cmax = __reduce_max_sync(0xffffffffu, active ? cx + npx - 1 : -1);
+          float* wt = s_wtab + (tid >> 5) * (CG_MAX_COMP * 8);
+          __syncwarp();             // the warp is done reading its table of the previous strip
+          n = cull_components(reinterpret_cast<const float*>(s_tab), n, lane,
+                              (float)(h.x0 + cmin - h.ox), (float)(h.x0 + cmax - h.ox),
+                              (float)(h.y0 + rmin - h.oy), (float)(h.y0 + rmax - h.oy), wt);
+          tb = reinterpret_cast<const real*>(wt);
+          stride = 8;
+        }
+        if (lane == 0) issued += (unsigned long long)n * (32 * PIX_PER_THREAD);
+        const real yl = (real)(h.y0 + row - h.oy);
+        const real xl0 = (real)(h.x0 + cx - h.ox);
+        real xl[PIX_PER_THREAD];
+#pragma unroll
+        for (int p = 0; p < PIX_PER_THREAD; ++p) xl[p] = xl0 + (real)p;
 #pragma unroll 2
-      for (int k = 0; k < K; ++k) {
-        const real A = s_tab[k * 6 + 0], B = s_tab[k * 6 + 1], C = s_tab[k * 6 + 2];
-        const real b10 = s_tab[k * 6 + 3], c01 = s_tab[k * 6 + 4], c00 = s_tab[k * 6 + 5];
-        const real b1 = rfma(B, yl, b10);
-        const real c1 = rfma(rfma(C, yl, c01), yl, c00);
+        for (int k = 0; k < n; ++k, tb += stride) {
+          const real A = tb[0], B = tb[1], C = tb[2], b10 = tb[3], c01 = tb[4], c00 = tb[5];
+          const real b1 = rfma(B, yl, b10);
+          const real c1 = rfma(rfma(C, yl, c01), yl, c00);
 #pragma unroll
-        for (int p = 0; p < PIX_PER_THREAD; ++p) {
-          const real arg = rfma(rfma(A, xl[p], b1), xl[p], c1);
-          acc[p] += rexp2(arg);
+          for (int p = 0; p < PIX_PER_THREAD; ++p) {
+            const real arg = rfma(rfma(A, xl[p], b1), xl[p], c1);
+            acc[p] += rexp2(arg);
+          }
         }
       }
-    }
 
-    if (MODE == MODE_PATCH) {
-      if (active) {
-        float* out = a.patches + (long long)item * a.max_patch_px + (long long)row * wbox + cx;
-        const real fl = (real)h.flux;
+      if (MODE == MODE_PATCH) {
+        if (active) {
+          float* out = a.patches + (long long)item * a.max_patch_px + (long long)row * wbox + cx;
 #pragma unroll
-        for (int p = 0; p < PIX_PER_THREAD; ++p)
-          if (p < npx) out[p] = (float)(acc[p] * fl);
-      }
-    } else {
-      double s = 0.0;
-      if (active) {
-        const DevImage& im = *a.imgs.p[h.img];
-        const real fl = (real)h.flux;
-        const long long poff = (long long)row * wbox + cx;
-        const float* auxp = (h.aux >= 0) ? a.aux + a.aux_offsets[h.aux] + poff : nullptr;
-        if (MODE == MODE_POISSON) {
-          const float* data = im.nelec + (long long)(h.y0 + row) * im.W + (h.x0 + cx);
-          const float* mask = (im.mask && !(h.flags & CG_ITEM_NO_MASK))
-                                  ? im.mask + (long long)(h.y0 + row) * im.W + (h.x0 + cx) : nullptr;
-          const real eps = (real)im.epsilon;
+          for (int p = 0; p < PIX_PER_THREAD; ++p)
+            if (p < npx) out[p] = (float)(acc[p] * fl);
+        }
+      } else {
+        double s = 0.0;
+        if (active) {
+          const DevImage& im = *imp;
+          const long long poff = (long long)row * wbox + cx;
+          const float* auxp = (h.aux >= 0) ? a.aux + a.aux_offsets[h.aux] + poff : nullptr;
+          if (MODE == MODE_POISSON) {
+            const float* data = im.nelec + (long long)(h.y0 + row) * im.W + (h.x0 + cx);
+            const float* mask = (im.mask && !(h.flags & CG_ITEM_NO_MASK))
+                                    ? im.mask + (long long)(h.y0 + row) * im.W + (h.x0 + cx) : nullptr;
+            const real eps = (real)im.epsilon;
 #pragma unroll
-          for (int p = 0; p < PIX_PER_THREAD; ++p) {
-            if (p < npx) {
-              const real bg = auxp ? (real)auxp[p] : eps;
-              const real lam = bg + fl * acc[p];
-              const bool good = (lam > (real)0) && (!mask || mask[p] != 0.f);
-              if (good) s += (double)data[p] * log_accurate(lam, &s_log) - (double)lam;
+            for (int p = 0; p < PIX_PER_THREAD; ++p) {
+              if (p < npx) {
+                const real bg = auxp ? (real)auxp[p] : eps;
+                const real lam = bg + fl * acc[p];
+                const bool good = (lam > (real)0) && (!mask || mask[p] != 0.f);
+                if (good) s += (double)data[p] * log_accurate(lam, logt) - (double)lam;
+              }
             }
-          }
-        } else {  // MODE_COND, sources.py:171-174
+          } else {  // MODE_COND, sources.py:171-174
 #pragma unroll
-          for (int p = 0; p < PIX_PER_THREAD; ++p) {
-            if (p < npx) {
-              const real m = fl * acc[p];
-              if (m >= (real)1.17549435e-38f) s += log_accurate(m, &s_log) * (double)auxp[p];
+            for (int p = 0; p < PIX_PER_THREAD; ++p) {
+              if (p < npx) {
+                const real m = fl * acc[p];
+                if (m >= (real)1.17549435e-38f) s += log_accurate(m, logt) * (double)auxp[p];
+              }
             }
           }
         }
-      }
-      s = warp_sum(s);
-      if ((tid & 31) == 0) s_red[tid >> 5] = s;
-      __syncthreads();
-      if (tid == 0) {
-        double t = 0;
+        s = warp_sum(s);
+        __syncthreads();            // s_red of the previous strip has been consumed
+        if (lane == 0) s_red[tid >> 5] = s;
+        __syncthreads();
+        if (tid == 0) {
+          double t = 0;
 #pragma unroll
-        for (int wv = 0; wv < STRIP_THREADS / 32; ++wv) t += s_red[wv];
-        a.partials[h.strip_start + strip] = t;
+          for (int wv = 0; wv < STRIP_THREADS / 32; ++wv) t += s_red[wv];
+          a.partials[h.strip_start + strip] = t;
+        }
       }
     }
+    if (tid == 0) s_work = nxt;
+    __syncthreads();
   }
+  if (lane == 0 && issued) atomicAdd(&a.cnt->issued, issued);
 }
 
 // per-item sum of strip partials (fixed order -> deterministic)
@@ -635,107 +838,198 @@ __global__ void items_finalize_kernel(const ItemHdr* hdr, const double* partials
 // ---------------------------------------------------------------------------
 // field reduce (gather) : lambda = eps + sum patches ; ll = sum x log lam - lam
 // ---------------------------------------------------------------------------
-#define TILE_W 64
-#define TILE_H 16
+// One WARP per half image tile (64 x 8 pixels; lane = 4 pixels x 4 rows), no
+// block-level synchronisation on the data path: the warp reads its tile's
+// source list, orders it by item index with shuffles (so that every pixel adds
+// its sources in source order -> bitwise reproducible), gathers the patches
+// and accumulates the Poisson terms in float64.
+#define FR_WARPS 4
 struct FieldArgs {
   ImgPtrs imgs;
-  int n_img, n_src;
+  int n_img;
   const ItemHdr* hdr;
   const float* patches;
   long long max_patch_px;
-  double* tile_partials;   // [n_img][max_tiles]
-  int max_tiles;
-  float* model[CG_MAX_IMAGES > 16 ? 16 : CG_MAX_IMAGES];  // optional outputs (first 16 images)
-  int has_model;
+  const int* tile_count;   // [n_img][max_tiles]
+  const int* tile_list;    // [n_img][max_tiles][TILE_LIST_CAP]
+  int* done;               // [n_img] blocks finished (zero on entry, reset on exit)
+  double* block_partials;  // [n_img][blocks_per_img]
+  double* ll;              // [n_img]
+  int max_tiles, blocks_per_img;
+  // overflow fallback: the items of image i are item_base[i] + s*item_stride[i], s < n_src[i]
+  int item_base[CG_MAX_IMAGES], item_stride[CG_MAX_IMAGES], n_src[CG_MAX_IMAGES];
+  float* const* model;     // device array [n_img] of optional model outputs, or NULL
+  const LogTable* logtab;  // precomputed at cg_init
 };
 
-__global__ void __launch_bounds__(256) field_reduce_kernel(FieldArgs a) {
+__device__ __forceinline__ void gather_patch(float (&lam)[4][4], const float* patches,
+                                             long long max_patch_px, int item, int bx0, int bx1,
+                                             int by0, int by1, int x, int ybase) {
+  const int wb = bx1 - bx0;
+  const float* base = patches + (long long)item * max_patch_px - bx0;
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int y = ybase + r;
+    if (y >= by0 && y < by1) {
+      const float* rowp = base + (long long)(y - by0) * wb;
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        const int xx = x + p;
+        if (xx >= bx0 && xx < bx1) lam[r][p] += rowp[xx];
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(FR_WARPS * 32) field_reduce_kernel(FieldArgs a) {
   const int img = blockIdx.y;
   const DevImage& im = *a.imgs.p[img];
   const int H = im.H, W = im.W;
   const int tiles_x = (W + TILE_W - 1) / TILE_W, tiles_y = (H + TILE_H - 1) / TILE_H;
-  const int tile = blockIdx.x;
-  if (tile >= tiles_x * tiles_y) return;
-  const int tx = tile % tiles_x, ty = tile / tiles_x;
+  const int n_tiles = tiles_x * tiles_y;
+  const int n_blocks = (2 * n_tiles + FR_WARPS - 1) / FR_WARPS;
+  if ((int)blockIdx.x >= n_blocks) return;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int X0 = tx * TILE_W, Y0 = ty * TILE_H;
-  const int x = X0 + (tid & 15) * 4, y = Y0 + (tid >> 4);
 
-  __shared__ int s_wcount[8];
-  __shared__ int4 s_box[256];
-  __shared__ int s_item[256];
-  __shared__ double s_red[8];
-  __shared__ LogTable s_log;
-  log_table_init(&s_log, tid, 256);
+  __shared__ double s_red[FR_WARPS];
+  __shared__ int s_last;
+  const LogTable* const logt = a.logtab;
 
-  const float eps = (float)im.epsilon;
-  float lam[4] = {eps, eps, eps, eps};
+  const int ht = blockIdx.x * FR_WARPS + warp;      // half-tile index
+  const int tile = ht >> 1;
+  double s = 0.0;
+  if (tile < n_tiles) {
+    const int tx = tile % tiles_x, ty = tile / tiles_x;
+    const int X0 = tx * TILE_W, Y0 = ty * TILE_H + (ht & 1) * (TILE_H / 2);
+    const int x = X0 + (lane & 15) * 4, ybase = Y0 + (lane >> 4) * 4;
+    const bool vec = (x + 3 < W) && ((W & 3) == 0) && (((uintptr_t)im.nelec & 15) == 0);
 
-  for (int base = 0; base < a.n_src; base += 256) {
-    const int sidx = base + tid;
-    bool hit = false;
-    int4 bx = make_int4(0, 0, 0, 0);
-    int item = 0;
-    if (sidx < a.n_src) {
-      item = sidx * a.n_img + img;
-      const ItemHdr* hp = a.hdr + item;
-      bx = *reinterpret_cast<const int4*>(hp);   // x0,x1,y0,y1
-      hit = (bx.y > bx.x) && (bx.w > bx.z) && bx.x < X0 + TILE_W && bx.y > X0 &&
-            bx.z < Y0 + TILE_H && bx.w > Y0;
-    }
-    const unsigned bal = __ballot_sync(0xffffffffu, hit);
-    if (lane == 0) s_wcount[warp] = __popc(bal);
-    __syncthreads();
-    int off = 0, nh = 0;
+    // the pixel counts do not depend on the list: issue their loads first
+    float d[4][4];
 #pragma unroll
-    for (int wv = 0; wv < 8; ++wv) {
-      int cnt = s_wcount[wv];
-      if (wv < warp) off += cnt;
-      nh += cnt;
-    }
-    if (hit) {
-      int pos = off + __popc(bal & ((1u << lane) - 1));
-      s_box[pos] = bx;
-      s_item[pos] = item;
-    }
-    __syncthreads();
-    for (int j = 0; j < nh; ++j) {
-      const int4 b = s_box[j];
-      if (y >= b.z && y < b.w) {
-        const int wb = b.y - b.x;
-        const float* rowp = a.patches + (long long)s_item[j] * a.max_patch_px +
-                            (long long)(y - b.z) * wb - b.x;
+    for (int r = 0; r < 4; ++r) {
+      const int y = ybase + r;
 #pragma unroll
-        for (int p = 0; p < 4; ++p) {
-          int xx = x + p;
-          if (xx >= b.x && xx < b.y) lam[p] += rowp[xx];
+      for (int p = 0; p < 4; ++p) d[r][p] = 0.f;
+      if (y < H && im.nelec) {
+        const float* rp = im.nelec + (long long)y * W + x;
+        if (vec) {
+          const float4 v = *reinterpret_cast<const float4*>(rp);
+          d[r][0] = v.x; d[r][1] = v.y; d[r][2] = v.z; d[r][3] = v.w;
+        } else {
+#pragma unroll
+          for (int p = 0; p < 4; ++p)
+            if (x + p < W) d[r][p] = rp[p];
         }
       }
     }
-    __syncthreads();
-  }
 
-  double s = 0.0;
-  if (y < H) {
-    const long long rowoff = (long long)y * W;
-    float d[4] = {0, 0, 0, 0};
-    if (im.nelec) {
-      if (x + 3 < W && ((rowoff + x) & 3) == 0 && ((uintptr_t)im.nelec & 15) == 0) {
-        float4 v = *reinterpret_cast<const float4*>(im.nelec + rowoff + x);
-        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
-      } else {
+    const float eps = (float)im.epsilon;
+    float lam[4][4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int p = 0; p < 4; ++p) lam[r][p] = eps;
+
+    const long long tslot = (long long)img * a.max_tiles + tile;
+    const int cnt = a.tile_count[tslot];
+    if (cnt <= TILE_LIST_CAP) {
+      // lane j owns list entries j and j+32
+      int it0 = 0x7fffffff, it1 = 0x7fffffff;
+      int4 b0 = make_int4(0, 0, 0, 0), b1 = b0;
+      if (lane < cnt) {
+        it0 = a.tile_list[tslot * TILE_LIST_CAP + lane];
+        b0 = *reinterpret_cast<const int4*>(a.hdr + it0);       // x0,x1,y0,y1
+      }
+      if (lane + 32 < cnt) {
+        it1 = a.tile_list[tslot * TILE_LIST_CAP + lane + 32];
+        b1 = *reinterpret_cast<const int4*>(a.hdr + it1);
+      }
+      int r0 = 0, r1 = 0;
+      if (cnt > 1) {
+        const int n0 = min(cnt, 32);
+        for (int j = 0; j < n0; ++j) {
+          const int v = __shfl_sync(0xffffffffu, it0, j);
+          r0 += (v < it0); r1 += (v < it1);
+        }
+        for (int j = 0; j < cnt - 32; ++j) {
+          const int v = __shfl_sync(0xffffffffu, it1, j);
+          r0 += (v < it0); r1 += (v < it1);
+        }
+      }
+      for (int r = 0; r < cnt; ++r) {
+        const unsigned m0 = __ballot_sync(0xffffffffu, lane < cnt && r0 == r);
+        int item, bx0, bx1, by0, by1;
+        if (m0) {
+          const int sl = __ffs(m0) - 1;
+          item = __shfl_sync(0xffffffffu, it0, sl);
+          bx0 = __shfl_sync(0xffffffffu, b0.x, sl); bx1 = __shfl_sync(0xffffffffu, b0.y, sl);
+          by0 = __shfl_sync(0xffffffffu, b0.z, sl); by1 = __shfl_sync(0xffffffffu, b0.w, sl);
+        } else {
+          const unsigned m1 = __ballot_sync(0xffffffffu, lane + 32 < cnt && r1 == r);
+          const int sl = __ffs(m1) - 1;
+          item = __shfl_sync(0xffffffffu, it1, sl);
+          bx0 = __shfl_sync(0xffffffffu, b1.x, sl); bx1 = __shfl_sync(0xffffffffu, b1.y, sl);
+          by0 = __shfl_sync(0xffffffffu, b1.z, sl); by1 = __shfl_sync(0xffffffffu, b1.w, sl);
+        }
+        gather_patch(lam, a.patches, a.max_patch_px, item, bx0, bx1, by0, by1, x, ybase);
+      }
+    } else {
+      // more sources than a list holds: scan every source of this image, 32 at
+      // a time; hits are taken in lane order = source order
+      const int ns = a.n_src[img];
+      const int YA = Y0, YB = Y0 + TILE_H / 2;
+      for (int base = 0; base < ns; base += 32) {
+        const int sidx = base + lane;
+        bool hit = false;
+        int4 bx = make_int4(0, 0, 0, 0);
+        int item = 0;
+        if (sidx < ns) {
+          item = a.item_base[img] + sidx * a.item_stride[img];
+          const ItemHdr* hp = a.hdr + item;
+          bx = *reinterpret_cast<const int4*>(hp);
+          hit = (hp->K > 0) && (bx.y > bx.x) && (bx.w > bx.z) && bx.x < X0 + TILE_W && bx.y > X0 &&
+                bx.z < YB && bx.w > YA;
+        }
+        unsigned bal = __ballot_sync(0xffffffffu, hit);
+        while (bal) {
+          const int sl = __ffs(bal) - 1;
+          bal &= bal - 1;
+          gather_patch(lam, a.patches, a.max_patch_px, __shfl_sync(0xffffffffu, item, sl),
+                       __shfl_sync(0xffffffffu, bx.x, sl), __shfl_sync(0xffffffffu, bx.y, sl),
+                       __shfl_sync(0xffffffffu, bx.z, sl), __shfl_sync(0xffffffffu, bx.w, sl), x, ybase);
+        }
+      }
+    }
+
+    float* mdl = a.model ? a.model[img] : nullptr;
+    // sum x log(lam) and sum lam, both in float64 (two independent chains)
+    double slam = 0.0;
+    if (x + 3 < W && ybase + 3 < H && im.nelec) {          // interior lane: no bounds tests
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          s = fma((double)d[r][p], log_accurate(lam[r][p], logt), s);
+          slam += (double)lam[r][p];
+        }
+    } else if (im.nelec) {
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
 #pragma unroll
         for (int p = 0; p < 4; ++p)
-          if (x + p < W) d[p] = im.nelec[rowoff + x + p];
-      }
-#pragma unroll
-      for (int p = 0; p < 4; ++p)
-        if (x + p < W) s += (double)d[p] * log_accurate(lam[p], &s_log) - (double)lam[p];
+          if (ybase + r < H && x + p < W) {
+            s = fma((double)d[r][p], log_accurate(lam[r][p], logt), s);
+            slam += (double)lam[r][p];
+          }
     }
-    if (a.has_model && img < 16 && a.model[img]) {
+    s -= slam;
+    if (mdl) {
 #pragma unroll
-      for (int p = 0; p < 4; ++p)
-        if (x + p < W) a.model[img][rowoff + x + p] = lam[p];
+      for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int p = 0; p < 4; ++p)
+          if (ybase + r < H && x + p < W) mdl[(long long)(ybase + r) * W + x + p] = lam[r][p];
     }
   }
   s = warp_sum(s);
@@ -744,27 +1038,27 @@ __global__ void __launch_bounds__(256) field_reduce_kernel(FieldArgs a) {
   if (tid == 0) {
     double t = 0;
 #pragma unroll
-    for (int wv = 0; wv < 8; ++wv) t += s_red[wv];
-    a.tile_partials[(long long)img * a.max_tiles + tile] = t;
+    for (int wv = 0; wv < FR_WARPS; ++wv) t += s_red[wv];
+    a.block_partials[(long long)img * a.blocks_per_img + blockIdx.x] = t;
+    __threadfence();
+    s_last = (atomicAdd(&a.done[img], 1) == n_blocks - 1);
   }
-}
-
-// one block per image: fixed-shape tree over the tile partials
-__global__ void __launch_bounds__(256) field_final_kernel(const double* tile_partials, int max_tiles,
-                                                          ImgPtrs imgs, double* ll) {
-  const int img = blockIdx.x;
-  const DevImage& im = *imgs.p[img];
-  const int nt = ((im.W + TILE_W - 1) / TILE_W) * ((im.H + TILE_H - 1) / TILE_H);
-  __shared__ double s_red[256];
-  double s = 0;
-  for (int t = threadIdx.x; t < nt; t += 256) s += tile_partials[(long long)img * max_tiles + t];
-  s_red[threadIdx.x] = s;
   __syncthreads();
-  for (int o = 128; o > 0; o >>= 1) {
-    if (threadIdx.x < o) s_red[threadIdx.x] += s_red[threadIdx.x + o];
+  if (s_last) {
+    // the last block of the image sums the block partials in a fixed tree
+    __threadfence();
+    __shared__ double s_fin[FR_WARPS * 32];
+    double t = 0;
+    const volatile double* bp = a.block_partials + (long long)img * a.blocks_per_img;
+    for (int i = tid; i < n_blocks; i += FR_WARPS * 32) t += bp[i];
+    s_fin[tid] = t;
     __syncthreads();
+    for (int o = FR_WARPS * 16; o > 0; o >>= 1) {
+      if (tid < o) s_fin[tid] += s_fin[tid + o];
+      __syncthreads();
+    }
+    if (tid == 0) { a.ll[img] = s_fin[0]; a.done[img] = 0; }
   }
-  if (threadIdx.x == 0) ll[img] = s_red[0];
 }
 
 // ---------------------------------------------------------------------------
@@ -1000,6 +1294,8 @@ static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; 
 
 struct WsLayout {
   size_t counters, hdr, tab, worklist, partials, item_ll, img_boxes, aux_offsets, tiles, patches;
+  size_t tile_count, done, tile_list, model_ptrs;   // full-field gather (tile_count and done are contiguous)
+  size_t tile_zero_bytes;
   // second pass (float64 re-score)
   size_t counters2, hdr2, tab2, worklist2, partials2, item_ll2, guard_list;
   size_t total;
@@ -1030,7 +1326,14 @@ static WsLayout ws_layout(long long n_items, long long max_patch_px, int with_pa
   L.img_boxes = take(sizeof(CgBox) * CG_MAX_IMAGES);
   L.aux_offsets = take(sizeof(long long) * CG_MAX_IMAGES);
   L.tiles = take(sizeof(double) * (size_t)n_tiles_total);
-  if (with_patches) L.patches = take(sizeof(float) * (size_t)(n_items * max_patch_px));
+  if (with_patches) {
+    L.tile_count = take(sizeof(int) * (size_t)n_tiles_total);
+    L.done = take(sizeof(int) * CG_MAX_IMAGES);
+    L.tile_zero_bytes = (L.done + sizeof(int) * CG_MAX_IMAGES) - L.tile_count;
+    L.tile_list = take(sizeof(int) * (size_t)n_tiles_total * TILE_LIST_CAP);
+    L.model_ptrs = take(sizeof(float*) * CG_MAX_IMAGES);
+    L.patches = take(sizeof(float) * (size_t)(n_items * max_patch_px));
+  }
   if (n_img_for_guard > 0) {
     L.guard_cap = GUARD_CAP;
     L.n_items2 = (long long)(GUARD_CAP + 1) * n_img_for_guard;
@@ -1081,6 +1384,15 @@ int cg_init(int device) {
   for (int i = 0; i < 6; ++i) { pc.exp_amp[i] = H_EXP_AMP_RAW[i] / se; pc.exp_var[i] = H_EXP_VAR[i]; }
   for (int i = 0; i < 8; ++i) { pc.dev_amp[i] = H_DEV_AMP_RAW[i] / sd; pc.dev_var[i] = H_DEV_VAR[i]; }
   CUDA_TRY(cudaMemcpyToSymbol(c_prof, &pc, sizeof pc));
+  if (!g_d_logtab) {
+    CUDA_TRY(cudaMalloc(&g_d_logtab, sizeof(LogTable)));
+    std::vector<double> lt(8192);
+    for (int idx = 0; idx < 8192; ++idx) {
+      const long double c = 1.0L + (2.0L * (idx & 31) + 1.0L) / 64.0L;
+      lt[idx] = (double)((long double)((idx >> 5) - 127) * 0.693147180559945309417232121458L + logl(c));
+    }
+    CUDA_TRY(cudaMemcpy(g_d_logtab, lt.data(), sizeof(LogTable), cudaMemcpyHostToDevice));
+  }
   if (!g_d_filters) {
     CUDA_TRY(cudaMalloc(&g_d_filters, sizeof(FilterTables)));
     CUDA_TRY(cudaMemset(g_d_filters, 0, sizeof(FilterTables)));
@@ -1102,6 +1414,14 @@ int64_t cg_launch_count(int reset) {
   long long v = g_launches.load();
   if (reset) g_launches.store(0);
   return v;
+}
+
+int64_t cg_last_issued_count(void* stream) {
+  if (!g_last_counters) return 0;
+  Counters c;
+  if (cudaStreamSynchronize((cudaStream_t)stream) != cudaSuccess) return -1;
+  if (cudaMemcpy(&c, g_last_counters, sizeof c, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+  return (int64_t)c.issued;
 }
 
 int64_t cg_last_eval_count(void* stream) {
@@ -1322,7 +1642,19 @@ static int fill_imgs(CgImage* const* imgs, int n_img, ImgPtrs* out) {
 
 }  // extern "C"
 
-static int render_grid() { return g_sm_count * 16; }
+static int g_cull = 1;
+
+// persistent grid: one CTA per resident slot
+template <typename real, int MODE>
+static int render_grid() {
+  static int per_sm = 0;
+  if (!per_sm) {
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_kernel<real, MODE>, STRIP_THREADS, 0) !=
+            cudaSuccess || per_sm < 1)
+      per_sm = 4;
+  }
+  return g_sm_count * per_sm;
+}
 
 template <typename real>
 static int run_prepare(const PrepArgs& pa, cudaStream_t st) {
@@ -1338,7 +1670,7 @@ static int run_render(const RenderArgs& ra, long long n_items, cudaStream_t st) 
   if (n_items == 0) return CG_OK;
   const bool prof = g_prof_on && g_prof_n < PROF_MAX;
   if (prof) cudaEventRecord(g_prof_ev[2 * g_prof_n], st);
-  render_kernel<real, MODE><<<render_grid(), STRIP_THREADS, 0, st>>>(ra);
+  render_kernel<real, MODE><<<render_grid<real, MODE>(), STRIP_THREADS, 0, st>>>(ra);
   if (prof) { cudaEventRecord(g_prof_ev[2 * g_prof_n + 1], st); ++g_prof_n; }
   LAUNCH_CHECK();
   return CG_OK;
@@ -1372,28 +1704,51 @@ int cg_render_patches(CgImage* const* imgs, int32_t n_img, const CgSource* d_src
   if (rc) return rc;
   RenderArgs ra;
   memset(&ra, 0, sizeof ra);
-  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.cnt = cnt;
+  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.worklist_cap = pa.worklist_cap; ra.cull = g_cull; ra.logtab = g_d_logtab; ra.cnt = cnt;
   ra.patches = d_patches; ra.max_patch_px = max_patch_px;
   rc = run_render<float, MODE_PATCH>(ra, n_items, st);
   g_last_counters = cnt;
   return rc;
 }
 
-int cg_field_loglik(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs, int32_t n_src,
-                    double bound_cap, int64_t max_patch_px, double* d_ll, float* const* h_d_model,
-                    void* d_ws, size_t ws_bytes, void* stream) {
+int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off, const CgSource* d_srcs,
+                     const int32_t* h_src_off, int32_t n_fields, double bound_cap,
+                     int64_t max_patch_px, double* d_ll, float* const* h_d_model, void* d_ws,
+                     size_t ws_bytes, void* stream) {
   NEED_INIT();
   cudaStream_t st = (cudaStream_t)stream;
+  if (n_fields < 1 || n_fields > CG_MAX_FIELDS) return fail(CG_EINVAL, "n_fields must be in [1,%d]", CG_MAX_FIELDS);
+  if (!h_img_off || !h_src_off) return fail(CG_EINVAL, "null offsets");
+  const int n_img = h_img_off[n_fields];
   PrepArgs pa;
   memset(&pa, 0, sizeof pa);
   int rc = fill_imgs(imgs, n_img, &pa.imgs);
   if (rc) return rc;
-  if (n_src < 0) return fail(CG_EINVAL, "negative n_src");
-  long long n_items = (long long)n_src * n_img;
+  FieldArgs fa;
+  memset(&fa, 0, sizeof fa);
+  long long n_items = 0;
+  pa.fb.n_fields = n_fields;
+  for (int f = 0; f < n_fields; ++f) {
+    const int ni = h_img_off[f + 1] - h_img_off[f], ns = h_src_off[f + 1] - h_src_off[f];
+    if (ni < 1 || ns < 0) return fail(CG_EINVAL, "field %d: bad image/source offsets", f);
+    pa.fb.item_off[f] = (int)n_items;
+    pa.fb.src_off[f] = h_src_off[f];
+    pa.fb.img_off[f] = h_img_off[f];
+    for (int b = 0; b < ni; ++b) {
+      const int gi = h_img_off[f] + b;
+      fa.item_base[gi] = (int)n_items + b;
+      fa.item_stride[gi] = ni;
+      fa.n_src[gi] = ns;
+    }
+    n_items += (long long)ns * ni;
+  }
+  pa.fb.item_off[n_fields] = (int)n_items;
+  pa.fb.src_off[n_fields] = h_src_off[n_fields];
+  pa.fb.img_off[n_fields] = n_img;
+  if (n_items > 0x7fffffffLL) return fail(CG_EINVAL, "too many (source, image) items");
   int max_tiles = 0;
   for (int i = 0; i < n_img; ++i) {
-    int t = ((imgs[i]->h.W + TILE_W - 1) / TILE_W) * ((imgs[i]->h.H + TILE_H - 1) / TILE_H);
-    max_tiles = std::max(max_tiles, t);
+    max_tiles = std::max(max_tiles, (int)cg_field_tiles(imgs[i]->h.H, imgs[i]->h.W));
     if (!imgs[i]->h.nelec) return fail(CG_EINVAL, "image %d has no nelec buffer", i);
   }
   WsLayout L = ws_layout(std::max<long long>(n_items, 1), max_patch_px, 1, 0, (long long)max_tiles * n_img);
@@ -1401,34 +1756,56 @@ int cg_field_loglik(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs,
   char* base = (char*)d_ws;
   Counters* cnt = (Counters*)(base + L.counters);
   CUDA_TRY(cudaMemsetAsync(cnt, 0, sizeof(Counters), st));
-  pa.n_img = n_img; pa.srcs = d_srcs; pa.n_src = n_src; pa.items = nullptr; pa.n_items = n_items;
-  pa.default_flags = CG_ITEM_FLUX_BAND; pa.implicit_mode = 0; pa.bound_cap = bound_cap;
+  CUDA_TRY(cudaMemsetAsync(base + L.tile_count, 0, L.tile_zero_bytes, st));
+  pa.n_img = n_img; pa.srcs = d_srcs; pa.n_src = h_src_off[n_fields]; pa.items = nullptr; pa.n_items = n_items;
+  pa.default_flags = CG_ITEM_FLUX_BAND; pa.implicit_mode = 3; pa.bound_cap = bound_cap;
   pa.max_patch_px = max_patch_px; pa.hdr = (ItemHdr*)(base + L.hdr); pa.tab = base + L.tab;
   pa.worklist = (int2*)(base + L.worklist); pa.worklist_cap = L.worklist_cap; pa.cnt = cnt;
   pa.filters = g_d_filters;
+  pa.tile_count = (int*)(base + L.tile_count); pa.tile_list = (int*)(base + L.tile_list);
+  pa.max_tiles = max_tiles;
   rc = run_prepare<float>(pa, st);
   if (rc) return rc;
   RenderArgs ra;
   memset(&ra, 0, sizeof ra);
-  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.cnt = cnt;
+  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.worklist_cap = pa.worklist_cap; ra.cull = g_cull; ra.logtab = g_d_logtab; ra.cnt = cnt;
   ra.patches = (float*)(base + L.patches); ra.max_patch_px = max_patch_px;
   rc = run_render<float, MODE_PATCH>(ra, n_items, st);
   if (rc) return rc;
-  FieldArgs fa;
-  memset(&fa, 0, sizeof fa);
-  fa.imgs = pa.imgs; fa.n_img = n_img; fa.n_src = n_src; fa.hdr = pa.hdr;
+  fa.imgs = pa.imgs; fa.n_img = n_img; fa.hdr = pa.hdr;
   fa.patches = ra.patches; fa.max_patch_px = max_patch_px;
-  fa.tile_partials = (double*)(base + L.tiles); fa.max_tiles = max_tiles;
+  fa.tile_count = pa.tile_count; fa.tile_list = pa.tile_list; fa.done = (int*)(base + L.done);
+  const int blocks_per_img = (2 * max_tiles + FR_WARPS - 1) / FR_WARPS;
+  fa.block_partials = (double*)(base + L.tiles); fa.max_tiles = max_tiles; fa.ll = d_ll;
+  fa.blocks_per_img = blocks_per_img; fa.logtab = g_d_logtab;
   if (h_d_model) {
-    if (n_img > 16) return fail(CG_EINVAL, "model output supports at most 16 images per call");
-    for (int i = 0; i < n_img; ++i) { fa.model[i] = h_d_model[i]; if (h_d_model[i]) fa.has_model = 1; }
+    bool any = false;
+    for (int i = 0; i < n_img; ++i) any = any || h_d_model[i];
+    if (any) {
+      CUDA_TRY(cudaMemcpyAsync(base + L.model_ptrs, h_d_model, sizeof(float*) * n_img, cudaMemcpyHostToDevice, st));
+      fa.model = (float* const*)(base + L.model_ptrs);
+    }
   }
-  field_reduce_kernel<<<dim3(max_tiles, n_img), 256, 0, st>>>(fa);
-  LAUNCH_CHECK();
-  field_final_kernel<<<n_img, 256, 0, st>>>(fa.tile_partials, max_tiles, pa.imgs, d_ll);
+  field_reduce_kernel<<<dim3(blocks_per_img, n_img), FR_WARPS * 32, 0, st>>>(fa);
   LAUNCH_CHECK();
   g_last_counters = cnt;
   return CG_OK;
+}
+
+int cg_field_loglik(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs, int32_t n_src,
+                    double bound_cap, int64_t max_patch_px, double* d_ll, float* const* h_d_model,
+                    void* d_ws, size_t ws_bytes, void* stream) {
+  if (n_src < 0) return fail(CG_EINVAL, "negative n_src");
+  const int32_t img_off[2] = {0, n_img}, src_off[2] = {0, n_src};
+  return cg_fields_loglik(imgs, img_off, d_srcs, src_off, 1, bound_cap, max_patch_px, d_ll, h_d_model,
+                          d_ws, ws_bytes, stream);
+}
+
+int cg_set_option(int32_t option, int32_t value) {
+  switch (option) {
+    case CG_OPT_CULL: g_cull = value ? 1 : 0; return CG_OK;
+    default: return fail(CG_EINVAL, "unknown option %d", option);
+  }
 }
 
 int cg_items_loglik(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs, int32_t n_src,
@@ -1461,7 +1838,7 @@ int cg_items_loglik(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs,
   pa.cnt = cnt; pa.out_boxes = d_boxes; pa.filters = g_d_filters;
   RenderArgs ra;
   memset(&ra, 0, sizeof ra);
-  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.cnt = cnt;
+  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.worklist_cap = pa.worklist_cap; ra.cull = g_cull; ra.logtab = g_d_logtab; ra.cnt = cnt;
   ra.aux = d_aux; ra.aux_offsets = (const long long*)d_aux_offsets;
   ra.partials = (double*)(base + L.partials);
   if (use_fp64) {
@@ -1526,7 +1903,7 @@ int cg_score_proposals(CgImage* const* imgs, int32_t n_img, const CgSource* d_sr
   if (rc) return rc;
   RenderArgs ra;
   memset(&ra, 0, sizeof ra);
-  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.cnt = cnt;
+  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.worklist_cap = pa.worklist_cap; ra.cull = g_cull; ra.logtab = g_d_logtab; ra.cnt = cnt;
   ra.aux = d_bg; ra.aux_offsets = d_off; ra.partials = (double*)(base + L.partials);
   rc = run_render<float, MODE_POISSON>(ra, n_items, st);
   if (rc) return rc;
@@ -1551,7 +1928,7 @@ int cg_score_proposals(CgImage* const* imgs, int32_t n_img, const CgSource* d_sr
     rc = run_prepare<double>(p2, st);
     if (rc) return rc;
     RenderArgs r2 = ra;
-    r2.hdr = p2.hdr; r2.tab = p2.tab; r2.worklist = p2.worklist; r2.cnt = cnt2;
+    r2.hdr = p2.hdr; r2.tab = p2.tab; r2.worklist = p2.worklist; r2.worklist_cap = p2.worklist_cap; r2.cnt = cnt2;
     r2.partials = (double*)(base + L.partials2);
     rc = run_render<double, MODE_POISSON>(r2, L.n_items2, st);
     if (rc) return rc;

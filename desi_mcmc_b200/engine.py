@@ -79,6 +79,16 @@ def last_eval_count() -> int:
     return n
 
 
+def last_issued_count() -> int:
+    """lane-evaluations the render kernel issued for the last call (after
+    component culling, idle lanes of a warp included)."""
+    return int(lib().cg_last_issued_count(stream_ptr()))
+
+
+def set_option(option: int, value: int) -> None:
+    check(lib().cg_set_option(int(option), int(value)))
+
+
 def profile_render(enable: bool) -> None:
     """Start (and reset) / stop per-launch CUDA-event timing of render_kernel."""
     check(lib().cg_profile_render(1 if enable else 0))
@@ -476,6 +486,79 @@ def field_loglik(images: Sequence[Image], srcs, bound_cap: float = 0.0,
     if sync:
         last_eval_count()
     return (ll, models) if return_model else ll
+
+
+class FieldSet(object):
+    """A batch of independent fields (models.py:75-79 loops the fields of a
+    CelesteBase) scored by ONE cg_fields_loglik call: one prepare, one render
+    and one gather launch for all of them.  Buffers are allocated once.
+
+    fields: list of (images, n_src_max).  loglik() takes, per field, either a
+    device byte tensor of packed CgSource or a host CgSource array (copied
+    through a pinned stage -- the per-step host->device traffic)."""
+
+    def __init__(self, image_lists: Sequence[Sequence[Image]], n_src_max: Sequence[int],
+                 bound_cap: float = 0.0, max_patch_px: int | None = None):
+        self.L = lib()
+        self.fields = [list(imgs) for imgs in image_lists]
+        F = len(self.fields)
+        if F < 1 or F > _ffi.CG_MAX_FIELDS:
+            raise ValueError("between 1 and %d fields per set" % _ffi.CG_MAX_FIELDS)
+        flat = [im for imgs in self.fields for im in imgs]
+        self.harr, self.n_img = _handles(flat)
+        self.img_off = np.zeros(F + 1, dtype=np.int32)
+        self.img_off[1:] = np.cumsum([len(f) for f in self.fields])
+        self.n_src_max = np.asarray(n_src_max, dtype=np.int64)
+        self.cap_off = np.zeros(F + 1, dtype=np.int64)
+        self.cap_off[1:] = np.cumsum(self.n_src_max)
+        self.bound_cap = float(bound_cap)
+        if max_patch_px is None:
+            side = int(2 * bound_cap + 3) if bound_cap > 0 else 203
+            max_patch_px = side * side
+        self.max_patch_px = int(max_patch_px)
+        n_items = int(sum(int(n) * len(f) for n, f in zip(self.n_src_max, self.fields)))
+        tiles = self.n_img * max(int(self.L.cg_field_tiles(im.shape[0], im.shape[1])) for im in flat)
+        need = int(self.L.cg_workspace_bytes(_ffi.CG_WS_FIELD, max(n_items, 1), self.n_img,
+                                             self.max_patch_px, tiles))
+        self.ws = torch.empty(need, dtype=torch.uint8, device=device())
+        nb = int(self.cap_off[-1]) * SRC_DTYPE.itemsize
+        self.d_srcs = torch.zeros(max(nb, 1), dtype=torch.uint8, device=device())
+        self.h_srcs = torch.zeros(max(nb, 1), dtype=torch.uint8).pin_memory()
+        self.h_np = self.h_srcs.numpy()
+        self.ll = torch.zeros(self.n_img, dtype=torch.float64, device=device())
+        self.h_ll = torch.zeros(self.n_img, dtype=torch.float64).pin_memory()
+        self.src_off = np.zeros(F + 1, dtype=np.int32)
+
+    def set_sources(self, per_field: Sequence[np.ndarray]) -> int:
+        """Host CgSource arrays -> pinned stage -> device (async); returns bytes copied."""
+        o = 0
+        for f, arr in enumerate(per_field):
+            n = arr.shape[0]
+            if n > self.n_src_max[f]:
+                raise ValueError("field %d: more sources than n_src_max" % f)
+            raw = arr.view(np.uint8).reshape(-1)
+            self.h_np[o:o + raw.size] = raw
+            self.src_off[f] = o // SRC_DTYPE.itemsize
+            o += raw.size
+        self.src_off[len(per_field)] = o // SRC_DTYPE.itemsize
+        self.d_srcs[:o].copy_(self.h_srcs[:o], non_blocking=True)
+        return o
+
+    def loglik_device(self) -> torch.Tensor:
+        """Sources already resident (set_sources called before); nothing synchronises."""
+        check(self.L.cg_fields_loglik(self.harr, self.img_off.ctypes.data, self.d_srcs.data_ptr(),
+                                      self.src_off.ctypes.data, len(self.fields), self.bound_cap,
+                                      self.max_patch_px, self.ll.data_ptr(), None,
+                                      self.ws.data_ptr(), self.ws.numel(), stream_ptr()))
+        return self.ll
+
+    def loglik(self, per_field: Sequence[np.ndarray]) -> np.ndarray:
+        """End to end: host source arrays in, per-image log-likelihoods (host) out."""
+        self.set_sources(per_field)
+        self.loglik_device()
+        self.h_ll.copy_(self.ll, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return self.h_ll.numpy()
 
 
 def items_loglik(images: Sequence[Image], srcs, items: np.ndarray, mode: int = CG_LL_POISSON_BG,

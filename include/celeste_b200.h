@@ -194,6 +194,23 @@ int cg_field_loglik(CgImage* const* imgs, int32_t n_img,
                     double* d_ll, float* const* h_d_model,
                     void* d_workspace, size_t workspace_bytes, void* stream);
 
+/* Batch of independent fields (models.py:75-79 loops the fields of a
+ * CelesteBase): field f owns images [h_img_off[f], h_img_off[f+1]) of imgs[]
+ * and sources [h_src_off[f], h_src_off[f+1]) of d_srcs; n_fields <= 16 and
+ * h_img_off[n_fields] <= CG_MAX_IMAGES.  d_ll[h_img_off[n_fields]] receives
+ * the per-image log-likelihoods; one prepare / render / gather launch each. */
+int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off,
+                     const CgSource* d_srcs, const int32_t* h_src_off, int32_t n_fields,
+                     double bound_cap, int64_t max_patch_px,
+                     double* d_ll, float* const* h_d_model,
+                     void* d_workspace, size_t workspace_bytes, void* stream);
+
+/* Library options.  CG_OPT_CULL (default 1): per-warp skipping of mixture
+ * components whose largest value over the warp's pixels is below 2^-27 of a
+ * lower bound of the mixture there (bounded relative error K*2^-27 on a rate). */
+#define CG_OPT_CULL 1
+int cg_set_option(int32_t option, int32_t value);
+
 /* Likelihood modes of cg_items_loglik */
 #define CG_LL_POISSON_BG 0  /* sources.py:6-12 with model = aux + rate, data = nelec crop, mask = image mask
                                (aux < 0: background = epsilon; sources.py:188-237) */
@@ -252,6 +269,9 @@ int64_t cg_launch_count(int reset);
  * cg_render_patches / cg_items_loglik / cg_score_proposals call: reads a
  * device counter, synchronises `stream`. */
 int64_t cg_last_eval_count(void* stream);
+/* Lane-evaluations the render kernel actually issued for that call (after
+ * component culling; counted per warp, idle lanes included). */
+int64_t cg_last_issued_count(void* stream);
 
 /* CUDA-event timing of every render_kernel launch (bench.py's roofline leg):
  * enable resets the record; read synchronises on the recorded events. */

@@ -251,3 +251,70 @@ def test_planck_star_render(engine, oracle):
     for i, img in enumerate(oimgs):
         want = oracle.celeste_likelihood(osrcs, img)
         assert abs(ll[i] - want) <= LL_RTOL * abs(want)
+
+
+def test_fields_batch_matches_single_calls(engine, oracle):
+    """cg_fields_loglik over three unequal fields == three cg_field_loglik calls
+    (bitwise: the gather sums sources in source order) and == the oracle."""
+    specs = [(81, 150, 170, 9), (82, 96, 200, 0), (83, 130, 131, 14)]
+    fields = [synth.make_field(sd, H=h, W=w, n_src=n, star_frac=.5) for sd, h, w, n in specs]
+    gimgs, packed, single = [], [], []
+    for fld in fields:
+        nelec = hp.simulate_nelec(oracle, fld, fld["seed"])
+        gi = hp.gpu_images(engine, fld, nelec)
+        pk = engine.pack_sources(hp.gpu_sources(engine, fld))
+        gimgs.append(gi)
+        packed.append(pk)
+        single.append(engine.field_loglik(gi, pk).cpu().numpy())
+    fs = engine.FieldSet(gimgs, [max(1, p.shape[0]) for p in packed])
+    got = fs.loglik(packed).copy()
+    assert np.array_equal(got, np.concatenate(single))
+    fld = fields[2]
+    oimgs = hp.oracle_images(oracle, fld, [im.nelec.cpu().numpy().astype(np.float64) for im in gimgs[2]])
+    osrcs = hp.oracle_sources(oracle, fld)
+    for b, img in enumerate(oimgs):
+        want = oracle.celeste_likelihood(osrcs, img)
+        assert abs(got[10 + b] - want) <= LL_RTOL * abs(want)
+
+
+def test_component_culling_error_bound(engine):
+    """Per-warp component culling changes a rate by at most K * 2^-27 relative."""
+    from desi_mcmc_b200 import _ffi
+    field = synth.make_field(84, H=220, W=260, n_src=12, star_frac=.3)
+    zeros = [np.zeros((220, 260))] * 5
+    gimgs = hp.gpu_images(engine, field, zeros)
+    gs = hp.gpu_sources(engine, field)
+    try:
+        engine.set_option(_ffi.CG_OPT_CULL, 0)
+        full, boxes = engine.render_patches(gimgs, gs)
+        issued_full = engine.last_issued_count()
+        engine.set_option(_ffi.CG_OPT_CULL, 1)
+        culled, boxes2 = engine.render_patches(gimgs, gs)
+        issued_cull = engine.last_issued_count()
+    finally:
+        engine.set_option(_ffi.CG_OPT_CULL, 1)
+    assert np.array_equal(boxes, boxes2)
+    full, culled = full.cpu().numpy().astype(np.float64), culled.cpu().numpy().astype(np.float64)
+    assert np.all(culled <= full * (1 + 1e-6))
+    nz = full > 0
+    rel = np.max((full[nz] - culled[nz]) / full[nz])
+    print("culling: max relative deficit %.3g, issued %.3g -> %.3g lane-evals" % (rel, issued_full, issued_cull))
+    assert rel <= 42 * 2.0 ** -27 + 2.5e-7          # + fp32 summation-order slack
+    assert issued_cull < issued_full
+
+
+def test_field_loglik_crowded_tile_overflow(engine, oracle):
+    """More sources over one 64x16 image tile than a tile list holds (48): the
+    gather falls back to scanning all sources; result still matches the oracle."""
+    field = synth.make_field(85, H=72, W=96, n_src=70, star_frac=.9, margin=30)
+    nelec = hp.simulate_nelec(oracle, field, 6)
+    gimgs = hp.gpu_images(engine, field, nelec)
+    oimgs = hp.oracle_images(oracle, field, nelec)
+    ll, models = engine.field_loglik(gimgs, hp.gpu_sources(engine, field), return_model=True)
+    ll = ll.cpu().numpy()
+    osrcs = hp.oracle_sources(oracle, field)
+    for i, img in enumerate(oimgs):
+        lam = oracle.gen_model_image(osrcs, img)
+        assert hp.rel_err(models[i].cpu().numpy(), lam, 1.0) < RATE_RTOL
+        want = oracle.celeste_likelihood(osrcs, img)
+        assert abs(ll[i] - want) <= LL_RTOL * abs(want)
