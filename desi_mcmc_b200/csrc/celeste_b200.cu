@@ -144,7 +144,7 @@ struct ItemHdr {
   int ox, oy;          // local origin (pixel nearest the source centre)
   int K;               // components (0: renders nothing)
   int img;
-  int strip_start, n_strips;
+  int strip_start, n_strips;   // first partial-sum slot / number of warp tiles
   int aux;
   int flags;
   double flux;         // rate multiplier (1 for unit-flux patches)
@@ -172,16 +172,21 @@ struct Counters {
 //   sl = log2(e) / (2 lambda_min(Sigma)) (steepest log2 drop per squared pixel).
 #define TAB_W 12
 #define TAB_STRIDE (CG_MAX_COMP * TAB_W)
-// the render kernel takes work in units of up to UNIT_STRIPS strips of one item
-#define UNIT_STRIPS 4
+
 #define STRIP_THREADS 256
 #define PIX_PER_THREAD 4
-#define STRIP_PIX (STRIP_THREADS * PIX_PER_THREAD)
-// A strip is 256 consecutive 4-pixel chunks of a footprint in TILE-MAJOR order
-// (tiles of TILE_CW chunks x TILE_R rows), so that the 32 chunks of a warp
-// form a compact block of pixels and whole components can be culled per warp.
+// Work decomposition of a footprint.  A LANE UNIT is two 4-pixel chunks in
+// the same columns of two rows of a 16-row tile band (rows r and r + R/2 of a
+// band of R rows); lane units are numbered in TILE-MAJOR order (tiles of
+// TILE_CW chunks x TILE_R row pairs = 16 x 16 pixels; edge tiles are narrower /
+// shorter and simply hold fewer units, so no lane is spent on padding tiles).
+// A WARP TILE is 32 consecutive lane units (256 pixels in a compact block, so
+// whole components can be culled for the warp); a work UNIT is up to UNIT_WT
+// consecutive warp tiles of one item and is processed by one warp.
 #define TILE_CW 4
 #define TILE_R 8
+#define WT_PIX (32 * 2 * PIX_PER_THREAD)
+#define UNIT_WT_MAX 8
 // a component is skipped for a warp when its largest value over the warp's
 // pixels is below 2^-CULL_T of a lower bound of the mixture there
 #define CULL_T 27.0f
@@ -220,6 +225,7 @@ struct PrepArgs {
   CgBox* out_boxes;         // optional
   const FilterTables* filters;
   // full-field path: per (image, 64x16 tile) list of the items that overlap it
+  int unit_wt;              // warp tiles per work unit (same value in RenderArgs)
   int* tile_count;          // [n_img][max_tiles] (NULL: no binning)
   int* tile_list;           // [n_img][max_tiles][TILE_LIST_CAP]
   int max_tiles;
@@ -522,8 +528,10 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
 
   const int wbox = x1 - x0, hbox = y1 - y0;
   const int cpr = (wbox + PIX_PER_THREAD - 1) / PIX_PER_THREAD;
-  const int n_strips = (int)(((long long)hbox * cpr + STRIP_THREADS - 1) / STRIP_THREADS);
-  const int n_units = (n_strips + UNIT_STRIPS - 1) / UNIT_STRIPS;
+  // row pairs: full 16-row bands hold 8, the last band ceil(rows / 2)
+  const int hp = (hbox / (2 * TILE_R)) * TILE_R + ((hbox % (2 * TILE_R)) + 1) / 2;
+  const int n_strips = (int)(((long long)hp * cpr + 31) / 32);               // warp tiles
+  const int n_units = (n_strips + a.unit_wt - 1) / a.unit_wt;
   const bool heavy = K > 4;
   int start = 0, wpos = 0;
   if (lane == 0) {
@@ -542,7 +550,7 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
   if (start + n_strips <= a.worklist_cap)
     for (int j = lane; j < n_units; j += 32) {
       const int slot = heavy ? (wpos + j) : (a.worklist_cap - 1 - (wpos + j));
-      a.worklist[slot] = make_int2((int)i, j * UNIT_STRIPS);   // (item, first strip of the unit)
+      a.worklist[slot] = make_int2((int)i, j * a.unit_wt);   // (item, first warp tile of the unit)
     }
   // bin the footprint into the image tiles it overlaps (full-field gather)
   if (a.tile_count && npx > 0 && K > 0) {
@@ -593,6 +601,7 @@ struct RenderArgs {
   const long long* aux_offsets;
   double* partials;           // one per strip
   int cull;                   // 0 disables component culling
+  int unit_wt;                // warp tiles per work unit
   const LogTable* logtab;
 };
 
@@ -605,21 +614,23 @@ __device__ __forceinline__ int fast_div(int q, int d, float rd) {
   return t;
 }
 
-// Chunk q of a (w x h) footprint in tile-major order -> (row, first column).
-// Tiles are TILE_CW chunks x TILE_R rows; edge tiles are narrower / shorter
-// and simply hold fewer chunks, so no lane is spent on padding tiles.
-__device__ __forceinline__ void chunk_decode(int q, int cpr, int hbox, float r_trow, int* row, int* cx) {
-  const int trow_chunks = cpr * TILE_R;
-  const int tr = fast_div(q, trow_chunks, r_trow);
-  const int rem = q - tr * trow_chunks;
-  const int R = min(TILE_R, hbox - tr * TILE_R);
+// Lane unit q of a (w x h) footprint in tile-major order -> rows (row0, row1)
+// and first column.  hp = number of row pairs (prepare_kernel), bands of
+// TILE_R row pairs = 2*TILE_R rows.  row1 >= hbox means the unit has one row.
+__device__ __forceinline__ void unit_decode(int q, int cpr, int hp, float r_band, int* row0,
+                                            int* row1, int* cx) {
+  const int band_units = cpr * TILE_R;
+  const int tr = fast_div(q, band_units, r_band);
+  const int rem = q - tr * band_units;
+  const int R = min(TILE_R, hp - tr * TILE_R);          // row pairs in this band
   const int ft = TILE_CW * R;
   const int tc = fast_div(rem, ft, __frcp_rn((float)ft));
   const int rem2 = rem - tc * ft;
   const int tw = min(TILE_CW, cpr - tc * TILE_CW);
   const int r = (tw == TILE_CW) ? (rem2 / TILE_CW) : fast_div(rem2, tw, __frcp_rn((float)tw));
   const int c = rem2 - r * tw;
-  *row = tr * TILE_R + r;
+  *row0 = tr * (2 * TILE_R) + r;
+  *row1 = *row0 + R;
   *cx = (tc * TILE_CW + c) * PIX_PER_THREAD;
 }
 
@@ -683,73 +694,77 @@ __device__ __forceinline__ int cull_components(const float* s_tab, int K, int la
 
 template <typename real, int MODE>
 __global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
-  __shared__ __align__(16) real s_tab[TAB_STRIDE];
-  __shared__ __align__(16) float s_wtab[(sizeof(real) == 4) ? (STRIP_THREADS / 32) * CG_MAX_COMP * 8 : 4];
-  __shared__ int s_work;
-  __shared__ double s_red[STRIP_THREADS / 32];
+  // per-warp staging: the item's component table and the culled, compacted table
+  __shared__ __align__(16) real s_tab_all[(STRIP_THREADS / 32) * TAB_STRIDE];
+  __shared__ __align__(16) float s_wtab_all[(sizeof(real) == 4) ? (STRIP_THREADS / 32) * CG_MAX_COMP * 8 : 4];
   const LogTable* const logt = a.logtab;
-  const int tid = threadIdx.x, lane = tid & 31;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  real* const s_tab = s_tab_all + warp * TAB_STRIDE;
+  float* const s_wtab = s_wtab_all + ((sizeof(real) == 4) ? warp * CG_MAX_COMP * 8 : 0);
   const int n_heavy = *((volatile int*)&a.cnt->heavy_strips);
   const int total = n_heavy + *((volatile int*)&a.cnt->light_strips);
   unsigned long long issued = 0;
 
-  if (tid == 0) s_work = atomicAdd(&a.cnt->work_counter, 1);
-  __syncthreads();
-  for (;;) {
-    const int wk = s_work;
-    if (wk >= total) break;
+  int wk = 0;
+  if (lane == 0) wk = atomicAdd(&a.cnt->work_counter, 1);
+  wk = __shfl_sync(0xffffffffu, wk, 0);
+  while (wk < total) {
     const int slot = (wk < n_heavy) ? wk : (a.worklist_cap - 1 - (wk - n_heavy));
     const int2 w = a.worklist[slot];
-    const int item = w.x, strip0 = w.y;
-    const ItemHdr h = a.hdr[item];
-    {
-      const real* gtab = reinterpret_cast<const real*>(a.tab) + (long long)item * TAB_STRIDE;
-      for (int t = tid; t < h.K * TAB_W; t += STRIP_THREADS) s_tab[t] = gtab[t];
-    }
-    __syncthreads();              // table staged; every thread has read s_work
+    const int item = w.x, wt0 = w.y;
     int nxt = 0;
-    if (tid == 0) nxt = atomicAdd(&a.cnt->work_counter, 1);   // in flight during the unit
+    if (lane == 0) nxt = atomicAdd(&a.cnt->work_counter, 1);     // in flight during the unit
+    const ItemHdr h = a.hdr[item];
+    __syncwarp();                 // the warp is done with the tables of its previous unit
+    {
+      const float4* g4 = reinterpret_cast<const float4*>(reinterpret_cast<const real*>(a.tab) +
+                                                          (long long)item * TAB_STRIDE);
+      float4* s4 = reinterpret_cast<float4*>(s_tab);
+      const int n4 = h.K * TAB_W * (int)sizeof(real) / 16;
+      for (int t = lane; t < n4; t += 32) s4[t] = g4[t];
+    }
+    __syncwarp();
 
     const int wbox = h.x1 - h.x0, hbox = h.y1 - h.y0;
     const int cpr = (wbox + PIX_PER_THREAD - 1) / PIX_PER_THREAD;
-    const int n_chunks = cpr * hbox;
-    const float r_trow = __frcp_rn((float)(cpr * TILE_R));
-    const int strip_end = min(strip0 + UNIT_STRIPS, h.n_strips);
+    const int hp = (hbox / (2 * TILE_R)) * TILE_R + ((hbox % (2 * TILE_R)) + 1) / 2;
+    const int n_lu = cpr * hp;
+    const float r_band = __frcp_rn((float)(cpr * TILE_R));
+    const int wt_end = min(wt0 + a.unit_wt, h.n_strips);
     const DevImage* imp = (MODE != MODE_PATCH) ? a.imgs.p[h.img] : nullptr;
     const real fl = (real)h.flux;
 
 #pragma unroll 1
-    for (int strip = strip0; strip < strip_end; ++strip) {
-      const int q = strip * STRIP_THREADS + tid;
-      const bool active = q < n_chunks;
-      int row = 0, cx = 0;
-      if (active) chunk_decode(q, cpr, hbox, r_trow, &row, &cx);
+    for (int wt = wt0; wt < wt_end; ++wt) {
+      const int q = wt * 32 + lane;
+      const bool active = q < n_lu;
+      int row0 = 0, row1 = 0, cx = 0;
+      if (active) unit_decode(q, cpr, hp, r_band, &row0, &row1, &cx);
+      const bool two = active && row1 < hbox;
       const int npx = active ? min(PIX_PER_THREAD, wbox - cx) : 0;
 
-      real acc[PIX_PER_THREAD];
-#pragma unroll
-      for (int p = 0; p < PIX_PER_THREAD; ++p) acc[p] = (real)0;
+      int n = h.K;
+      const real* tb = s_tab;
+      int stride = TAB_W;
+      if (sizeof(real) == 4 && a.cull && n > 1) {
+        const int rmin = __reduce_min_sync(0xffffffffu, active ? row0 : 0x7fffffff);
+        const int rmax = __reduce_max_sync(0xffffffffu, active ? (two ? row1 : row0) : -1);
+        const int cmin = __reduce_min_sync(0xffffffffu, active ? cx : 0x7fffffff);
+        const int cmax = __reduce_max_sync(0xffffffffu, active ? cx + npx - 1 : -1);
+        __syncwarp();             // the warp is done reading the culled table of the previous tile
+        n = cull_components(reinterpret_cast<const float*>(s_tab), n, lane,
+                            (float)(h.x0 + cmin - h.ox), (float)(h.x0 + cmax - h.ox),
+                            (float)(h.y0 + rmin - h.oy), (float)(h.y0 + rmax - h.oy), s_wtab);
+        tb = reinterpret_cast<const real*>(s_wtab);
+        stride = 8;
+      }
+      if (lane == 0) issued += (unsigned long long)n * WT_PIX;
 
-      const unsigned act = __ballot_sync(0xffffffffu, active);
-      if (act) {                    // warp-uniform
-        int n = h.K;
-        const real* tb = s_tab;
-        int stride = TAB_W;
-        if (sizeof(real) == 4 && a.cull && n > 1) {
-          const int rmin = __reduce_min_sync(0xffffffffu, active ? row : 0x7fffffff);
-          const int rmax = __reduce_max_sync(0xffffffffu, active ? row : -1);
-          const int cmin = __reduce_min_sync(0xffffffffu, active ? cx : 0x7fffffff);
-          const int cmax = __reduce_max_sync(0xffffffffu, active ? cx + npx - 1 : -1);
-          float* wt = s_wtab + (tid >> 5) * (CG_MAX_COMP * 8);
-          __syncwarp();             // the warp is done reading its table of the previous strip
-          n = cull_components(reinterpret_cast<const float*>(s_tab), n, lane,
-                              (float)(h.x0 + cmin - h.ox), (float)(h.x0 + cmax - h.ox),
-                              (float)(h.y0 + rmin - h.oy), (float)(h.y0 + rmax - h.oy), wt);
-          tb = reinterpret_cast<const real*>(wt);
-          stride = 8;
-        }
-        if (lane == 0) issued += (unsigned long long)n * (32 * PIX_PER_THREAD);
-        const real yl = (real)(h.y0 + row - h.oy);
+      real acc0[PIX_PER_THREAD], acc1[PIX_PER_THREAD];
+#pragma unroll
+      for (int p = 0; p < PIX_PER_THREAD; ++p) { acc0[p] = (real)0; acc1[p] = (real)0; }
+      {
+        const real y0l = (real)(h.y0 + row0 - h.oy), y1l = (real)(h.y0 + row1 - h.oy);
         const real xl0 = (real)(h.x0 + cx - h.ox);
         real xl[PIX_PER_THREAD];
 #pragma unroll
@@ -757,67 +772,63 @@ __global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
 #pragma unroll 2
         for (int k = 0; k < n; ++k, tb += stride) {
           const real A = tb[0], B = tb[1], C = tb[2], b10 = tb[3], c01 = tb[4], c00 = tb[5];
-          const real b1 = rfma(B, yl, b10);
-          const real c1 = rfma(rfma(C, yl, c01), yl, c00);
+          const real b1a = rfma(B, y0l, b10), b1b = rfma(B, y1l, b10);
+          const real c1a = rfma(rfma(C, y0l, c01), y0l, c00);
+          const real c1b = rfma(rfma(C, y1l, c01), y1l, c00);
 #pragma unroll
           for (int p = 0; p < PIX_PER_THREAD; ++p) {
-            const real arg = rfma(rfma(A, xl[p], b1), xl[p], c1);
-            acc[p] += rexp2(arg);
+            acc0[p] += rexp2(rfma(rfma(A, xl[p], b1a), xl[p], c1a));
+            acc1[p] += rexp2(rfma(rfma(A, xl[p], b1b), xl[p], c1b));
           }
         }
       }
 
       if (MODE == MODE_PATCH) {
         if (active) {
-          float* out = a.patches + (long long)item * a.max_patch_px + (long long)row * wbox + cx;
+          float* out = a.patches + (long long)item * a.max_patch_px + (long long)row0 * wbox + cx;
 #pragma unroll
           for (int p = 0; p < PIX_PER_THREAD; ++p)
-            if (p < npx) out[p] = (float)(acc[p] * fl);
+            if (p < npx) out[p] = (float)(acc0[p] * fl);
+          if (two) {
+            out += (long long)(row1 - row0) * wbox;
+#pragma unroll
+            for (int p = 0; p < PIX_PER_THREAD; ++p)
+              if (p < npx) out[p] = (float)(acc1[p] * fl);
+          }
         }
       } else {
         double s = 0.0;
         if (active) {
           const DevImage& im = *imp;
-          const long long poff = (long long)row * wbox + cx;
-          const float* auxp = (h.aux >= 0) ? a.aux + a.aux_offsets[h.aux] + poff : nullptr;
-          if (MODE == MODE_POISSON) {
-            const float* data = im.nelec + (long long)(h.y0 + row) * im.W + (h.x0 + cx);
-            const float* mask = (im.mask && !(h.flags & CG_ITEM_NO_MASK))
-                                    ? im.mask + (long long)(h.y0 + row) * im.W + (h.x0 + cx) : nullptr;
-            const real eps = (real)im.epsilon;
+          const real eps = (real)im.epsilon;
+          const bool use_mask = im.mask && !(h.flags & CG_ITEM_NO_MASK);
+#pragma unroll
+          for (int rr = 0; rr < 2; ++rr) {
+            if (rr == 1 && !two) break;
+            const int row = rr ? row1 : row0;
+            const long long poff = (long long)row * wbox + cx;
+            const float* auxp = (h.aux >= 0) ? a.aux + a.aux_offsets[h.aux] + poff : nullptr;
+            const long long ioff = (long long)(h.y0 + row) * im.W + (h.x0 + cx);
 #pragma unroll
             for (int p = 0; p < PIX_PER_THREAD; ++p) {
               if (p < npx) {
-                const real bg = auxp ? (real)auxp[p] : eps;
-                const real lam = bg + fl * acc[p];
-                const bool good = (lam > (real)0) && (!mask || mask[p] != 0.f);
-                if (good) s += (double)data[p] * log_accurate(lam, logt) - (double)lam;
-              }
-            }
-          } else {  // MODE_COND, sources.py:171-174
-#pragma unroll
-            for (int p = 0; p < PIX_PER_THREAD; ++p) {
-              if (p < npx) {
-                const real m = fl * acc[p];
-                if (m >= (real)1.17549435e-38f) s += log_accurate(m, logt) * (double)auxp[p];
+                const real v = fl * (rr ? acc1[p] : acc0[p]);
+                if (MODE == MODE_POISSON) {
+                  const real lam = (auxp ? (real)auxp[p] : eps) + v;
+                  const bool good = (lam > (real)0) && (!use_mask || im.mask[ioff + p] != 0.f);
+                  if (good) s += (double)im.nelec[ioff + p] * log_accurate(lam, logt) - (double)lam;
+                } else {      // MODE_COND, sources.py:171-174
+                  if (v >= (real)1.17549435e-38f) s += log_accurate(v, logt) * (double)auxp[p];
+                }
               }
             }
           }
         }
         s = warp_sum(s);
-        __syncthreads();            // s_red of the previous strip has been consumed
-        if (lane == 0) s_red[tid >> 5] = s;
-        __syncthreads();
-        if (tid == 0) {
-          double t = 0;
-#pragma unroll
-          for (int wv = 0; wv < STRIP_THREADS / 32; ++wv) t += s_red[wv];
-          a.partials[h.strip_start + strip] = t;
-        }
+        if (lane == 0) a.partials[h.strip_start + wt] = s;
       }
     }
-    if (tid == 0) s_work = nxt;
-    __syncthreads();
+    wk = __shfl_sync(0xffffffffu, nxt, 0);
   }
   if (lane == 0 && issued) atomicAdd(&a.cnt->issued, issued);
 }
@@ -881,7 +892,7 @@ __device__ __forceinline__ void gather_patch(float (&lam)[4][4], const float* pa
   }
 }
 
-__global__ void __launch_bounds__(FR_WARPS * 32) field_reduce_kernel(FieldArgs a) {
+__global__ void __launch_bounds__(FR_WARPS * 32, 8) field_reduce_kernel(FieldArgs a) {
   const int img = blockIdx.y;
   const DevImage& im = *a.imgs.p[img];
   const int H = im.H, W = im.W;
@@ -892,7 +903,6 @@ __global__ void __launch_bounds__(FR_WARPS * 32) field_reduce_kernel(FieldArgs a
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
   __shared__ double s_red[FR_WARPS];
-  __shared__ int s_last;
   const LogTable* const logt = a.logtab;
 
   const int ht = blockIdx.x * FR_WARPS + warp;      // half-tile index
@@ -1040,25 +1050,27 @@ __global__ void __launch_bounds__(FR_WARPS * 32) field_reduce_kernel(FieldArgs a
 #pragma unroll
     for (int wv = 0; wv < FR_WARPS; ++wv) t += s_red[wv];
     a.block_partials[(long long)img * a.blocks_per_img + blockIdx.x] = t;
-    __threadfence();
-    s_last = (atomicAdd(&a.done[img], 1) == n_blocks - 1);
   }
+}
+
+// one block per image: fixed-shape tree over the block partials (a separate
+// launch is cheaper than a fence + atomic in every gather block)
+__global__ void __launch_bounds__(256) field_final_kernel(FieldArgs a) {
+  const int img = blockIdx.x;
+  const DevImage& im = *a.imgs.p[img];
+  const int n_tiles = ((im.W + TILE_W - 1) / TILE_W) * ((im.H + TILE_H - 1) / TILE_H);
+  const int n_blocks = (2 * n_tiles + FR_WARPS - 1) / FR_WARPS;
+  __shared__ double s_fin[256];
+  double t = 0;
+  const double* bp = a.block_partials + (long long)img * a.blocks_per_img;
+  for (int i = threadIdx.x; i < n_blocks; i += 256) t += bp[i];
+  s_fin[threadIdx.x] = t;
   __syncthreads();
-  if (s_last) {
-    // the last block of the image sums the block partials in a fixed tree
-    __threadfence();
-    __shared__ double s_fin[FR_WARPS * 32];
-    double t = 0;
-    const volatile double* bp = a.block_partials + (long long)img * a.blocks_per_img;
-    for (int i = tid; i < n_blocks; i += FR_WARPS * 32) t += bp[i];
-    s_fin[tid] = t;
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) s_fin[threadIdx.x] += s_fin[threadIdx.x + o];
     __syncthreads();
-    for (int o = FR_WARPS * 16; o > 0; o >>= 1) {
-      if (tid < o) s_fin[tid] += s_fin[tid + o];
-      __syncthreads();
-    }
-    if (tid == 0) { a.ll[img] = s_fin[0]; a.done[img] = 0; }
   }
+  if (threadIdx.x == 0) a.ll[img] = s_fin[0];
 }
 
 // ---------------------------------------------------------------------------
@@ -1312,7 +1324,7 @@ static WsLayout ws_layout(long long n_items, long long max_patch_px, int with_pa
   memset(&L, 0, sizeof L);
   size_t o = 0;
   auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes, 256); return r; };
-  long long strips_per_item = (max_patch_px + STRIP_PIX - 1) / STRIP_PIX + 64;
+  long long strips_per_item = (max_patch_px + WT_PIX - 1) / WT_PIX + 64;   // warp tiles
   // rows whose width is not a multiple of 8 waste chunk slots: bound chunks by px/8 + rows
   long long cap = n_items * strips_per_item;
   if (cap > 0x7fffffffLL) cap = 0x7fffffffLL;
@@ -1656,9 +1668,19 @@ static int render_grid() {
   return g_sm_count * per_sm;
 }
 
+// warp tiles per work unit: coarse units amortise the table staging, fine ones
+// balance a small launch over the resident warps
+static int choose_unit_wt(long long n_items) {
+  const long long warps = (long long)g_sm_count * 32;
+  long long u = (n_items * 16) / (warps * 8);
+  return (int)std::min<long long>(std::max<long long>(u, 1), UNIT_WT_MAX);
+}
+
 template <typename real>
-static int run_prepare(const PrepArgs& pa, cudaStream_t st) {
-  if (pa.n_items == 0) return CG_OK;
+static int run_prepare(const PrepArgs& pa_in, cudaStream_t st) {
+  if (pa_in.n_items == 0) return CG_OK;
+  PrepArgs pa = pa_in;
+  pa.unit_wt = choose_unit_wt(pa.n_items);
   unsigned blocks = (unsigned)((pa.n_items + 3) / 4);
   prepare_kernel<real><<<blocks, 128, 0, st>>>(pa);
   LAUNCH_CHECK();
@@ -1666,8 +1688,10 @@ static int run_prepare(const PrepArgs& pa, cudaStream_t st) {
 }
 
 template <typename real, int MODE>
-static int run_render(const RenderArgs& ra, long long n_items, cudaStream_t st) {
+static int run_render(const RenderArgs& ra_in, long long n_items, cudaStream_t st) {
   if (n_items == 0) return CG_OK;
+  RenderArgs ra = ra_in;
+  ra.unit_wt = choose_unit_wt(n_items);
   const bool prof = g_prof_on && g_prof_n < PROF_MAX;
   if (prof) cudaEventRecord(g_prof_ev[2 * g_prof_n], st);
   render_kernel<real, MODE><<<render_grid<real, MODE>(), STRIP_THREADS, 0, st>>>(ra);
@@ -1787,6 +1811,8 @@ int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off, const CgSou
     }
   }
   field_reduce_kernel<<<dim3(blocks_per_img, n_img), FR_WARPS * 32, 0, st>>>(fa);
+  LAUNCH_CHECK();
+  field_final_kernel<<<n_img, 256, 0, st>>>(fa);
   LAUNCH_CHECK();
   g_last_counters = cnt;
   return CG_OK;
