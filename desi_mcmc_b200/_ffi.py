@@ -39,6 +39,7 @@ CG_WS_RENDER, CG_WS_FIELD, CG_WS_ITEMS, CG_WS_SCORE = 0, 1, 2, 3
 
 CG_LL_POISSON_BG = 0
 CG_LL_CONDITIONAL = 1
+CG_LL_CONDITIONAL_SUM = 2
 
 
 class CgImageDesc(C.Structure):
@@ -103,6 +104,7 @@ PROTOTYPES = {
                                   _vp, _vp, _i32, _vp, _sz, _vp]),
     "cg_score_proposals": (C.c_int, [_vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _dbl,
                                      _vp, _vp, _vp, _vp, _sz, _vp]),
+    "cg_poisson_loglike": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _vp]),
     "cg_planck_fluxes": (C.c_int, [_vp, _vp, _i64, _vp, _vp]),
     "cg_eigen_fluxes": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp]),
     "cg_launch_count": (_i64, [C.c_int]),

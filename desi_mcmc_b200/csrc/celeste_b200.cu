@@ -602,6 +602,7 @@ struct RenderArgs {
   double* partials;           // one per strip
   int cull;                   // 0 disables component culling
   int unit_wt;                // warp tiles per work unit
+  int cond_sum;               // MODE_COND: subtract the rendered rates (CG_LL_CONDITIONAL_SUM)
   const LogTable* logtab;
 };
 
@@ -819,6 +820,7 @@ __global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
                   if (good) s += (double)im.nelec[ioff + p] * log_accurate(lam, logt) - (double)lam;
                 } else {      // MODE_COND, sources.py:171-174
                   if (v >= (real)1.17549435e-38f) s += log_accurate(v, logt) * (double)auxp[p];
+                  if (a.cond_sum) s -= (double)v;     // celeste_galaxy_conditionals.py:41
                 }
               }
             }
@@ -1257,6 +1259,40 @@ __global__ void __launch_bounds__(256) eigen_flux_kernel(const double* z, const 
     }
     if (fluxes && ll) ll[c] = isinf(m[c]) ? -INFINITY : -0.5 * l;
   }
+}
+
+// ---------------------------------------------------------------------------
+// sources.py:6-12 on arbitrary arrays (float64 in, float64 arithmetic)
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) poisson_partial_kernel(const double* data, const double* model,
+                                                               const double* mask, long long n,
+                                                               double* partials) {
+  double s = 0;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
+    const double m = model[i];
+    if (m > 0. && (!mask || mask[i] != 0.)) s += log(m) * data[i] - m;
+  }
+  __shared__ double s_red[8];
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0;
+    for (int w = 0; w < 8; ++w) t += s_red[w];
+    partials[blockIdx.x] = t;
+  }
+}
+__global__ void __launch_bounds__(256) sum_partials_kernel(const double* partials, int n, double* out) {
+  __shared__ double s_fin[256];
+  double t = 0;
+  for (int i = threadIdx.x; i < n; i += 256) t += partials[i];
+  s_fin[threadIdx.x] = t;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) s_fin[threadIdx.x] += s_fin[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *out = s_fin[0];
 }
 
 // ---------------------------------------------------------------------------
@@ -1841,9 +1877,10 @@ int cg_items_loglik(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs,
                     size_t ws_bytes, void* stream) {
   NEED_INIT();
   cudaStream_t st = (cudaStream_t)stream;
-  if (mode != CG_LL_POISSON_BG && mode != CG_LL_CONDITIONAL) return fail(CG_EINVAL, "unknown mode %d", mode);
+  if (mode != CG_LL_POISSON_BG && mode != CG_LL_CONDITIONAL && mode != CG_LL_CONDITIONAL_SUM)
+    return fail(CG_EINVAL, "unknown mode %d", mode);
   if (!d_items) return fail(CG_EINVAL, "d_items is required");
-  if (mode == CG_LL_CONDITIONAL && !d_aux) return fail(CG_EINVAL, "conditional mode needs photon patches");
+  if (mode != CG_LL_POISSON_BG && !d_aux) return fail(CG_EINVAL, "conditional mode needs photon patches");
   PrepArgs pa;
   memset(&pa, 0, sizeof pa);
   int rc = fill_imgs(imgs, n_img, &pa.imgs);
@@ -1867,6 +1904,7 @@ int cg_items_loglik(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs,
   ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.worklist_cap = pa.worklist_cap; ra.cull = g_cull; ra.logtab = g_d_logtab; ra.cnt = cnt;
   ra.aux = d_aux; ra.aux_offsets = (const long long*)d_aux_offsets;
   ra.partials = (double*)(base + L.partials);
+  ra.cond_sum = (mode == CG_LL_CONDITIONAL_SUM);
   if (use_fp64) {
     rc = run_prepare<double>(pa, st);
     if (rc) return rc;
@@ -1969,6 +2007,22 @@ int cg_score_proposals(CgImage* const* imgs, int32_t n_img, const CgSource* d_sr
   if (d_n_guard)
     CUDA_TRY(cudaMemcpyAsync(d_n_guard, &cnt->guard_count, sizeof(int), cudaMemcpyDeviceToDevice, st));
   g_last_counters = cnt;
+  return CG_OK;
+}
+
+// ---- sources.py:6-12 ---------------------------------------------------------------
+static double* g_scratch = nullptr;   // 1024 doubles of block partials
+int cg_poisson_loglike(const double* d_data, const double* d_model, const double* d_mask, int64_t n,
+                       double* d_out, void* stream) {
+  NEED_INIT();
+  if (n < 0) return fail(CG_EINVAL, "negative size");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!g_scratch) CUDA_TRY(cudaMalloc(&g_scratch, sizeof(double) * 1024));
+  int blocks = (int)std::min<long long>(1024, std::max<long long>(1, (n + 255) / 256));
+  poisson_partial_kernel<<<blocks, 256, 0, st>>>(d_data, d_model, d_mask, n, g_scratch);
+  LAUNCH_CHECK();
+  sum_partials_kernel<<<1, 256, 0, st>>>(g_scratch, blocks, d_out);
+  LAUNCH_CHECK();
   return CG_OK;
 }
 

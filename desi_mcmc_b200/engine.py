@@ -190,7 +190,7 @@ def pack_sources(srcs: Sequence, out: np.ndarray | None = None) -> np.ndarray:
         r["u"] = s.u
         flags = 0
         if s.fluxes is not None:
-            r["flux"] = s.fluxes
+            r["flux"] = [s.fluxes[c] for c in BANDS] if isinstance(s.fluxes, dict) else s.fluxes
         if s.a == 0 and s.t:
             flags |= CG_SRC_PLANCK
             r["t"] = s.t
@@ -298,6 +298,44 @@ class Image(object):
 
     def nmgy2counts(self, flux):
         return (flux / self.calib) * self.kappa
+
+    def cd_at_pixel(self, x, y):
+        """fits_image.py:196-216: finite-difference CD matrix (10 px step)."""
+        ra0, dec0 = self.pixel2equa(np.array([x, y]))
+        step = 10.
+        rax, decx = self.pixel2equa(np.array([x + step, y]))
+        ray, decy = self.pixel2equa(np.array([x, y + step]))
+        cosd = np.cos(dec0 * (np.pi / 180.))
+        return np.array([[(rax - ra0) / step * cosd, (ray - ra0) / step * cosd],
+                         [(decx - dec0) / step, (decy - dec0) / step]])
+
+    def contains(self, s_equa, pad=50):
+        """fits_image.py:157-164."""
+        px, py = self.equa2pixel(s_equa)
+        return (px > -pad) and (px < self.shape[1] + pad) and (py > -pad) and (py < self.shape[0] + pad)
+
+    @property
+    def psf(self):
+        """fits_image.py:219-221: the PSF as a mixture-of-Gaussians object."""
+        if getattr(self, "_psf", None) is None:
+            from .compat.mog import MixtureOfGaussians
+            self._psf = MixtureOfGaussians(self.means, self.covars, self.weights)
+        return self._psf
+
+    @property
+    def invcovars(self):
+        return self.psf.icovs
+
+    @property
+    def logdets(self):
+        return np.log(self.psf.dets)
+
+    @property
+    def invvar(self):
+        """host copy of the mask (all ones when the image has none)."""
+        if self.d_mask is None:
+            return np.ones(self.shape)
+        return self.d_mask.cpu().numpy().astype(np.float64)
 
     def set_epsilon(self, epsilon: float):
         """Field.resample_photons re-draws epsilon every sweep (models.py:156-160)."""

@@ -215,6 +215,7 @@ int cg_set_option(int32_t option, int32_t value);
 #define CG_LL_POISSON_BG 0  /* sources.py:6-12 with model = aux + rate, data = nelec crop, mask = image mask
                                (aux < 0: background = epsilon; sources.py:188-237) */
 #define CG_LL_CONDITIONAL 1 /* sources.py:134-183: sum_{rate>0} log(rate)*z - band_flux*sum(psf_w); z = aux patch */
+#define CG_LL_CONDITIONAL_SUM 2 /* celeste_galaxy_conditionals.py:15-42: sum z*log(rate) - rate over the box */
 
 /* A13/A14/A15 building block: per-item log-likelihood over its box.  The aux
  * patch of item i (background or photon counts, float, box-shaped row-major)
@@ -245,6 +246,12 @@ int cg_score_proposals(CgImage* const* imgs, int32_t n_img,
                        double guard,
                        double* d_delta, uint8_t* d_accept, int32_t* d_n_guard,
                        void* d_workspace, size_t workspace_bytes, void* stream);
+
+/* sources.py:6-12 poisson_loglike(data, model_img, mask) on arbitrary device
+ * arrays (float64): sum over {model > 0 and mask != 0} of log(model)*data - model.
+ * d_mask may be NULL (all good).  d_out: one double. */
+int cg_poisson_loglike(const double* d_data, const double* d_model, const double* d_mask,
+                       int64_t n, double* d_out, void* stream);
 
 /* ---- A16: planck.py:94-158 ----------------------------------------------- */
 /* out[i*5+band] = photons_expected_brightness(T[i], b[i], band); float64. */
