@@ -1296,6 +1296,286 @@ __global__ void __launch_bounds__(256) sum_partials_kernel(const double* partial
 }
 
 // ---------------------------------------------------------------------------
+// N1: photon allocation (celeste_sample_sources.pyx:61-156)
+// ---------------------------------------------------------------------------
+// Counter-based generator (Philox-4x32, 10 rounds; Salmon et al. 2011): every
+// pixel owns the stream keyed by (seed, image, pixel), so the draws do not
+// depend on scheduling.  The reference consumes one MT19937 stream serially
+// over pixels; that order cannot be reproduced in parallel, so parity for this
+// row is distributional (tests: conservation, moments, chi-square vs the
+// binomial pmf), as SURVEY.md 8(f) N1 anticipates.
+struct Philox {
+  uint32_t key[2], ctr[4];
+  __device__ __forceinline__ void round_once(uint32_t k0, uint32_t k1) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, ctr[0]), lo0 = 0xD2511F53u * ctr[0];
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, ctr[2]), lo1 = 0xCD9E8D57u * ctr[2];
+    const uint32_t c0 = hi1 ^ ctr[1] ^ k0, c2 = hi0 ^ ctr[3] ^ k1;
+    ctr[0] = c0; ctr[1] = lo1; ctr[2] = c2; ctr[3] = lo0;
+  }
+  // uniform in (0, 1) with 53 random bits, from counter value (a, b, c, d)
+  __device__ __forceinline__ double uniform(uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    ctr[0] = a; ctr[1] = b; ctr[2] = c; ctr[3] = d;
+    uint32_t k0 = key[0], k1 = key[1];
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+      round_once(k0, k1);
+      k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    const unsigned long long bits = ((unsigned long long)(ctr[0] >> 5) << 26) | (ctr[1] >> 6);
+    return ((double)bits + 0.5) * (1.0 / 9007199254740992.0);
+  }
+};
+
+// One binomial(n, p) variate from ONE uniform by inversion (exact up to
+// float64 rounding of the pmf recurrences): from zero when n*min(p,q) is
+// small, else outwards from the mode (Kemp 1986), whose expected number of
+// steps is O(sqrt(n p q)).  deps/randomkit/distributions.c:239-449 switches
+// between inversion and BTPE rejection; both sample the same law.
+__device__ double binomial_from_uniform(long long n, double p, double U) {
+  if (n <= 0 || !(p > 0.)) return 0.;
+  if (p >= 1.) return (double)n;
+  const bool flip = p > 0.5;
+  const double pp = flip ? 1. - p : p, q = 1. - pp, r = pp / q;
+  const double dn = (double)n;
+  double X;
+  if (dn * pp < 12.) {
+    double px = exp(dn * log1p(-pp));
+    X = 0.;
+    while (U > px && X < dn) {
+      U -= px;
+      X += 1.;
+      px *= (dn - X + 1.) * r / X;
+      if (px <= 0.) break;
+    }
+  } else {
+    const double m = floor((dn + 1.) * pp);
+    const double fm = exp(lgamma(dn + 1.) - lgamma(m + 1.) - lgamma(dn - m + 1.) + m * log(pp) +
+                          (dn - m) * log1p(-pp));
+    X = m;
+    U -= fm;
+    if (U > 0.) {
+      double lo = m, hi = m, flo = fm, fhi = fm;
+      for (;;) {
+        bool moved = false;
+        if (hi < dn) {
+          fhi *= (dn - hi) / (hi + 1.) * r;
+          hi += 1.;
+          U -= fhi;
+          moved = true;
+          if (U <= 0.) { X = hi; break; }
+        }
+        if (lo > 0.) {
+          flo *= lo / (dn - lo + 1.) / r;
+          lo -= 1.;
+          U -= flo;
+          moved = true;
+          if (U <= 0.) { X = lo; break; }
+        }
+        if (!moved || (fhi <= 0. && flo <= 0.)) break;   // rounding residue: stay at the mode
+      }
+    }
+  }
+  return flip ? dn - X : X;
+}
+
+// instrumentation: count draws of binomial(n, p) for the sampler's unit test
+__global__ void binomial_test_kernel(long long n, double p, unsigned long long seed, long long count,
+                                     double* out) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  Philox g;
+  g.key[0] = (uint32_t)seed; g.key[1] = (uint32_t)(seed >> 32);
+  out[i] = binomial_from_uniform(n, p, g.uniform((uint32_t)i, (uint32_t)(i >> 32), 0u, 0x5eedu));
+}
+
+struct AllocArgs {
+  ImgPtrs imgs;
+  int n_img, n_src;
+  const CgBox* boxes;      // [n_src * n_img], item = src * n_img + img
+  const float* patches;    // rate patches, item-major, stride max_patch_px
+  float* samp;             // sampled photon patches, same layout (zeroed by the caller)
+  long long max_patch_px;
+  int* tile_count;         // [n_img][max_tiles]
+  int* tile_list;          // [n_img][max_tiles][TILE_LIST_CAP]
+  double* block_partials;  // [n_img][blocks_per_img]
+  double* noise_sum;       // [n_img]
+  int max_tiles, blocks_per_img;
+  unsigned long long seed;
+};
+
+// one warp per item: append the item to the list of every image tile its box overlaps
+__global__ void __launch_bounds__(128) bin_boxes_kernel(AllocArgs a) {
+  const int lane = threadIdx.x & 31;
+  const long long i = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (i >= (long long)a.n_src * a.n_img) return;
+  const int img = (int)(i % a.n_img);
+  const CgBox b = a.boxes[i];
+  if (b.x1 <= b.x0 || b.y1 <= b.y0) return;
+  const int W = a.imgs.p[img]->W;
+  const int tiles_x = (W + TILE_W - 1) / TILE_W;
+  const int txa = b.x0 / TILE_W, txb = (b.x1 - 1) / TILE_W;
+  const int tya = b.y0 / TILE_H, tyb = (b.y1 - 1) / TILE_H;
+  const int nx = txb - txa + 1, nt = nx * (tyb - tya + 1);
+  for (int j = lane; j < nt; j += 32) {
+    const int t = (tya + j / nx) * tiles_x + txa + (j % nx);
+    const long long slot = (long long)img * a.max_tiles + t;
+    const int pos = atomicAdd(&a.tile_count[slot], 1);
+    if (pos < TILE_LIST_CAP) a.tile_list[slot * TILE_LIST_CAP + pos] = (int)i;
+  }
+}
+
+// One warp per half image tile (64 x 8 pixels; lane = 4 pixels x 4 rows).
+// For every pixel: the sources whose box strictly contains it
+// (celeste_sample_sources.pyx:53-54: x > x0 and x < x1 and y > y0 and y < y1,
+// so the first row and column of a patch never receive photons), then the
+// multinomial split of int(nelec) over [rates..., epsilon] by conditional
+// binomials in source order (:127-156); the remainder is sky noise (:112).
+__global__ void __launch_bounds__(FR_WARPS * 32) sample_counts_kernel(AllocArgs a) {
+  const int img = blockIdx.y;
+  const DevImage& im = *a.imgs.p[img];
+  const int H = im.H, W = im.W;
+  const int tiles_x = (W + TILE_W - 1) / TILE_W, tiles_y = (H + TILE_H - 1) / TILE_H;
+  const int n_tiles = tiles_x * tiles_y;
+  const int n_blocks = (2 * n_tiles + FR_WARPS - 1) / FR_WARPS;
+  if ((int)blockIdx.x >= n_blocks) return;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  __shared__ int s_item[FR_WARPS][TILE_LIST_CAP];
+  __shared__ int4 s_box[FR_WARPS][TILE_LIST_CAP];
+  __shared__ double s_red[FR_WARPS];
+
+  const int ht = blockIdx.x * FR_WARPS + warp;
+  const int tile = ht >> 1;
+  double noise = 0.0;
+  if (tile < n_tiles) {
+    const int tx = tile % tiles_x, ty = tile / tiles_x;
+    const int X0 = tx * TILE_W, Y0 = ty * TILE_H + (ht & 1) * (TILE_H / 2);
+    const int x = X0 + (lane & 15) * 4, ybase = Y0 + (lane >> 4) * 4;
+    const long long tslot = (long long)img * a.max_tiles + tile;
+    const int cnt_raw = a.tile_count[tslot];
+    int cnt = 0;
+    // ordered (by item = source order) list of the boxes over this half tile
+    if (cnt_raw <= TILE_LIST_CAP) {
+      int it0 = 0x7fffffff, it1 = 0x7fffffff;
+      if (lane < cnt_raw) it0 = a.tile_list[tslot * TILE_LIST_CAP + lane];
+      if (lane + 32 < cnt_raw) it1 = a.tile_list[tslot * TILE_LIST_CAP + lane + 32];
+      int r0 = 0, r1 = 0;
+      for (int j = 0; j < min(cnt_raw, 32); ++j) {
+        const int v = __shfl_sync(0xffffffffu, it0, j);
+        r0 += (v < it0); r1 += (v < it1);
+      }
+      for (int j = 0; j < cnt_raw - 32; ++j) {
+        const int v = __shfl_sync(0xffffffffu, it1, j);
+        r0 += (v < it0); r1 += (v < it1);
+      }
+      if (lane < cnt_raw) {
+        s_item[warp][r0] = it0;
+        const CgBox b = a.boxes[it0];
+        s_box[warp][r0] = make_int4(b.x0, b.x1, b.y0, b.y1);
+      }
+      if (lane + 32 < cnt_raw) {
+        s_item[warp][r1] = it1;
+        const CgBox b = a.boxes[it1];
+        s_box[warp][r1] = make_int4(b.x0, b.x1, b.y0, b.y1);
+      }
+      cnt = cnt_raw;
+      __syncwarp();
+    }
+    const float eps = (float)im.epsilon;
+    Philox g;
+    g.key[0] = (uint32_t)a.seed; g.key[1] = (uint32_t)(a.seed >> 32);
+
+    for (int r = 0; r < 4; ++r) {
+      const int y = ybase + r;
+      if (y >= H) break;
+      for (int p = 0; p < 4; ++p) {
+        const int xx = x + p;
+        if (xx >= W) break;
+        const double nph = (double)im.nelec[(long long)y * W + xx];
+        // pass 1: total rate of the sources that own this pixel
+        double sum_probs = 0.;
+        int owners = 0;
+        if (cnt_raw <= TILE_LIST_CAP) {
+          for (int j = 0; j < cnt; ++j) {
+            const int4 b = s_box[warp][j];
+            if (xx > b.x && xx < b.y && y > b.z && y < b.w) {
+              sum_probs += (double)a.patches[(long long)s_item[warp][j] * a.max_patch_px +
+                                             (long long)(y - b.z) * (b.y - b.x) + (xx - b.x)];
+              ++owners;
+            }
+          }
+        } else {
+          for (int s = 0; s < a.n_src; ++s) {
+            const long long item = (long long)s * a.n_img + img;
+            const CgBox b = a.boxes[item];
+            if (xx > b.x0 && xx < b.x1 && y > b.y0 && y < b.y1) {
+              sum_probs += (double)a.patches[item * a.max_patch_px + (long long)(y - b.y0) * (b.x1 - b.x0) +
+                                             (xx - b.x0)];
+              ++owners;
+            }
+          }
+        }
+        if (owners == 0) { noise += nph; continue; }     // :94-96
+        sum_probs += (double)eps;
+        long long unsampled = (long long)nph;            // int(num_photons_xy), :110
+        const uint32_t pix = (uint32_t)((long long)y * W + xx);
+        int draw = 0;
+        // pass 2: conditional binomials in source order
+        const int n_scan = (cnt_raw <= TILE_LIST_CAP) ? cnt : a.n_src;
+        for (int j = 0; j < n_scan && unsampled > 0; ++j) {
+          long long item;
+          int4 b;
+          if (cnt_raw <= TILE_LIST_CAP) {
+            item = s_item[warp][j];
+            b = s_box[warp][j];
+          } else {
+            item = (long long)j * a.n_img + img;
+            const CgBox bb = a.boxes[item];
+            b = make_int4(bb.x0, bb.x1, bb.y0, bb.y1);
+          }
+          if (!(xx > b.x && xx < b.y && y > b.z && y < b.w)) continue;
+          const long long off = item * a.max_patch_px + (long long)(y - b.z) * (b.y - b.x) + (xx - b.x);
+          const double rate = (double)a.patches[off];
+          const double U = g.uniform(pix, (uint32_t)img, (uint32_t)draw++, 0xa110cu);
+          const double got = binomial_from_uniform(unsampled, rate / sum_probs, U);
+          a.samp[off] = (float)got;
+          unsampled -= (long long)got;
+          sum_probs -= rate;
+        }
+        noise += (double)unsampled;                      // samples[S-1] += unsampled, :155
+      }
+    }
+  }
+  noise = warp_sum(noise);
+  if (lane == 0) s_red[warp] = noise;
+  __syncthreads();
+  if (tid == 0) {
+    double t = 0;
+#pragma unroll
+    for (int wv = 0; wv < FR_WARPS; ++wv) t += s_red[wv];
+    a.block_partials[(long long)img * a.blocks_per_img + blockIdx.x] = t;
+  }
+}
+
+// per-image sum of the block partials (fixed order)
+__global__ void __launch_bounds__(256) alloc_final_kernel(AllocArgs a) {
+  const int img = blockIdx.x;
+  const DevImage& im = *a.imgs.p[img];
+  const int n_tiles = ((im.W + TILE_W - 1) / TILE_W) * ((im.H + TILE_H - 1) / TILE_H);
+  const int n_blocks = (2 * n_tiles + FR_WARPS - 1) / FR_WARPS;
+  __shared__ double s_fin[256];
+  double t = 0;
+  const double* bp = a.block_partials + (long long)img * a.blocks_per_img;
+  for (int i = threadIdx.x; i < n_blocks; i += 256) t += bp[i];
+  s_fin[threadIdx.x] = t;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) s_fin[threadIdx.x] += s_fin[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) a.noise_sum[img] = s_fin[0];
+}
+
+// ---------------------------------------------------------------------------
 // XU (MUFU.EX2) throughput probe: the roofline denominator of render_kernel,
 // measured on the device it runs on.  8 independent ex2 chains per thread.
 // ---------------------------------------------------------------------------
@@ -2022,6 +2302,68 @@ int cg_poisson_loglike(const double* d_data, const double* d_model, const double
   poisson_partial_kernel<<<blocks, 256, 0, st>>>(d_data, d_model, d_mask, n, g_scratch);
   LAUNCH_CHECK();
   sum_partials_kernel<<<1, 256, 0, st>>>(g_scratch, blocks, d_out);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
+// ---- N1: celeste_sample_sources.pyx:61-122 -------------------------------------
+size_t cg_alloc_workspace_bytes(int32_t n_img, int64_t n_tiles) {
+  size_t o = 0;
+  auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes, 256); return r; };
+  take(sizeof(int) * (size_t)n_tiles);                       // tile_count
+  take(sizeof(int) * (size_t)n_tiles * TILE_LIST_CAP);       // tile_list
+  take(sizeof(double) * (size_t)n_tiles);                    // block partials
+  (void)n_img;
+  return o + 256;
+}
+
+int cg_sample_source_counts(CgImage* const* imgs, int32_t n_img, int32_t n_src, const CgBox* d_boxes,
+                            const float* d_patches, int64_t max_patch_px, uint64_t seed,
+                            float* d_samp, double* d_noise_sum, void* d_ws, size_t ws_bytes,
+                            void* stream) {
+  NEED_INIT();
+  cudaStream_t st = (cudaStream_t)stream;
+  AllocArgs a;
+  memset(&a, 0, sizeof a);
+  int rc = fill_imgs(imgs, n_img, &a.imgs);
+  if (rc) return rc;
+  if (n_src < 0) return fail(CG_EINVAL, "negative n_src");
+  int max_tiles = 0;
+  for (int i = 0; i < n_img; ++i) {
+    max_tiles = std::max(max_tiles, (int)cg_field_tiles(imgs[i]->h.H, imgs[i]->h.W));
+    if (!imgs[i]->h.nelec) return fail(CG_EINVAL, "image %d has no nelec buffer", i);
+  }
+  const long long n_tiles = (long long)max_tiles * n_img;
+  if (cg_alloc_workspace_bytes(n_img, n_tiles) > ws_bytes)
+    return fail(CG_ENOMEM, "workspace too small: need %zu bytes, have %zu",
+                cg_alloc_workspace_bytes(n_img, n_tiles), ws_bytes);
+  char* base = (char*)d_ws;
+  size_t o = 0;
+  auto take = [&](size_t bytes) { size_t r = o; o = align_up(o + bytes, 256); return r; };
+  a.tile_count = (int*)(base + take(sizeof(int) * (size_t)n_tiles));
+  a.tile_list = (int*)(base + take(sizeof(int) * (size_t)n_tiles * TILE_LIST_CAP));
+  a.block_partials = (double*)(base + take(sizeof(double) * (size_t)n_tiles));
+  a.n_img = n_img; a.n_src = n_src; a.boxes = d_boxes; a.patches = d_patches; a.samp = d_samp;
+  a.max_patch_px = max_patch_px; a.noise_sum = d_noise_sum; a.max_tiles = max_tiles;
+  a.blocks_per_img = (2 * max_tiles + FR_WARPS - 1) / FR_WARPS; a.seed = seed;
+  CUDA_TRY(cudaMemsetAsync(a.tile_count, 0, sizeof(int) * (size_t)n_tiles, st));
+  const long long n_items = (long long)n_src * n_img;
+  if (n_items > 0) {
+    CUDA_TRY(cudaMemsetAsync(d_samp, 0, sizeof(float) * (size_t)(n_items * max_patch_px), st));
+    bin_boxes_kernel<<<(unsigned)((n_items + 3) / 4), 128, 0, st>>>(a);
+    LAUNCH_CHECK();
+  }
+  sample_counts_kernel<<<dim3(a.blocks_per_img, n_img), FR_WARPS * 32, 0, st>>>(a);
+  LAUNCH_CHECK();
+  alloc_final_kernel<<<n_img, 256, 0, st>>>(a);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
+int cg_binomial_draws(int64_t n, double p, uint64_t seed, int64_t count, double* d_out, void* stream) {
+  NEED_INIT();
+  if (count <= 0) return CG_OK;
+  binomial_test_kernel<<<(unsigned)((count + 255) / 256), 256, 0, (cudaStream_t)stream>>>(n, p, seed, count, d_out);
   LAUNCH_CHECK();
   return CG_OK;
 }

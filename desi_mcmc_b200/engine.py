@@ -493,6 +493,68 @@ def render_patches(images: Sequence[Image], srcs, items: np.ndarray | None = Non
     return patches, boxes.cpu().numpy().view(BOX_DTYPE)
 
 
+def binomial_draws(n: int, p: float, seed: int, count: int) -> np.ndarray:
+    """sample_binomial (celeste_sample_sources.pyx:161-166): count device draws."""
+    out = torch.zeros(count, dtype=torch.float64, device=device())
+    check(lib().cg_binomial_draws(int(n), float(p), int(seed), int(count), out.data_ptr(), stream_ptr()))
+    return out.cpu().numpy()
+
+
+class PhotonAllocation(object):
+    """Result of resample_photons: device patches in the item = src*n_img + img
+    layout.  rates / samp: [n_items, max_patch_px] float32; boxes: host BOX_DTYPE
+    array; noise_sums: host float64 [n_img]."""
+
+    def __init__(self, rates, samp, boxes, d_boxes, noise_sums, n_src, n_img):
+        self.rates, self.samp, self.boxes, self.d_boxes = rates, samp, boxes, d_boxes
+        self.noise_sums, self.n_src, self.n_img = noise_sums, n_src, n_img
+
+    def patch(self, src: int, img: int, which: str = "samp") -> np.ndarray:
+        it = src * self.n_img + img
+        b = self.boxes[it]
+        h, w = int(b["y1"] - b["y0"]), int(b["x1"] - b["x0"])
+        buf = self.samp if which == "samp" else self.rates
+        return buf[it, :h * w].cpu().numpy().astype(np.float64).reshape(h, w)
+
+
+def resample_photons(images: Sequence[Image], srcs, seed: int, bound_cap: float = 0.0,
+                     max_patch_px: int | None = None, flags: int = CG_ITEM_FLUX_BAND) -> PhotonAllocation:
+    """N1 (celeste_mcmc.py:98-150 + celeste_sample_sources.pyx:61-122) for all
+    images of a field: render every source's rate patch, then split every
+    pixel's photons over the overlapping sources and the sky."""
+    L = lib()
+    harr, n_img = _handles(images)
+    if isinstance(srcs, np.ndarray):
+        _need_filters(srcs)
+    d_srcs, n_src = _srcs_dev(srcs)
+    if max_patch_px is None:
+        side = int(2 * bound_cap + 3) if bound_cap > 0 else 203
+        max_patch_px = side * side
+    n_items = n_src * n_img
+    rates = torch.zeros((max(n_items, 1), max_patch_px), dtype=torch.float32, device=device())
+    samp = torch.empty_like(rates)
+    d_boxes = torch.zeros(max(n_items, 1) * BOX_DTYPE.itemsize, dtype=torch.uint8, device=device())
+    if n_items:
+        ws = _workspace(_ffi.CG_WS_RENDER, n_items, n_img, max_patch_px)
+        check(L.cg_render_patches(harr, n_img, d_srcs.data_ptr(), n_src, None, n_items, flags,
+                                  float(bound_cap), max_patch_px, rates.data_ptr(), d_boxes.data_ptr(),
+                                  ws.data_ptr(), ws.numel(), stream_ptr()))
+    tiles = n_img * max(int(L.cg_field_tiles(im.shape[0], im.shape[1])) for im in images)
+    need = int(L.cg_alloc_workspace_bytes(n_img, tiles))
+    aws = _state["ws"].get("alloc")
+    if aws is None or aws.numel() < need:
+        aws = torch.empty(need, dtype=torch.uint8, device=device())
+        _state["ws"]["alloc"] = aws
+    noise = torch.zeros(n_img, dtype=torch.float64, device=device())
+    check(L.cg_sample_source_counts(harr, n_img, n_src, d_boxes.data_ptr(), rates.data_ptr(), max_patch_px,
+                                    int(seed) & 0xFFFFFFFFFFFFFFFF, samp.data_ptr(), noise.data_ptr(),
+                                    aws.data_ptr(), aws.numel(), stream_ptr()))
+    if n_items:
+        last_eval_count()
+    boxes = d_boxes.cpu().numpy().view(BOX_DTYPE)[:n_items]
+    return PhotonAllocation(rates, samp, boxes, d_boxes, noise.cpu().numpy(), n_src, n_img)
+
+
 def field_workspace(images: Sequence[Image], n_src: int, max_patch_px: int):
     n_img = len(images)
     tiles = n_img * max(int(lib().cg_field_tiles(im.shape[0], im.shape[1])) for im in images)

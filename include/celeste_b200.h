@@ -253,6 +253,26 @@ int cg_score_proposals(CgImage* const* imgs, int32_t n_img,
 int cg_poisson_loglike(const double* d_data, const double* d_model, const double* d_mask,
                        int64_t n, double* d_out, void* stream);
 
+/* ---- N1: celeste_sample_sources.pyx:61-156 ------------------------------- */
+/* sample_source_counts for n_img images at once.  Item = src*n_img + img (the
+ * layout cg_render_patches produces with d_items = NULL): d_boxes[item] is the
+ * source's patch box, d_patches + item*max_patch_px its rate patch.  For every
+ * pixel the photons int(nelec) are split over the sources whose box STRICTLY
+ * contains the pixel (the reference's test, :53-54) and the sky rate epsilon
+ * by conditional binomials in source order; d_samp (same layout as d_patches)
+ * receives the per-source counts, d_noise_sum[n_img] the sky photons (:96,:112).
+ * Random numbers: Philox-4x32-10 keyed by (seed, image, pixel, draw) -- the
+ * reference's serial MT19937 stream cannot be followed in parallel, so parity
+ * is distributional.  Workspace: cg_alloc_workspace_bytes(n_img, n_img*max_i
+ * cg_field_tiles(H_i, W_i)). */
+size_t cg_alloc_workspace_bytes(int32_t n_img, int64_t n_tiles);
+int cg_sample_source_counts(CgImage* const* imgs, int32_t n_img, int32_t n_src,
+                            const CgBox* d_boxes, const float* d_patches, int64_t max_patch_px,
+                            uint64_t seed, float* d_samp, double* d_noise_sum,
+                            void* d_workspace, size_t workspace_bytes, void* stream);
+/* sample_binomial (:161-166): count draws of binomial(n, p) -> d_out (float64). */
+int cg_binomial_draws(int64_t n, double p, uint64_t seed, int64_t count, double* d_out, void* stream);
+
 /* ---- A16: planck.py:94-158 ----------------------------------------------- */
 /* out[i*5+band] = photons_expected_brightness(T[i], b[i], band); float64. */
 int cg_planck_fluxes(const double* d_T, const double* d_b, int64_t n,

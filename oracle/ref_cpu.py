@@ -763,3 +763,91 @@ def set_filter_tables_npz(npz_path):
         h_vecs[b] = sens[b] / (h * c / wl[b]) * dLam
     _FILTERS = (wl, sens, h_vecs)
     return _FILTERS
+
+
+# --------------------------------------------------------------------------
+# celeste_sample_sources.pyx (N1).  rk_binomial of the vendored randomkit is
+# the generator behind numpy.random.RandomState.binomial (verified stream-equal
+# in tests/test_cpu_oracle.py), so the legacy RandomState stands in for the
+# rk_state the Cython code reaches into.
+# --------------------------------------------------------------------------
+class NativePatch(object):
+    """celeste_sample_sources.pyx:31-41."""
+
+    def __init__(self, data, ylim, xlim):
+        self.data = data
+        self.x0, self.x1 = int(xlim[0]), int(xlim[1])
+        self.y0, self.y1 = int(ylim[0]), int(ylim[1])
+
+
+def sample_multinomial(n, probs, random_state):
+    """celeste_sample_sources.pyx:127-156 (conditional binomials)."""
+    S = probs.shape[0]
+    samples = np.zeros(S, dtype=np.int64)
+    unsampled = int(n)
+    sum_probs = 0.
+    for s in range(S):
+        sum_probs += probs[s]
+    for s in range(S - 1):
+        curr_prob = probs[s]
+        curr_sample = int(random_state.binomial(unsampled, curr_prob / sum_probs))
+        samples[s] += curr_sample
+        unsampled -= curr_sample
+        if unsampled <= 0:
+            break
+        sum_probs -= curr_prob
+    samples[S - 1] += unsampled
+    return samples
+
+
+def sample_source_counts(src_imgs, samp_imgs, nelec, src_boxes, epsilon, random_state=None):
+    """celeste_sample_sources.pyx:61-122, including the strict box test of
+    get_bounding_boxes_idx (:53-54)."""
+    random_state = random_state or np.random.RandomState()
+    dim0, dim1 = nelec.shape
+    noise_sum = 0.
+    for y in range(dim0):
+        for x in range(dim1):
+            num_photons_xy = nelec[y, x]
+            possible = [s for s in range(src_boxes.shape[0])
+                        if x > src_boxes[s, 0] and x < src_boxes[s, 1] and
+                        y > src_boxes[s, 2] and y < src_boxes[s, 3]]
+            if len(possible) == 0:
+                noise_sum += num_photons_xy
+                continue
+            S = len(possible) + 1
+            model_fluxes = np.zeros(S)
+            for i, pi in enumerate(possible):
+                p = src_imgs[pi]
+                model_fluxes[i] = p.data[y - p.y0, x - p.x0]
+            model_fluxes[S - 1] = epsilon
+            src_photons = sample_multinomial(int(num_photons_xy), model_fluxes, random_state)
+            for i, pi in enumerate(possible):
+                p = samp_imgs[pi]
+                p.data[y - p.y0, x - p.x0] = src_photons[i]
+            noise_sum += src_photons[S - 1]
+    return samp_imgs, noise_sum
+
+
+def galaxy_source_like_grad(th, Z_s, images):
+    """celeste_galaxy_conditionals.py:44-88: analytic in theta and the fluxes,
+    central differences (1e-5) in sigma, phi, rho, u."""
+    theta_s, sig_s, phi_s, rho_s = th[0:4]
+    u_s = th[4:6]
+    bs = dict(zip(BANDS, th[-5:]))
+    grad_theta_s = 0.
+    grad_bs = dict(zip(BANDS, np.zeros(len(BANDS))))
+    for n, img in enumerate(images):
+        R_s = gen_galaxy_transformation(sig_s, rho_s, phi_s, img.Ups_n)
+        f_exp, _, _ = gen_galaxy_prof_psf_image('exp', R_s, u_s, img)
+        f_dev, _, _ = gen_galaxy_prof_psf_image('dev', R_s, u_s, img)
+        f_nms = theta_s * f_exp + (1. - theta_s) * f_dev
+        grad_theta_s += np.sum((Z_s[n] / f_nms - bs[img.band]) * (f_exp - f_dev))
+        grad_bs[img.band] += 1. / bs[img.band] * np.sum(Z_s[n]) - np.sum(f_nms)
+    grad_RU = np.zeros(5)
+    for i, th_i in enumerate([1, 2, 3, 4, 5]):
+        de = np.zeros(th.shape)
+        de[th_i] = 1e-5
+        dell = galaxy_source_like(th + de, Z_s, images) - galaxy_source_like(th - de, Z_s, images)
+        grad_RU[i] = dell / (2. * de[th_i])
+    return np.concatenate([[grad_theta_s], grad_RU, np.array([grad_bs[b] for b in BANDS])])

@@ -151,3 +151,23 @@ def test_oracle_vs_golden_vectors():
     rs = np.random.RandomState(0)
     want = [rs.binomial(914, 6.29379e-16)] + [rs.binomial(1000, .3) for _ in range(7)]
     assert list(g["rk_binom"]) == want and g["rk_binom"][0] == 0
+
+
+def test_oracle_sample_source_counts_conserves_photons():
+    """celeste_sample_sources.pyx:61-156 restated over the legacy RandomState
+    stream: every photon lands in one source patch or the sky sum, pixels on a
+    patch's first row/column are never offered to it (:53-54)."""
+    rng = np.random.RandomState(3)
+    nelec = rng.poisson(200., size=(12, 15)).astype(np.float64)
+    boxes = np.array([[1, 9, 2, 10], [5, 14, 4, 12]])
+    src = [ref.NativePatch(rng.uniform(1., 50., size=(8, 8)), (2, 10), (1, 9)),
+           ref.NativePatch(rng.uniform(1., 50., size=(8, 9)), (4, 12), (5, 14))]
+    samp = [ref.NativePatch(np.zeros((8, 8)), (2, 10), (1, 9)), ref.NativePatch(np.zeros((8, 9)), (4, 12), (5, 14))]
+    samp, noise = ref.sample_source_counts(src, samp, nelec, boxes, 30., np.random.RandomState(0))
+    assert noise + samp[0].data.sum() + samp[1].data.sum() == nelec.sum()
+    assert np.all(samp[0].data[0] == 0) and np.all(samp[0].data[:, 0] == 0) and samp[0].data.sum() > 0
+    again = [ref.NativePatch(np.zeros((8, 8)), (2, 10), (1, 9)), ref.NativePatch(np.zeros((8, 9)), (4, 12), (5, 14))]
+    again, noise2 = ref.sample_source_counts(src, again, nelec, boxes, 30., np.random.RandomState(0))
+    assert noise2 == noise and np.array_equal(again[1].data, samp[1].data)
+    # test_celeste_sample_sources.py:4-8
+    assert ref.sample_multinomial(914, np.array([6.29379e-16, 1.]), np.random.RandomState(0))[0] == 0
