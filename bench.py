@@ -42,41 +42,71 @@ WORKLOAD = ("C2 full-field log-likelihood: synthetic Stripe-82 frame 2048x1489 x
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks + throttle reasons during the timed region."""
+    """SM clock + throttle reasons during the timed region: NVML in-process
+    (a sample every ~2 ms), nvidia-smi as the fallback."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.rows, self._stop_ev = index, [], threading.Event()
+        self.index, self._stop_ev = index, threading.Event()
+        self.sm, self.mx, self.reasons, self.how = [], [], set(), "nvidia-smi"
+        self.nv = self.h = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and vis.split(",")[index].strip().isdigit() else index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nv, self.how = pynvml, "nvml"
+        except Exception:
+            self.nv = None
+
+    def _sample_nvml(self):
+        nv = self.nv
+        self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+        if not self.mx:
+            self.mx.append(float(nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)))
+        try:
+            r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+        except Exception:
+            r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+        for nm, bit in (("hw_slowdown", 0x8), ("sw_power_cap", 0x4), ("sw_thermal_slowdown", 0x20),
+                        ("hw_thermal_slowdown", 0x40)):
+            if r & bit:
+                self.reasons.add(nm)
+
+    def _sample_smi(self):
+        out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                              "--format=csv,noheader,nounits"], capture_output=True,
+                             text=True, timeout=5).stdout.strip()
+        r = [c.strip() for c in out.split(",")]
+        if r and r[0].replace(".", "").isdigit():
+            self.sm.append(float(r[0]))
+        if len(r) > 1 and r[1].replace(".", "").isdigit():
+            self.mx.append(float(r[1]))
+        for nm, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[4:8]):
+            if v.lower().startswith("active"):
+                self.reasons.add(nm)
 
     def run(self):
         while not self._stop_ev.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True,
-                                     text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([c.strip() for c in out.split(",")])
+                if self.nv is not None:
+                    self._sample_nvml()
+                else:
+                    self._sample_smi()
             except Exception:
                 pass
-            self._stop_ev.wait(0.1)
+            self._stop_ev.wait(0.002 if self.nv is not None else 0.1)
 
     def stop(self):
         self._stop_ev.set()
         self.join(timeout=6)
-        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
-        reasons = set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            for nm, v in zip(names, r[4:8]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
-        return {"sm_mhz": statistics.median(sm) if sm else None,
-                "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": statistics.median(self.sm) if self.sm else None,
+                "sm_max_mhz": max(self.mx) if self.mx else None,
+                "reasons": sorted(self.reasons), "samples": len(self.sm), "how": self.how}
 
 
 def cpu_baseline(field, budget_s):
@@ -173,10 +203,17 @@ def run_reference(args, rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--fields-per-gpu", type=int, default=8)
+    ap.add_argument("--streams", type=int, default=2,
+                    help="side streams the field sets of a step are spread over (gather of one set "
+                         "overlaps the render of the next)")
+    ap.add_argument("--unfused", action="store_true", help="field path = render patches, then gather "
+                    "(the first design) instead of the fused tile kernel")
+    ap.add_argument("--no-graph", action="store_true", help="launch every step kernel by kernel "
+                    "instead of replaying the captured CUDA graph")
     ap.add_argument("--fields-per-call", type=int, default=2,
                     help="fields batched into one cg_fields_loglik call (patches of a call stay in L2)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
@@ -202,6 +239,7 @@ def main():
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     engine.init(local)
+    engine.set_option(_ffi.CG_OPT_FIELD_FUSED, 0 if args.unfused else 1)
     dev = engine.device()
     F = args.fields_per_gpu
 
@@ -238,9 +276,10 @@ def main():
     stats = torch.zeros(64, dtype=torch.float64, device=dev)     # [sum ll, n_star, ...]
     n_star = float(sum(1 for fld in fields for s in fld["sources"] if s["a"] == 0))
 
+    sweep = engine.FieldSweep(sets, n_streams=args.streams)
+
     def step_device():
-        for fs in sets:
-            fs.loglik_device()
+        sweep.run()
         if world > 1:
             stats.zero_()
             stats[0] = sum(fs.ll.sum() for fs in sets)
@@ -266,31 +305,51 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    # ---- device-resident leg
+    # ---- roofline leg: the same step launched kernel by kernel on one stream, every
+    # render_kernel launch bracketed by CUDA events on that stream (events cannot
+    # be timed inside a graph replay, and overlapped kernels would share the SMs)
+    for _ in range(args.warmup):
+        for fs in sets:
+            fs.loglik_device()
+    barrier()
+    engine.launch_count(reset=True)
+    engine.profile_render(True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        for fs in sets:
+            fs.loglik_device()
+    e1.record()
+    barrier()
+    serial_ms = e0.elapsed_time(e1)
+    launches = engine.launch_count()        # kernels of args.steps steps (a graph replay launches the same ones)
+    render_ms, render_n = engine.profile_render_read()
+    engine.profile_render(False)
+    ll_serial = np.concatenate([fs.ll.cpu().numpy() for fs in sets])
+
+    # ---- device-resident leg (the headline `value`): the captured step
+    if not args.no_graph:
+        sweep.capture()
     for _ in range(args.warmup):
         step_device()
     barrier()
     sampler = ClockSampler(local)
     sampler.start()
-    engine.launch_count(reset=True)
-    engine.profile_render(True)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
         step_device()
     e1.record()
     barrier()
     dev_ms = max_over_ranks(e0.elapsed_time(e1))
-    launches = engine.launch_count()
-    render_ms, render_n = engine.profile_render_read()
-    engine.profile_render(False)
     ll_ref = np.concatenate([fs.ll.cpu().numpy() for fs in sets])
+    assert np.array_equal(ll_serial, ll_ref), "graph replay and serial launches differ"
 
     # ---- end-to-end leg: host source arrays -> pinned -> device, ll -> host
     def step_e2e():
         for fs, g in zip(sets, groups):
             fs.set_sources([srcs_host[f] for f in g])
-            fs.loglik_device()
+        sweep.run()
+        for fs in sets:
             fs.h_ll.copy_(fs.ll, non_blocking=True)
         if world > 1:
             stats.zero_()
@@ -342,7 +401,8 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": "f32 rates, f64 log-likelihood accumulation",
             "data": "synthetic",
             "config": {"workload": WORKLOAD, "fields_per_gpu": F, "fields_total": F * world,
-                       "fields_per_call": FPC,
+                       "fields_per_call": FPC, "streams": sweep.n_streams,
+                       "launch": "kernel by kernel" if args.no_graph else "one CUDA graph replay per step",
                        "evals_per_step_per_gpu": evals_step, "issued_lane_evals_per_step_per_gpu": issued_step,
                        "pixels_per_step_per_gpu": F * 5 * H * W,
                        "l2": "inputs larger than L2 (%d MB of pixel data per GPU per step)" % (F * 5 * H * W * 4 >> 20),
@@ -351,7 +411,8 @@ def main():
             "e2e": {"value": e2e_value, "unit": "evals/s", "ms_per_step": 1e3 * e2e_s / args.steps,
                     "h2d_bytes_per_step": F * N_SRC * _ffi.SRC_DTYPE.itemsize, "d2h_bytes_per_step": F * 5 * 8},
             "gpu_launches": launches,
-            "roofline": {"kernel": "render_kernel<float, MODE_PATCH>", "bound": "xu",
+            "roofline": {"kernel": "render_kernel<float, MODE_PATCH>" if args.unfused else "field_tile_kernel",
+                         "bound": "xu",
                          "achieved": achieved, "peak": xu_peak, "unit": "evals/s (1 eval = 1 MUFU.EX2 + 3 FP32)",
                          "frac": (achieved / xu_peak) if achieved else None,
                          "peak_source": "measured live: MUFU.EX2 probe kernel on this GPU (cg_pipe_probe); "
@@ -361,7 +422,8 @@ def main():
                          "note": "achieved = algorithmic evals (footprint pixels x components, SURVEY 8d) / kernel time; "
                                  "issued = MUFU.EX2 lane-operations actually executed after per-warp component culling",
                          "fp32_fma_peak": fma_peak, "kernel_ms_total": render_ms, "kernel_launches": render_n,
-                         "kernel_share_of_step": render_ms / dev_ms if dev_ms else None,
+                         "kernel_share_of_step": render_ms / serial_ms if serial_ms else None,
+                         "serial_ms_per_step": serial_ms / args.steps,
                          "traffic": None,
                          "hbm_peak_gbs": peaks.get("hbm_gbs")},
             "clocks": clocks,

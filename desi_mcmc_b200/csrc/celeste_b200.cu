@@ -227,8 +227,9 @@ struct PrepArgs {
   // full-field path: per (image, 64x16 tile) list of the items that overlap it
   int unit_wt;              // warp tiles per work unit (same value in RenderArgs)
   int* tile_count;          // [n_img][max_tiles] (NULL: no binning)
-  int* tile_list;           // [n_img][max_tiles][TILE_LIST_CAP]
+  int* tile_list;           // [n_img][max_tiles][bin_cap]
   int max_tiles;
+  int bin_w, bin_h, bin_cap;
 };
 
 // ---------------------------------------------------------------------------
@@ -278,6 +279,9 @@ __device__ __forceinline__ float log_residual(float lam) {
   p = fmaf(r, p, -0.5f);
   p = fmaf(r, p, 1.0f);
   return r * p;
+}
+__device__ __forceinline__ double log_table(float lam, const LogTable* t) {
+  return __ldg(&t->t[(__float_as_int(lam) >> 18) & 8191]);
 }
 __device__ __forceinline__ double log_accurate(float lam, const LogTable* t) {
   return __ldg(&t->t[(__float_as_int(lam) >> 18) & 8191]) + (double)log_residual(lam);
@@ -534,35 +538,41 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
   const int n_units = (n_strips + a.unit_wt - 1) / a.unit_wt;
   const bool heavy = K > 4;
   int start = 0, wpos = 0;
+  const bool listed = a.worklist != nullptr;      // the fused field path renders by image tile, not by work list
   if (lane == 0) {
-    if (n_strips) {
+    if (n_strips && listed) {
       start = atomicAdd(&a.cnt->total_strips, n_strips);
       wpos = atomicAdd(heavy ? &a.cnt->heavy_strips : &a.cnt->light_strips, n_units);
     }
     if (npx) atomicAdd(&a.cnt->evals, (unsigned long long)npx * (unsigned long long)K);
     if (err) atomicExch(&a.cnt->err_flag, 1);
-    if (start + n_strips > a.worklist_cap) { atomicExch(&a.cnt->err_flag, 3); }
+    if (listed && start + n_strips > a.worklist_cap) { atomicExch(&a.cnt->err_flag, 3); }
   }
   start = __shfl_sync(0xffffffffu, start, 0);
   wpos = __shfl_sync(0xffffffffu, wpos, 0);
   // heavy strips fill the list from the front, light ones from the back: the
   // render kernel drains the front first (longest-processing-time-first)
-  if (start + n_strips <= a.worklist_cap)
+  if (listed && start + n_strips <= a.worklist_cap)
     for (int j = lane; j < n_units; j += 32) {
       const int slot = heavy ? (wpos + j) : (a.worklist_cap - 1 - (wpos + j));
       a.worklist[slot] = make_int2((int)i, j * a.unit_wt);   // (item, first warp tile of the unit)
     }
   // bin the footprint into the image tiles it overlaps (full-field gather)
   if (a.tile_count && npx > 0 && K > 0) {
-    const int tiles_x = (W + TILE_W - 1) / TILE_W;
-    const int txa = x0 / TILE_W, txb = (x1 - 1) / TILE_W;
-    const int tya = y0 / TILE_H, tyb = (y1 - 1) / TILE_H;
+    // bin_w x bin_h bins with lists of bin_cap entries: 64 x 16 / 64 for the
+    // patch gather, 16 x 16 / 32 for the fused tile kernel
+    const int bw = a.bin_w, bh = a.bin_h, cap = a.bin_cap;
+    const int tiles_x = (W + bw - 1) / bw;
+    const int txa = x0 / bw, txb = (x1 - 1) / bw;
+    const int tya = y0 / bh, tyb = (y1 - 1) / bh;
     const int nx = txb - txa + 1, nt = nx * (tyb - tya + 1);
     for (int j = lane; j < nt; j += 32) {
       const int t = (tya + j / nx) * tiles_x + txa + (j % nx);
       const long long slot = (long long)it.img * a.max_tiles + t;
       const int pos = atomicAdd(&a.tile_count[slot], 1);
-      if (pos < TILE_LIST_CAP) a.tile_list[slot * TILE_LIST_CAP + pos] = (int)i;
+      // entry = item * 64 + K (K <= CG_MAX_COMP < 64): the tile kernels weigh a bin
+      // without touching the item headers
+      if (pos < cap) a.tile_list[slot * cap + pos] = (int)i * 64 + K;
     }
   }
   if (lane == 0) {
@@ -857,6 +867,7 @@ __global__ void items_finalize_kernel(const ItemHdr* hdr, const double* partials
 // its sources in source order -> bitwise reproducible), gathers the patches
 // and accumulates the Poisson terms in float64.
 #define FR_WARPS 4
+#define FT_BUCKETS 8
 struct FieldArgs {
   ImgPtrs imgs;
   int n_img;
@@ -873,6 +884,13 @@ struct FieldArgs {
   int item_base[CG_MAX_IMAGES], item_stride[CG_MAX_IMAGES], n_src[CG_MAX_IMAGES];
   float* const* model;     // device array [n_img] of optional model outputs, or NULL
   const LogTable* logtab;  // precomputed at cg_init
+  // fused tile path (field_tile_kernel)
+  const float* tab;        // component tables, n_items * TAB_STRIDE
+  int2* order;             // [FT_BUCKETS][tiles_total] (bin id, list length) by weight class
+  int* sched;              // [FT_BUCKETS] class sizes, [FT_BUCKETS] work counter (zero on entry)
+  Counters* cnt;
+  int cull;
+  int tiles_total;         // n_img * max_tiles (fused path: max_tiles counts 16 x 16 bins)
 };
 
 __device__ __forceinline__ void gather_patch(float (&lam)[4][4], const float* patches,
@@ -945,16 +963,31 @@ __global__ void __launch_bounds__(FR_WARPS * 32, 8) field_reduce_kernel(FieldArg
 
     const long long tslot = (long long)img * a.max_tiles + tile;
     const int cnt = a.tile_count[tslot];
-    if (cnt <= TILE_LIST_CAP) {
+    float* mdl = a.model ? a.model[img] : nullptr;
+    if (cnt == 0 && !mdl) {
+      // no source touches this tile: lambda = epsilon on every pixel, so the
+      // tile's terms are log(eps) * sum(x) - n * eps -- one log per warp
+      // instead of one per pixel (most of a Stripe-82 frame is empty sky)
+      double sd = 0.0;
+      int npx = 0;
+      if (im.nelec) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          sd += ((double)d[r][0] + (double)d[r][1]) + ((double)d[r][2] + (double)d[r][3]);
+          if (ybase + r < H) npx += max(0, min(4, W - x));
+        }
+      }
+      s = fma(sd, log_accurate(eps, logt), -(double)npx * (double)eps);
+    } else if (cnt <= TILE_LIST_CAP) {
       // lane j owns list entries j and j+32
       int it0 = 0x7fffffff, it1 = 0x7fffffff;
       int4 b0 = make_int4(0, 0, 0, 0), b1 = b0;
       if (lane < cnt) {
-        it0 = a.tile_list[tslot * TILE_LIST_CAP + lane];
+        it0 = a.tile_list[tslot * TILE_LIST_CAP + lane] >> 6;
         b0 = *reinterpret_cast<const int4*>(a.hdr + it0);       // x0,x1,y0,y1
       }
       if (lane + 32 < cnt) {
-        it1 = a.tile_list[tslot * TILE_LIST_CAP + lane + 32];
+        it1 = a.tile_list[tslot * TILE_LIST_CAP + lane + 32] >> 6;
         b1 = *reinterpret_cast<const int4*>(a.hdr + it1);
       }
       int r0 = 0, r1 = 0;
@@ -1014,10 +1047,11 @@ __global__ void __launch_bounds__(FR_WARPS * 32, 8) field_reduce_kernel(FieldArg
       }
     }
 
-    float* mdl = a.model ? a.model[img] : nullptr;
     // sum x log(lam) and sum lam, both in float64 (two independent chains)
     double slam = 0.0;
-    if (x + 3 < W && ybase + 3 < H && im.nelec) {          // interior lane: no bounds tests
+    if (cnt == 0 && !mdl) {
+      // done above
+    } else if (x + 3 < W && ybase + 3 < H && im.nelec) {   // interior lane: no bounds tests
 #pragma unroll
       for (int r = 0; r < 4; ++r)
 #pragma unroll
@@ -1069,6 +1103,454 @@ __global__ void __launch_bounds__(256) field_final_kernel(FieldArgs a) {
   s_fin[threadIdx.x] = t;
   __syncthreads();
   for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) s_fin[threadIdx.x] += s_fin[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) a.ll[img] = s_fin[0];
+}
+
+// ---------------------------------------------------------------------------
+// fused field path: render + gather + Poisson terms by IMAGE TILE
+// ---------------------------------------------------------------------------
+// One WARP owns a 16 x 16 pixel bin of an image (lane = 4 pixels of rows r and
+// r + 8, the lane layout of render_kernel) and is fully autonomous: no block
+// barrier anywhere.  It walks the bin's source list in source order (bitwise
+// reproducible), culls each source's components against the part of the
+// footprint inside its 256 pixels (tables read straight from L2, survivors
+// compacted into the warp's shared-memory table), accumulates
+// lambda = eps + sum_s rate_s in registers and finishes with the Poisson terms:
+// neither lambda nor any patch ever leaves the SM.  Pixel traffic is the 4 B of
+// nelec per pixel, read once.
+//
+// Bins differ in cost by three orders of magnitude (empty sky ... several
+// overlapping galaxies), so bin_order_kernel first sorts them into FT_BUCKETS
+// weight classes (weight = components in the bin's list) and the persistent
+// warps drain the classes heaviest first through one atomic counter, two work
+// indices ahead so that neither the atomic nor the descriptor load is waited for.
+#define BIN_W 16
+#define BIN_H 16
+#define BIN_CAP 32
+#define BINS_PER_TILE ((TILE_W / BIN_W) * (TILE_H / BIN_H))
+#define FT_THREADS 256
+#define FT_CHUNK 8
+#define FT_LIGHT 2          // classes below this are latency-bound (no galaxy in the bin)
+// bins per claimed work unit by weight class: heavy bins one at a time (balance), sky in bulk
+__device__ __forceinline__ constexpr int ft_chunk(int cls) {
+  return cls >= 5 ? 1 : (cls >= 3 ? 2 : (cls == 2 ? 4 : FT_CHUNK));
+}
+
+__device__ __forceinline__ int ft_bucket(int w) {
+  if (w <= 0) return 0;
+  if (w < 8) return 1;
+  if (w < 32) return 2;
+  return min(FT_BUCKETS - 1, 3 + (31 - __clz(w >> 5)));     // 32.. -> 3, 64.. -> 4, 128.. -> 5, ...
+}
+
+__device__ __forceinline__ int bins_of(const DevImage& im, int* bins_x) {
+  *bins_x = (im.W + BIN_W - 1) / BIN_W;
+  return *bins_x * ((im.H + BIN_H - 1) / BIN_H);
+}
+
+__global__ void __launch_bounds__(256) bin_order_kernel(FieldArgs a) {
+  const int g = blockIdx.x * 256 + threadIdx.x;
+  int b = -1, cnt = 0;
+  if (g < a.tiles_total) {
+    const int img = g / a.max_tiles, t = g - img * a.max_tiles;
+    int bx;
+    if (t < bins_of(*a.imgs.p[img], &bx)) {
+      cnt = a.tile_count[g];
+      if (cnt > BIN_CAP) {
+        b = FT_BUCKETS - 1;
+      } else {
+        int w = 0;
+        for (int j = 0; j < cnt; ++j) w += a.tile_list[(long long)g * BIN_CAP + j] & 63;
+        b = ft_bucket(w);
+      }
+    }
+  }
+  // warp-aggregated append to the class list
+  const unsigned lane = threadIdx.x & 31;
+  const unsigned peers = __match_any_sync(0xffffffffu, b);
+  if (b >= 0) {
+    const int leader = __ffs(peers) - 1;
+    int base = 0;
+    if ((int)lane == leader) base = atomicAdd(&a.sched[b], __popc(peers));
+    base = __shfl_sync(peers, base, leader);
+    a.order[(long long)b * a.tiles_total + base + __popc(peers & ((1u << lane) - 1u))] = make_int2(g, cnt);
+  }
+}
+
+// cull_components with the table read from global memory (L2), 2 components per lane
+__device__ __forceinline__ int ft_cull(const float* gtab, int K, int lane, float xa, float xb,
+                                       float ya, float yb, float* wtab) {
+  float lb = -INFINITY;
+  float4 e0[2], e1[2];
+  float qs[2], kx[2], ky[2], dx2[2], dy2[2];
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    const int k = lane + 32 * r;
+    qs[r] = -INFINITY; kx[r] = ky[r] = 0.f; dx2[r] = dy2[r] = 0.f;
+    if (k < K) {
+      const float4* t4 = reinterpret_cast<const float4*>(gtab + k * TAB_W);
+      e0[r] = __ldg(t4);
+      e1[r] = __ldg(t4 + 1);
+      const float4 e2 = __ldg(t4 + 2);
+      const float mx = e1[r].z, my = e1[r].w;
+      qs[r] = e2.x; kx[r] = e2.y; ky[r] = e2.z;
+      const float fx = fmaxf(fabsf(xa - mx), fabsf(xb - mx)), fy = fmaxf(fabsf(ya - my), fabsf(yb - my));
+      const float l = qs[r] - e2.w * (fx * fx + fy * fy);
+      if (l == l) lb = fmaxf(lb, l);
+      const float dx = fmaxf(0.f, fmaxf(xa - mx, mx - xb)), dy = fmaxf(0.f, fmaxf(ya - my, my - yb));
+      dx2[r] = dx * dx; dy2[r] = dy * dy;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) lb = fmaxf(lb, __shfl_xor_sync(0xffffffffu, lb, o));
+  const float thr = lb - (CULL_T + 0.5f);
+  bool keep[2];
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    const float rho = (qs[r] - thr) * 1.0001f;
+    keep[r] = (lane + 32 * r < K) && !(rho < 0.f) && !(dx2[r] > rho * kx[r]) && !(dy2[r] > rho * ky[r]);
+  }
+  const unsigned m0 = __ballot_sync(0xffffffffu, keep[0]);
+  const unsigned m1 = __ballot_sync(0xffffffffu, keep[1]);
+  const unsigned lt = (1u << lane) - 1u;
+  if (keep[0]) {
+    float* d = wtab + __popc(m0 & lt) * 8;
+    *reinterpret_cast<float4*>(d) = e0[0];
+    *reinterpret_cast<float2*>(d + 4) = make_float2(e1[0].x, e1[0].y);
+  }
+  if (keep[1]) {
+    float* d = wtab + (__popc(m0) + __popc(m1 & lt)) * 8;
+    *reinterpret_cast<float4*>(d) = e0[1];
+    *reinterpret_cast<float2*>(d + 4) = make_float2(e1[1].x, e1[1].y);
+  }
+  __syncwarp();
+  return __popc(m0) + __popc(m1);
+}
+
+// evaluate the compacted mixture (8 floats per component in the warp's shared
+// table: one 16-byte + one 8-byte load) at the lane's pixels: two rows / one row
+__device__ __forceinline__ void ft_eval2(const float* tb, int n, float y0l, float y1l,
+                                         const float (&xl)[4], float (&acc0)[4], float (&acc1)[4]) {
+#pragma unroll 2
+  for (int k = 0; k < n; ++k, tb += 8) {
+    const float4 t0 = *reinterpret_cast<const float4*>(tb);      // A, B, C, b10
+    const float2 t1 = *reinterpret_cast<const float2*>(tb + 4);  // c01, c00
+    const float b1a = fmaf(t0.y, y0l, t0.w), b1b = fmaf(t0.y, y1l, t0.w);
+    const float c1a = fmaf(fmaf(t0.z, y0l, t1.x), y0l, t1.y);
+    const float c1b = fmaf(fmaf(t0.z, y1l, t1.x), y1l, t1.y);
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      acc0[p] += ex2_approx(fmaf(fmaf(t0.x, xl[p], b1a), xl[p], c1a));
+      acc1[p] += ex2_approx(fmaf(fmaf(t0.x, xl[p], b1b), xl[p], c1b));
+    }
+  }
+}
+__device__ __forceinline__ void ft_eval1(const float* tb, int n, float yl,
+                                         const float (&xl)[4], float (&acc)[4]) {
+#pragma unroll 4
+  for (int k = 0; k < n; ++k, tb += 8) {
+    const float4 t0 = *reinterpret_cast<const float4*>(tb);
+    const float2 t1 = *reinterpret_cast<const float2*>(tb + 4);
+    const float b1 = fmaf(t0.y, yl, t0.w);
+    const float c1 = fmaf(fmaf(t0.z, yl, t1.x), yl, t1.y);
+#pragma unroll
+    for (int p = 0; p < 4; ++p) acc[p] += ex2_approx(fmaf(fmaf(t0.x, xl[p], b1), xl[p], c1));
+  }
+}
+
+struct FtGeom { int X0, Y0, x, yA, yB; };
+
+// one source on the warp's bin: cull, evaluate, add the rates inside the footprint
+__device__ __forceinline__ void ft_source(const FieldArgs& a, int item, int K, int4 bx, int2 o, float fl,
+                                          const FtGeom& q, int lane, float* wtab,
+                                          float (&lam)[2][4], unsigned long long& issued) {
+  const int ix0 = max(q.X0, bx.x), ix1 = min(q.X0 + BIN_W, bx.y);
+  const int iy0 = max(q.Y0, bx.z), iy1 = min(q.Y0 + BIN_H, bx.w);
+  if (ix0 >= ix1 || iy0 >= iy1 || K <= 0) return;                // warp-uniform
+  const float* gtab = a.tab + (long long)item * TAB_STRIDE;
+  int n = K;
+  __syncwarp();                       // the warp is done reading its previous table
+  if (a.cull && n > 1) {
+    n = ft_cull(gtab, n, lane, (float)(ix0 - o.x), (float)(ix1 - 1 - o.x), (float)(iy0 - o.y),
+                (float)(iy1 - 1 - o.y), wtab);
+  } else {
+    // no culling: copy the quadratics as they are (the eval loops read shared memory only)
+    for (int k = lane; k < n; k += 32) {
+      const float4* t4 = reinterpret_cast<const float4*>(gtab + k * TAB_W);
+      const float4 e0 = __ldg(t4), e1 = __ldg(t4 + 1);
+      *reinterpret_cast<float4*>(wtab + k * 8) = e0;
+      *reinterpret_cast<float2*>(wtab + k * 8 + 4) = make_float2(e1.x, e1.y);
+    }
+    __syncwarp();
+  }
+  const float* tb = wtab;
+  float xl[4];
+#pragma unroll
+  for (int p = 0; p < 4; ++p) xl[p] = (float)(q.x + p - o.x);
+  const bool doA = iy0 < q.Y0 + 8, doB = iy1 > q.Y0 + 8;         // which row halves the footprint reaches
+  float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
+  if (doA && doB) {
+    ft_eval2(tb, n, (float)(q.yA - o.y), (float)(q.yB - o.y), xl, acc0, acc1);
+    if (lane == 0) issued += (unsigned long long)n * 256;
+  } else if (doA) {
+    ft_eval1(tb, n, (float)(q.yA - o.y), xl, acc0);
+    if (lane == 0) issued += (unsigned long long)n * 128;
+  } else {
+    ft_eval1(tb, n, (float)(q.yB - o.y), xl, acc1);
+    if (lane == 0) issued += (unsigned long long)n * 128;
+  }
+  const bool inA = q.yA >= bx.z && q.yA < bx.w, inB = q.yB >= bx.z && q.yB < bx.w;
+#pragma unroll
+  for (int p = 0; p < 4; ++p) {
+    const bool inx = (q.x + p >= bx.x) && (q.x + p < bx.y);
+    lam[0][p] += (inA && inx) ? acc0[p] * fl : 0.f;
+    lam[1][p] += (inB && inx) ? acc1[p] * fl : 0.f;
+  }
+}
+
+__global__ void __launch_bounds__(FT_THREADS, 4) field_tile_kernel(FieldArgs a) {
+  __shared__ __align__(16) float s_wtab[FT_THREADS / 32][CG_MAX_COMP * 8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* const wtab = s_wtab[warp];
+  const LogTable* const logt = a.logtab;
+
+  // class sizes (written by bin_order_kernel, complete before this launch)
+  __shared__ int s_csize[FT_BUCKETS];
+  if (threadIdx.x < FT_BUCKETS) s_csize[threadIdx.x] = a.sched[threadIdx.x];
+  __syncthreads();
+  int total = 0;
+#pragma unroll
+  for (int b = 0; b < FT_BUCKETS; ++b) total += s_csize[b];
+  unsigned long long issued = 0;
+
+  // Work is claimed in UNITS of 1 (heavy classes) to FT_CHUNK (sky) bins of one
+  // class -- one same-address atomic per unit -- two units ahead: while unit c0
+  // is processed the descriptors of unit c1 are loading (lane j holds bin j of
+  // the unit) and the atomic for c2 is in flight.
+  // Units of the LIGHT classes (sky, stars only: a chain of dependent loads and
+  // a handful of exps -- latency-bound) are interleaved evenly with the HEAVY
+  // ones (XU-bound), heaviest first within each pool, so that the SM always has
+  // arithmetic to issue while the light warps wait on memory.
+  int n_light = 0, n_heavy = 0;
+#pragma unroll
+  for (int b = 0; b < FT_BUCKETS; ++b) {
+    const int nu = (s_csize[b] + ft_chunk(b) - 1) / ft_chunk(b);
+    if (b < FT_LIGHT) n_light += nu; else n_heavy += nu;
+  }
+  total = n_light + n_heavy;                                   // units
+  auto load_unit = [&](int u) -> int2 {
+    // Bresenham split of the unit index into the two pools
+    const int lb = (int)(((long long)u * n_light) / total);           // light units before u
+    const bool light = (int)(((long long)(u + 1) * n_light) / total) > lb;
+    int v = light ? lb : u - lb;
+    int cls = light ? FT_LIGHT - 1 : FT_BUCKETS - 1;
+    const int lo = light ? 0 : FT_LIGHT;
+#pragma unroll
+    for (int b = FT_BUCKETS - 1; b > 0; --b) {
+      const int nu = (s_csize[b] + ft_chunk(b) - 1) / ft_chunk(b);
+      if (cls == b && b > lo && v >= nu) { v -= nu; cls = b - 1; }
+    }
+    const int first = v * ft_chunk(cls) + lane;
+    int2 dsc = make_int2(-1, 0);
+    if (lane < ft_chunk(cls) && first < s_csize[cls]) dsc = a.order[(long long)cls * a.tiles_total + first];
+    return dsc;
+  };
+  int c0 = 0, c1 = 0;
+  if (lane == 0) {
+    c0 = atomicAdd(&a.sched[FT_BUCKETS], 1);
+    c1 = atomicAdd(&a.sched[FT_BUCKETS], 1);
+  }
+  c0 = __shfl_sync(0xffffffffu, c0, 0);
+  c1 = __shfl_sync(0xffffffffu, c1, 0);
+  int2 dcur = make_int2(-1, 0);
+  if (c0 < total) dcur = load_unit(c0);
+
+  while (c0 < total) {
+    int c2 = 0;
+    if (lane == 0) c2 = atomicAdd(&a.sched[FT_BUCKETS], 1);
+    int2 dnext = make_int2(-1, 0);
+    if (c1 < total) dnext = load_unit(c1);
+
+   for (int cj = 0; cj < FT_CHUNK; ++cj) {
+    const int g = __shfl_sync(0xffffffffu, dcur.x, cj), cnt = __shfl_sync(0xffffffffu, dcur.y, cj);
+    if (g < 0) break;
+    const int img = g / a.max_tiles, bin = g - img * a.max_tiles;
+    const DevImage& im = *a.imgs.p[img];
+    const int H = im.H, W = im.W;
+    const int bins_x = (W + BIN_W - 1) / BIN_W;
+    FtGeom q;
+    q.X0 = (bin % bins_x) * BIN_W; q.Y0 = (bin / bins_x) * BIN_H;
+    q.x = q.X0 + (lane & 3) * 4; q.yA = q.Y0 + (lane >> 2); q.yB = q.yA + 8;
+
+    // pixel counts: independent of the source list, issue the loads first
+    float d[2][4];
+    {
+      const bool vec = ((W & 3) == 0) && (((uintptr_t)im.nelec & 15) == 0);
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const int y = r ? q.yB : q.yA;
+#pragma unroll
+        for (int p = 0; p < 4; ++p) d[r][p] = 0.f;
+        if (y < H && q.x < W) {
+          const float* rp = im.nelec + (long long)y * W + q.x;
+          if (vec) {
+            const float4 v = __ldcs(reinterpret_cast<const float4*>(rp));     // read once: streaming
+            d[r][0] = v.x; d[r][1] = v.y; d[r][2] = v.z; d[r][3] = v.w;
+          } else {
+#pragma unroll
+            for (int p = 0; p < 4; ++p)
+              if (q.x + p < W) d[r][p] = rp[p];
+          }
+        }
+      }
+    }
+    const float eps = (float)im.epsilon;
+    float* mdl = a.model ? a.model[img] : nullptr;
+    double s = 0.0;
+
+    if (cnt == 0 && !mdl) {
+      // no source reaches this bin: lambda = epsilon on every pixel, so its terms
+      // are log(eps) * sum(x) - n * eps -- one log per warp instead of one per pixel
+      double sd = 0.0;
+      int npx = 0;
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        sd += ((double)d[r][0] + (double)d[r][1]) + ((double)d[r][2] + (double)d[r][3]);
+        if ((r ? q.yB : q.yA) < H) npx += max(0, min(4, W - q.x));
+      }
+      s = fma(sd, log_accurate(eps, logt), -(double)npx * (double)eps);
+    } else {
+      float lam[2][4];
+#pragma unroll
+      for (int r = 0; r < 2; ++r)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) lam[r][p] = eps;
+
+      // candidates per round, one per lane: the bin's list (one round; lane j owns
+      // entry j) or, when the list overflowed, every source of the image 32 at a
+      // time.  They are taken in source order: rank by value / by lane.
+      const bool scan = cnt > BIN_CAP;
+      const int ns = scan ? a.n_src[img] : 0;
+      const int rounds = scan ? (ns + 31) / 32 : 1;
+      for (int rd = 0; rd < rounds; ++rd) {
+        int e = 0x7fffffff;
+        int4 bx = make_int4(0, 0, 0, 0);
+        int2 o = make_int2(0, 0);
+        float fl = 0.f;
+        bool valid = false;
+        if (!scan) {
+          if (lane < cnt) {
+            e = a.tile_list[(long long)g * BIN_CAP + lane];
+            valid = true;
+          }
+        } else {
+          const int sidx = rd * 32 + lane;
+          if (sidx < ns) {
+            e = (a.item_base[img] + sidx * a.item_stride[img]) * 64;
+            valid = true;
+          }
+        }
+        if (valid) {
+          const ItemHdr* hp = a.hdr + (e >> 6);
+          bx = *reinterpret_cast<const int4*>(hp);
+          o = *reinterpret_cast<const int2*>(&hp->ox);
+          fl = (float)hp->flux;
+          if (scan) {
+            const int K = hp->K;
+            e += K;
+            valid = (K > 0) && bx.x < q.X0 + BIN_W && bx.y > q.X0 && bx.z < q.Y0 + BIN_H && bx.w > q.Y0;
+          }
+        }
+        const unsigned vm = __ballot_sync(0xffffffffu, valid);
+        const int nv = __popc(vm);
+        int rk = __popc(vm & ((1u << lane) - 1u));               // scan: lane order = source order
+        if (!scan && nv > 1) {
+          rk = 0;
+          for (int j = 0; j < nv; ++j) rk += (__shfl_sync(0xffffffffu, e, j) < e);
+        }
+        for (int r = 0; r < nv; ++r) {
+          const unsigned m = __ballot_sync(0xffffffffu, valid && rk == r);
+          const int sl = __ffs(m) - 1;
+          const int ee = __shfl_sync(0xffffffffu, e, sl);
+          int4 b;
+          b.x = __shfl_sync(0xffffffffu, bx.x, sl); b.y = __shfl_sync(0xffffffffu, bx.y, sl);
+          b.z = __shfl_sync(0xffffffffu, bx.z, sl); b.w = __shfl_sync(0xffffffffu, bx.w, sl);
+          const int2 oo = make_int2(__shfl_sync(0xffffffffu, o.x, sl), __shfl_sync(0xffffffffu, o.y, sl));
+          ft_source(a, ee >> 6, ee & 63, b, oo, __shfl_sync(0xffffffffu, fl, sl), q, lane, wtab, lam, issued);
+        }
+      }
+
+      // Poisson terms.  log(lam) = T[bin] + res (log_accurate): sum x T in float64,
+      // sum x res (|res| < 1/60) and the 4-pixel row sums of lam in fp32, then float64
+      float sres = 0.f;
+      double slam = 0.0;
+      if (q.x + 3 < W && q.yB < H) {                          // interior lane: no bounds tests
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+#pragma unroll
+          for (int p = 0; p < 4; ++p) {
+            s = fma((double)d[r][p], log_table(lam[r][p], logt), s);
+            sres = fmaf(d[r][p], log_residual(lam[r][p]), sres);
+          }
+          slam += (double)((lam[r][0] + lam[r][1]) + (lam[r][2] + lam[r][3]));
+        }
+        if (mdl) {
+          float* m0 = mdl + (long long)q.yA * W + q.x;
+          float* m1 = mdl + (long long)q.yB * W + q.x;
+          if (((W & 3) == 0) && (((uintptr_t)mdl & 15) == 0)) {
+            *reinterpret_cast<float4*>(m0) = make_float4(lam[0][0], lam[0][1], lam[0][2], lam[0][3]);
+            *reinterpret_cast<float4*>(m1) = make_float4(lam[1][0], lam[1][1], lam[1][2], lam[1][3]);
+          } else {
+#pragma unroll
+            for (int p = 0; p < 4; ++p) { m0[p] = lam[0][p]; m1[p] = lam[1][p]; }
+          }
+        }
+      } else {
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+          const int y = r ? q.yB : q.yA;
+          if (y < H) {
+#pragma unroll
+            for (int p = 0; p < 4; ++p)
+              if (q.x + p < W) {
+                s = fma((double)d[r][p], log_table(lam[r][p], logt), s);
+                sres = fmaf(d[r][p], log_residual(lam[r][p]), sres);
+                slam += (double)lam[r][p];
+                if (mdl) mdl[(long long)y * W + q.x + p] = lam[r][p];
+              }
+          }
+        }
+      }
+      s += (double)sres - slam;
+    }
+    s = warp_sum(s);
+    if (lane == 0) a.block_partials[g] = s;
+   }
+
+    c0 = c1;
+    dcur = dnext;
+    c1 = __shfl_sync(0xffffffffu, c2, 0);
+  }
+  if (lane == 0 && issued) atomicAdd(&a.cnt->issued, issued);
+}
+
+// one block per image: fixed-shape tree over its bin sums
+__global__ void __launch_bounds__(1024) field_tile_final_kernel(FieldArgs a) {
+  const int img = blockIdx.x;
+  int bx;
+  const int n_bins = bins_of(*a.imgs.p[img], &bx);
+  __shared__ double s_fin[1024];
+  double t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+  const double* bp = a.block_partials + (long long)img * a.max_tiles;
+  int i = threadIdx.x;
+  for (; i + 3072 < n_bins; i += 4096) { t0 += bp[i]; t1 += bp[i + 1024]; t2 += bp[i + 2048]; t3 += bp[i + 3072]; }
+  for (; i < n_bins; i += 1024) t0 += bp[i];
+  s_fin[threadIdx.x] = (t0 + t1) + (t2 + t3);
+  __syncthreads();
+  for (int o = 512; o > 0; o >>= 1) {
     if (threadIdx.x < o) s_fin[threadIdx.x] += s_fin[threadIdx.x + o];
     __syncthreads();
   }
@@ -1623,7 +2105,7 @@ static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; 
 struct WsLayout {
   size_t counters, hdr, tab, worklist, partials, item_ll, img_boxes, aux_offsets, tiles, patches;
   size_t tile_count, done, tile_list, model_ptrs;   // full-field gather (tile_count and done are contiguous)
-  size_t tile_zero_bytes;
+  size_t tile_zero_bytes, order;
   // second pass (float64 re-score)
   size_t counters2, hdr2, tab2, worklist2, partials2, item_ll2, guard_list;
   size_t total;
@@ -1653,12 +2135,13 @@ static WsLayout ws_layout(long long n_items, long long max_patch_px, int with_pa
   L.item_ll = take(sizeof(double) * n_items);
   L.img_boxes = take(sizeof(CgBox) * CG_MAX_IMAGES);
   L.aux_offsets = take(sizeof(long long) * CG_MAX_IMAGES);
-  L.tiles = take(sizeof(double) * (size_t)n_tiles_total);
+  L.tiles = take(sizeof(double) * (size_t)n_tiles_total * (with_patches ? BINS_PER_TILE : 1));
   if (with_patches) {
-    L.tile_count = take(sizeof(int) * (size_t)n_tiles_total);
+    L.tile_count = take(sizeof(int) * (size_t)n_tiles_total * BINS_PER_TILE);
     L.done = take(sizeof(int) * CG_MAX_IMAGES);
     L.tile_zero_bytes = (L.done + sizeof(int) * CG_MAX_IMAGES) - L.tile_count;
-    L.tile_list = take(sizeof(int) * (size_t)n_tiles_total * TILE_LIST_CAP);
+    L.tile_list = take(sizeof(int) * (size_t)n_tiles_total * BINS_PER_TILE * BIN_CAP);   // >= n_tiles * TILE_LIST_CAP
+    L.order = take(sizeof(int2) * (size_t)n_tiles_total * BINS_PER_TILE * FT_BUCKETS);
     L.model_ptrs = take(sizeof(float*) * CG_MAX_IMAGES);
     L.patches = take(sizeof(float) * (size_t)(n_items * max_patch_px));
   }
@@ -1971,6 +2454,7 @@ static int fill_imgs(CgImage* const* imgs, int n_img, ImgPtrs* out) {
 }  // extern "C"
 
 static int g_cull = 1;
+static int g_field_fused = 1;   // CG_OPT_FIELD_FUSED
 
 // persistent grid: one CTA per resident slot
 template <typename real, int MODE>
@@ -2003,15 +2487,28 @@ static int run_prepare(const PrepArgs& pa_in, cudaStream_t st) {
   return CG_OK;
 }
 
+// CUDA-event bracket of the dominant kernel's launches (cg_profile_render)
+static bool prof_begin(cudaStream_t st) {
+  bool prof = g_prof_on && g_prof_n < PROF_MAX;
+  if (prof) {      // events of a captured launch cannot be timed: skip them inside a CUDA graph capture
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) prof = false;
+  }
+  if (prof) cudaEventRecord(g_prof_ev[2 * g_prof_n], st);
+  return prof;
+}
+static void prof_end(bool prof, cudaStream_t st) {
+  if (prof) { cudaEventRecord(g_prof_ev[2 * g_prof_n + 1], st); ++g_prof_n; }
+}
+
 template <typename real, int MODE>
 static int run_render(const RenderArgs& ra_in, long long n_items, cudaStream_t st) {
   if (n_items == 0) return CG_OK;
   RenderArgs ra = ra_in;
   ra.unit_wt = choose_unit_wt(n_items);
-  const bool prof = g_prof_on && g_prof_n < PROF_MAX;
-  if (prof) cudaEventRecord(g_prof_ev[2 * g_prof_n], st);
+  const bool prof = prof_begin(st);
   render_kernel<real, MODE><<<render_grid<real, MODE>(), STRIP_THREADS, 0, st>>>(ra);
-  if (prof) { cudaEventRecord(g_prof_ev[2 * g_prof_n + 1], st); ++g_prof_n; }
+  prof_end(prof, st);
   LAUNCH_CHECK();
   return CG_OK;
 }
@@ -2100,18 +2597,23 @@ int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off, const CgSou
   pa.n_img = n_img; pa.srcs = d_srcs; pa.n_src = h_src_off[n_fields]; pa.items = nullptr; pa.n_items = n_items;
   pa.default_flags = CG_ITEM_FLUX_BAND; pa.implicit_mode = 3; pa.bound_cap = bound_cap;
   pa.max_patch_px = max_patch_px; pa.hdr = (ItemHdr*)(base + L.hdr); pa.tab = base + L.tab;
-  pa.worklist = (int2*)(base + L.worklist); pa.worklist_cap = L.worklist_cap; pa.cnt = cnt;
+  pa.worklist = g_field_fused ? nullptr : (int2*)(base + L.worklist); pa.worklist_cap = L.worklist_cap; pa.cnt = cnt;
   pa.filters = g_d_filters;
   pa.tile_count = (int*)(base + L.tile_count); pa.tile_list = (int*)(base + L.tile_list);
-  pa.max_tiles = max_tiles;
+  const int max_bins = max_tiles * BINS_PER_TILE;      // 16 x 16 bins of the fused path
+  pa.max_tiles = g_field_fused ? max_bins : max_tiles;
+  pa.bin_w = g_field_fused ? BIN_W : TILE_W; pa.bin_h = g_field_fused ? BIN_H : TILE_H;
+  pa.bin_cap = g_field_fused ? BIN_CAP : TILE_LIST_CAP;
   rc = run_prepare<float>(pa, st);
   if (rc) return rc;
   RenderArgs ra;
   memset(&ra, 0, sizeof ra);
   ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.worklist_cap = pa.worklist_cap; ra.cull = g_cull; ra.logtab = g_d_logtab; ra.cnt = cnt;
   ra.patches = (float*)(base + L.patches); ra.max_patch_px = max_patch_px;
-  rc = run_render<float, MODE_PATCH>(ra, n_items, st);
-  if (rc) return rc;
+  if (!g_field_fused) {
+    rc = run_render<float, MODE_PATCH>(ra, n_items, st);
+    if (rc) return rc;
+  }
   fa.imgs = pa.imgs; fa.n_img = n_img; fa.hdr = pa.hdr;
   fa.patches = ra.patches; fa.max_patch_px = max_patch_px;
   fa.tile_count = pa.tile_count; fa.tile_list = pa.tile_list; fa.done = (int*)(base + L.done);
@@ -2126,10 +2628,27 @@ int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off, const CgSou
       fa.model = (float* const*)(base + L.model_ptrs);
     }
   }
-  field_reduce_kernel<<<dim3(blocks_per_img, n_img), FR_WARPS * 32, 0, st>>>(fa);
-  LAUNCH_CHECK();
-  field_final_kernel<<<n_img, 256, 0, st>>>(fa);
-  LAUNCH_CHECK();
+  if (g_field_fused) {
+    fa.tab = (const float*)pa.tab; fa.order = (int2*)(base + L.order); fa.sched = fa.done;
+    fa.cnt = cnt; fa.cull = g_cull; fa.max_tiles = max_bins; fa.tiles_total = max_bins * n_img;
+    static int per_sm = 0;
+    if (!per_sm && (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, field_tile_kernel, FT_THREADS, 0) !=
+                        cudaSuccess || per_sm < 1))
+      per_sm = 8;
+    bin_order_kernel<<<(fa.tiles_total + 255) / 256, 256, 0, st>>>(fa);
+    LAUNCH_CHECK();
+    const bool prof = prof_begin(st);
+    field_tile_kernel<<<g_sm_count * per_sm, FT_THREADS, 0, st>>>(fa);
+    prof_end(prof, st);
+    LAUNCH_CHECK();
+    field_tile_final_kernel<<<n_img, 1024, 0, st>>>(fa);
+    LAUNCH_CHECK();
+  } else {
+    field_reduce_kernel<<<dim3(blocks_per_img, n_img), FR_WARPS * 32, 0, st>>>(fa);
+    LAUNCH_CHECK();
+    field_final_kernel<<<n_img, 256, 0, st>>>(fa);
+    LAUNCH_CHECK();
+  }
   g_last_counters = cnt;
   return CG_OK;
 }
@@ -2146,6 +2665,7 @@ int cg_field_loglik(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs,
 int cg_set_option(int32_t option, int32_t value) {
   switch (option) {
     case CG_OPT_CULL: g_cull = value ? 1 : 0; return CG_OK;
+    case CG_OPT_FIELD_FUSED: g_field_fused = value ? 1 : 0; return CG_OK;
     default: return fail(CG_EINVAL, "unknown option %d", option);
   }
 }

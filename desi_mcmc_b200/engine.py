@@ -661,6 +661,64 @@ class FieldSet(object):
         return self.h_ll.numpy()
 
 
+class FieldSweep(object):
+    """Every field set of a rank scored as ONE step (models.py:75-79 loops the
+    fields; they are independent, so their launches may overlap).
+
+    The sets are enqueued round-robin on ``n_streams`` side streams forked from
+    the current stream, so the HBM-bound gather of one set runs under the
+    XU-bound render of the next; ``capture()`` records the whole step once as a
+    CUDA graph and ``run()`` replays it (one driver call per step instead of
+    4 launches + 2 memsets per set).  The number of sources per field is baked
+    into the captured launches: call ``capture()`` again after ``set_sources``
+    changed a count (parameter VALUES may change freely)."""
+
+    def __init__(self, sets: Sequence["FieldSet"], n_streams: int = 2):
+        self.sets = list(sets)
+        self.n_streams = max(1, min(int(n_streams), len(self.sets)))
+        self._side = [torch.cuda.Stream(device=device()) for _ in range(self.n_streams)] \
+            if self.n_streams > 1 else []
+        self.graph = None
+        self._counts = None
+
+    def _enqueue(self):
+        if not self._side:
+            for fs in self.sets:
+                fs.loglik_device()
+            return
+        cur = torch.cuda.current_stream()
+        for s in self._side:
+            s.wait_stream(cur)
+        for i, fs in enumerate(self.sets):
+            with torch.cuda.stream(self._side[i % len(self._side)]):
+                fs.loglik_device()
+        for s in self._side:
+            cur.wait_stream(s)
+
+    def capture(self):
+        self._enqueue()                      # warm-up outside the capture (lazy occupancy queries)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._enqueue()
+        self.graph = g
+        self._counts = [fs.src_off.copy() for fs in self.sets]
+        return self
+
+    def run(self):
+        """Enqueue one step on the current stream; nothing synchronises."""
+        if self.graph is not None:
+            for fs, c in zip(self.sets, self._counts):
+                if not np.array_equal(fs.src_off, c):
+                    raise RuntimeError("source counts changed since capture(): capture again")
+            self.graph.replay()
+        else:
+            self._enqueue()
+
+    def loglik_all(self) -> torch.Tensor:
+        return torch.cat([fs.ll for fs in self.sets])
+
+
 def items_loglik(images: Sequence[Image], srcs, items: np.ndarray, mode: int = CG_LL_POISSON_BG,
                  aux: torch.Tensor | None = None, aux_offsets: np.ndarray | None = None,
                  bound_cap: float = 0.0, max_patch_px: int = 0, use_fp64: bool = False):

@@ -318,3 +318,31 @@ def test_field_loglik_crowded_tile_overflow(engine, oracle):
         assert hp.rel_err(models[i].cpu().numpy(), lam, 1.0) < RATE_RTOL
         want = oracle.celeste_likelihood(osrcs, img)
         assert abs(ll[i] - want) <= LL_RTOL * abs(want)
+
+
+def test_field_loglik_scan_rounds(engine, oracle):
+    """150 sources over one tile: the overflow scan of the fused tile kernel
+    needs two rounds of 128 sources; the patch-gather path must agree too, and
+    two runs are bitwise identical (sources are added in source order)."""
+    from desi_mcmc_b200 import _ffi
+    field = synth.make_field(86, H=48, W=80, n_src=150, star_frac=.95, margin=20)
+    nelec = hp.simulate_nelec(oracle, field, 8)
+    gimgs = hp.gpu_images(engine, field, nelec)
+    oimgs = hp.oracle_images(oracle, field, nelec)
+    srcs = hp.gpu_sources(engine, field)
+    osrcs = hp.oracle_sources(oracle, field)
+    ll, models = engine.field_loglik(gimgs, srcs, return_model=True)
+    ll = ll.cpu().numpy()
+    ll_again = engine.field_loglik(gimgs, srcs).cpu().numpy()
+    assert np.array_equal(ll, ll_again)
+    engine.set_option(_ffi.CG_OPT_FIELD_FUSED, 0)
+    try:
+        ll_gather = engine.field_loglik(gimgs, srcs).cpu().numpy()
+    finally:
+        engine.set_option(_ffi.CG_OPT_FIELD_FUSED, 1)
+    for i, img in enumerate(oimgs):
+        lam = oracle.gen_model_image(osrcs, img)
+        assert hp.rel_err(models[i].cpu().numpy(), lam, 1.0) < RATE_RTOL
+        want = oracle.celeste_likelihood(osrcs, img)
+        assert abs(ll[i] - want) <= LL_RTOL * abs(want)
+        assert abs(ll_gather[i] - want) <= LL_RTOL * abs(want)
