@@ -210,11 +210,9 @@ def main():
     ap.add_argument("--streams", type=int, default=2,
                     help="side streams the field sets of a step are spread over (gather of one set "
                          "overlaps the render of the next)")
-    ap.add_argument("--unfused", action="store_true", help="field path = render patches, then gather "
-                    "(the first design) instead of the fused tile kernel")
     ap.add_argument("--no-graph", action="store_true", help="launch every step kernel by kernel "
                     "instead of replaying the captured CUDA graph")
-    ap.add_argument("--fields-per-call", type=int, default=2,
+    ap.add_argument("--fields-per-call", type=int, default=8,
                     help="fields batched into one cg_fields_loglik call (patches of a call stay in L2)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -239,7 +237,6 @@ def main():
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     engine.init(local)
-    engine.set_option(_ffi.CG_OPT_FIELD_FUSED, 0 if args.unfused else 1)
     dev = engine.device()
     F = args.fields_per_gpu
 
@@ -411,8 +408,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": "evals/s", "ms_per_step": 1e3 * e2e_s / args.steps,
                     "h2d_bytes_per_step": F * N_SRC * _ffi.SRC_DTYPE.itemsize, "d2h_bytes_per_step": F * 5 * 8},
             "gpu_launches": launches,
-            "roofline": {"kernel": "render_kernel<float, MODE_PATCH>" if args.unfused else "field_tile_kernel",
-                         "bound": "xu",
+            "roofline": {"kernel": "field_tile_kernel", "bound": "xu",
                          "achieved": achieved, "peak": xu_peak, "unit": "evals/s (1 eval = 1 MUFU.EX2 + 3 FP32)",
                          "frac": (achieved / xu_peak) if achieved else None,
                          "peak_source": "measured live: MUFU.EX2 probe kernel on this GPU (cg_pipe_probe); "

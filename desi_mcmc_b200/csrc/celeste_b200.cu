@@ -190,10 +190,11 @@ struct Counters {
 // a component is skipped for a warp when its largest value over the warp's
 // pixels is below 2^-CULL_T of a lower bound of the mixture there
 #define CULL_T 27.0f
-// full-field gather: image tiles of 64 x 16 pixels, per-tile source lists
+// photon allocation: image tiles of 64 x 16 pixels, per-tile source lists (the field path bins 16 x 16, see BIN_W)
 #define TILE_W 64
 #define TILE_H 16
 #define TILE_LIST_CAP 64
+#define FR_WARPS 4          // warps per block of the photon-allocation kernel (one per half tile)
 
 #define CG_MAX_FIELDS 16
 struct FieldBatch {   // implicit_mode 3: independent fields, each a cross product of its sources x images
@@ -559,8 +560,7 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
     }
   // bin the footprint into the image tiles it overlaps (full-field gather)
   if (a.tile_count && npx > 0 && K > 0) {
-    // bin_w x bin_h bins with lists of bin_cap entries: 64 x 16 / 64 for the
-    // patch gather, 16 x 16 / 32 for the fused tile kernel
+    // bin_w x bin_h bins with lists of bin_cap entries (16 x 16 / 32: field_tile_kernel)
     const int bw = a.bin_w, bh = a.bin_h, cap = a.bin_cap;
     const int tiles_x = (W + bw - 1) / bw;
     const int txa = x0 / bw, txb = (x1 - 1) / bw;
@@ -859,255 +859,29 @@ __global__ void items_finalize_kernel(const ItemHdr* hdr, const double* partials
 }
 
 // ---------------------------------------------------------------------------
-// field reduce (gather) : lambda = eps + sum patches ; ll = sum x log lam - lam
+// full-field log-likelihood : lambda = eps + sum_s rate_s ; ll = sum x log lam - lam
 // ---------------------------------------------------------------------------
-// One WARP per half image tile (64 x 8 pixels; lane = 4 pixels x 4 rows), no
-// block-level synchronisation on the data path: the warp reads its tile's
-// source list, orders it by item index with shuffles (so that every pixel adds
-// its sources in source order -> bitwise reproducible), gathers the patches
-// and accumulates the Poisson terms in float64.
-#define FR_WARPS 4
 #define FT_BUCKETS 8
 struct FieldArgs {
   ImgPtrs imgs;
   int n_img;
   const ItemHdr* hdr;
-  const float* patches;
-  long long max_patch_px;
-  const int* tile_count;   // [n_img][max_tiles]
-  const int* tile_list;    // [n_img][max_tiles][TILE_LIST_CAP]
-  int* done;               // [n_img] blocks finished (zero on entry, reset on exit)
-  double* block_partials;  // [n_img][blocks_per_img]
+  const float* tab;        // component tables, n_items * TAB_STRIDE
+  const int* tile_count;   // [n_img][max_tiles] sources listed per 16 x 16 bin
+  const int* tile_list;    // [n_img][max_tiles][BIN_CAP] entries item * 64 + K, unordered
+  int2* order;             // [FT_BUCKETS][tiles_total] (bin id, list length) by weight class
+  int* sched;              // [FT_BUCKETS] class sizes, [FT_BUCKETS] work counter (zero on entry)
+  double* block_partials;  // [n_img][max_tiles] per-bin sums
   double* ll;              // [n_img]
-  int max_tiles, blocks_per_img;
-  // overflow fallback: the items of image i are item_base[i] + s*item_stride[i], s < n_src[i]
+  int max_tiles;           // 16 x 16 bins per image (largest image of the call)
+  int tiles_total;         // n_img * max_tiles
+  // list overflow fallback: the items of image i are item_base[i] + s*item_stride[i], s < n_src[i]
   int item_base[CG_MAX_IMAGES], item_stride[CG_MAX_IMAGES], n_src[CG_MAX_IMAGES];
   float* const* model;     // device array [n_img] of optional model outputs, or NULL
   const LogTable* logtab;  // precomputed at cg_init
-  // fused tile path (field_tile_kernel)
-  const float* tab;        // component tables, n_items * TAB_STRIDE
-  int2* order;             // [FT_BUCKETS][tiles_total] (bin id, list length) by weight class
-  int* sched;              // [FT_BUCKETS] class sizes, [FT_BUCKETS] work counter (zero on entry)
   Counters* cnt;
   int cull;
-  int tiles_total;         // n_img * max_tiles (fused path: max_tiles counts 16 x 16 bins)
 };
-
-__device__ __forceinline__ void gather_patch(float (&lam)[4][4], const float* patches,
-                                             long long max_patch_px, int item, int bx0, int bx1,
-                                             int by0, int by1, int x, int ybase) {
-  const int wb = bx1 - bx0;
-  const float* base = patches + (long long)item * max_patch_px - bx0;
-#pragma unroll
-  for (int r = 0; r < 4; ++r) {
-    const int y = ybase + r;
-    if (y >= by0 && y < by1) {
-      const float* rowp = base + (long long)(y - by0) * wb;
-#pragma unroll
-      for (int p = 0; p < 4; ++p) {
-        const int xx = x + p;
-        if (xx >= bx0 && xx < bx1) lam[r][p] += rowp[xx];
-      }
-    }
-  }
-}
-
-__global__ void __launch_bounds__(FR_WARPS * 32, 8) field_reduce_kernel(FieldArgs a) {
-  const int img = blockIdx.y;
-  const DevImage& im = *a.imgs.p[img];
-  const int H = im.H, W = im.W;
-  const int tiles_x = (W + TILE_W - 1) / TILE_W, tiles_y = (H + TILE_H - 1) / TILE_H;
-  const int n_tiles = tiles_x * tiles_y;
-  const int n_blocks = (2 * n_tiles + FR_WARPS - 1) / FR_WARPS;
-  if ((int)blockIdx.x >= n_blocks) return;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-
-  __shared__ double s_red[FR_WARPS];
-  const LogTable* const logt = a.logtab;
-
-  const int ht = blockIdx.x * FR_WARPS + warp;      // half-tile index
-  const int tile = ht >> 1;
-  double s = 0.0;
-  if (tile < n_tiles) {
-    const int tx = tile % tiles_x, ty = tile / tiles_x;
-    const int X0 = tx * TILE_W, Y0 = ty * TILE_H + (ht & 1) * (TILE_H / 2);
-    const int x = X0 + (lane & 15) * 4, ybase = Y0 + (lane >> 4) * 4;
-    const bool vec = (x + 3 < W) && ((W & 3) == 0) && (((uintptr_t)im.nelec & 15) == 0);
-
-    // the pixel counts do not depend on the list: issue their loads first
-    float d[4][4];
-#pragma unroll
-    for (int r = 0; r < 4; ++r) {
-      const int y = ybase + r;
-#pragma unroll
-      for (int p = 0; p < 4; ++p) d[r][p] = 0.f;
-      if (y < H && im.nelec) {
-        const float* rp = im.nelec + (long long)y * W + x;
-        if (vec) {
-          const float4 v = *reinterpret_cast<const float4*>(rp);
-          d[r][0] = v.x; d[r][1] = v.y; d[r][2] = v.z; d[r][3] = v.w;
-        } else {
-#pragma unroll
-          for (int p = 0; p < 4; ++p)
-            if (x + p < W) d[r][p] = rp[p];
-        }
-      }
-    }
-
-    const float eps = (float)im.epsilon;
-    float lam[4][4];
-#pragma unroll
-    for (int r = 0; r < 4; ++r)
-#pragma unroll
-      for (int p = 0; p < 4; ++p) lam[r][p] = eps;
-
-    const long long tslot = (long long)img * a.max_tiles + tile;
-    const int cnt = a.tile_count[tslot];
-    float* mdl = a.model ? a.model[img] : nullptr;
-    if (cnt == 0 && !mdl) {
-      // no source touches this tile: lambda = epsilon on every pixel, so the
-      // tile's terms are log(eps) * sum(x) - n * eps -- one log per warp
-      // instead of one per pixel (most of a Stripe-82 frame is empty sky)
-      double sd = 0.0;
-      int npx = 0;
-      if (im.nelec) {
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-          sd += ((double)d[r][0] + (double)d[r][1]) + ((double)d[r][2] + (double)d[r][3]);
-          if (ybase + r < H) npx += max(0, min(4, W - x));
-        }
-      }
-      s = fma(sd, log_accurate(eps, logt), -(double)npx * (double)eps);
-    } else if (cnt <= TILE_LIST_CAP) {
-      // lane j owns list entries j and j+32
-      int it0 = 0x7fffffff, it1 = 0x7fffffff;
-      int4 b0 = make_int4(0, 0, 0, 0), b1 = b0;
-      if (lane < cnt) {
-        it0 = a.tile_list[tslot * TILE_LIST_CAP + lane] >> 6;
-        b0 = *reinterpret_cast<const int4*>(a.hdr + it0);       // x0,x1,y0,y1
-      }
-      if (lane + 32 < cnt) {
-        it1 = a.tile_list[tslot * TILE_LIST_CAP + lane + 32] >> 6;
-        b1 = *reinterpret_cast<const int4*>(a.hdr + it1);
-      }
-      int r0 = 0, r1 = 0;
-      if (cnt > 1) {
-        const int n0 = min(cnt, 32);
-        for (int j = 0; j < n0; ++j) {
-          const int v = __shfl_sync(0xffffffffu, it0, j);
-          r0 += (v < it0); r1 += (v < it1);
-        }
-        for (int j = 0; j < cnt - 32; ++j) {
-          const int v = __shfl_sync(0xffffffffu, it1, j);
-          r0 += (v < it0); r1 += (v < it1);
-        }
-      }
-      for (int r = 0; r < cnt; ++r) {
-        const unsigned m0 = __ballot_sync(0xffffffffu, lane < cnt && r0 == r);
-        int item, bx0, bx1, by0, by1;
-        if (m0) {
-          const int sl = __ffs(m0) - 1;
-          item = __shfl_sync(0xffffffffu, it0, sl);
-          bx0 = __shfl_sync(0xffffffffu, b0.x, sl); bx1 = __shfl_sync(0xffffffffu, b0.y, sl);
-          by0 = __shfl_sync(0xffffffffu, b0.z, sl); by1 = __shfl_sync(0xffffffffu, b0.w, sl);
-        } else {
-          const unsigned m1 = __ballot_sync(0xffffffffu, lane + 32 < cnt && r1 == r);
-          const int sl = __ffs(m1) - 1;
-          item = __shfl_sync(0xffffffffu, it1, sl);
-          bx0 = __shfl_sync(0xffffffffu, b1.x, sl); bx1 = __shfl_sync(0xffffffffu, b1.y, sl);
-          by0 = __shfl_sync(0xffffffffu, b1.z, sl); by1 = __shfl_sync(0xffffffffu, b1.w, sl);
-        }
-        gather_patch(lam, a.patches, a.max_patch_px, item, bx0, bx1, by0, by1, x, ybase);
-      }
-    } else {
-      // more sources than a list holds: scan every source of this image, 32 at
-      // a time; hits are taken in lane order = source order
-      const int ns = a.n_src[img];
-      const int YA = Y0, YB = Y0 + TILE_H / 2;
-      for (int base = 0; base < ns; base += 32) {
-        const int sidx = base + lane;
-        bool hit = false;
-        int4 bx = make_int4(0, 0, 0, 0);
-        int item = 0;
-        if (sidx < ns) {
-          item = a.item_base[img] + sidx * a.item_stride[img];
-          const ItemHdr* hp = a.hdr + item;
-          bx = *reinterpret_cast<const int4*>(hp);
-          hit = (hp->K > 0) && (bx.y > bx.x) && (bx.w > bx.z) && bx.x < X0 + TILE_W && bx.y > X0 &&
-                bx.z < YB && bx.w > YA;
-        }
-        unsigned bal = __ballot_sync(0xffffffffu, hit);
-        while (bal) {
-          const int sl = __ffs(bal) - 1;
-          bal &= bal - 1;
-          gather_patch(lam, a.patches, a.max_patch_px, __shfl_sync(0xffffffffu, item, sl),
-                       __shfl_sync(0xffffffffu, bx.x, sl), __shfl_sync(0xffffffffu, bx.y, sl),
-                       __shfl_sync(0xffffffffu, bx.z, sl), __shfl_sync(0xffffffffu, bx.w, sl), x, ybase);
-        }
-      }
-    }
-
-    // sum x log(lam) and sum lam, both in float64 (two independent chains)
-    double slam = 0.0;
-    if (cnt == 0 && !mdl) {
-      // done above
-    } else if (x + 3 < W && ybase + 3 < H && im.nelec) {   // interior lane: no bounds tests
-#pragma unroll
-      for (int r = 0; r < 4; ++r)
-#pragma unroll
-        for (int p = 0; p < 4; ++p) {
-          s = fma((double)d[r][p], log_accurate(lam[r][p], logt), s);
-          slam += (double)lam[r][p];
-        }
-    } else if (im.nelec) {
-#pragma unroll
-      for (int r = 0; r < 4; ++r)
-#pragma unroll
-        for (int p = 0; p < 4; ++p)
-          if (ybase + r < H && x + p < W) {
-            s = fma((double)d[r][p], log_accurate(lam[r][p], logt), s);
-            slam += (double)lam[r][p];
-          }
-    }
-    s -= slam;
-    if (mdl) {
-#pragma unroll
-      for (int r = 0; r < 4; ++r)
-#pragma unroll
-        for (int p = 0; p < 4; ++p)
-          if (ybase + r < H && x + p < W) mdl[(long long)(ybase + r) * W + x + p] = lam[r][p];
-    }
-  }
-  s = warp_sum(s);
-  if (lane == 0) s_red[warp] = s;
-  __syncthreads();
-  if (tid == 0) {
-    double t = 0;
-#pragma unroll
-    for (int wv = 0; wv < FR_WARPS; ++wv) t += s_red[wv];
-    a.block_partials[(long long)img * a.blocks_per_img + blockIdx.x] = t;
-  }
-}
-
-// one block per image: fixed-shape tree over the block partials (a separate
-// launch is cheaper than a fence + atomic in every gather block)
-__global__ void __launch_bounds__(256) field_final_kernel(FieldArgs a) {
-  const int img = blockIdx.x;
-  const DevImage& im = *a.imgs.p[img];
-  const int n_tiles = ((im.W + TILE_W - 1) / TILE_W) * ((im.H + TILE_H - 1) / TILE_H);
-  const int n_blocks = (2 * n_tiles + FR_WARPS - 1) / FR_WARPS;
-  __shared__ double s_fin[256];
-  double t = 0;
-  const double* bp = a.block_partials + (long long)img * a.blocks_per_img;
-  for (int i = threadIdx.x; i < n_blocks; i += 256) t += bp[i];
-  s_fin[threadIdx.x] = t;
-  __syncthreads();
-  for (int o = 128; o > 0; o >>= 1) {
-    if (threadIdx.x < o) s_fin[threadIdx.x] += s_fin[threadIdx.x + o];
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) a.ll[img] = s_fin[0];
-}
 
 // ---------------------------------------------------------------------------
 // fused field path: render + gather + Poisson terms by IMAGE TILE
@@ -1311,7 +1085,8 @@ __device__ __forceinline__ void ft_source(const FieldArgs& a, int item, int K, i
   }
 }
 
-__global__ void __launch_bounds__(FT_THREADS, 4) field_tile_kernel(FieldArgs a) {
+// 3 CTAs x 8 warps per SM at 80 registers (no spills; 4 CTAs at 64 registers spill the pixel counts and measured slower)
+__global__ void __launch_bounds__(FT_THREADS, 3) field_tile_kernel(FieldArgs a) {
   __shared__ __align__(16) float s_wtab[FT_THREADS / 32][CG_MAX_COMP * 8];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float* const wtab = s_wtab[warp];
@@ -2103,7 +1878,7 @@ static int g_prof_n = 0;
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
-  size_t counters, hdr, tab, worklist, partials, item_ll, img_boxes, aux_offsets, tiles, patches;
+  size_t counters, hdr, tab, worklist, partials, item_ll, img_boxes, aux_offsets, tiles;
   size_t tile_count, done, tile_list, model_ptrs;   // full-field gather (tile_count and done are contiguous)
   size_t tile_zero_bytes, order;
   // second pass (float64 re-score)
@@ -2140,10 +1915,9 @@ static WsLayout ws_layout(long long n_items, long long max_patch_px, int with_pa
     L.tile_count = take(sizeof(int) * (size_t)n_tiles_total * BINS_PER_TILE);
     L.done = take(sizeof(int) * CG_MAX_IMAGES);
     L.tile_zero_bytes = (L.done + sizeof(int) * CG_MAX_IMAGES) - L.tile_count;
-    L.tile_list = take(sizeof(int) * (size_t)n_tiles_total * BINS_PER_TILE * BIN_CAP);   // >= n_tiles * TILE_LIST_CAP
+    L.tile_list = take(sizeof(int) * (size_t)n_tiles_total * BINS_PER_TILE * BIN_CAP);
     L.order = take(sizeof(int2) * (size_t)n_tiles_total * BINS_PER_TILE * FT_BUCKETS);
     L.model_ptrs = take(sizeof(float*) * CG_MAX_IMAGES);
-    L.patches = take(sizeof(float) * (size_t)(n_items * max_patch_px));
   }
   if (n_img_for_guard > 0) {
     L.guard_cap = GUARD_CAP;
@@ -2454,7 +2228,6 @@ static int fill_imgs(CgImage* const* imgs, int n_img, ImgPtrs* out) {
 }  // extern "C"
 
 static int g_cull = 1;
-static int g_field_fused = 1;   // CG_OPT_FIELD_FUSED
 
 // persistent grid: one CTA per resident slot
 template <typename real, int MODE>
@@ -2597,29 +2370,20 @@ int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off, const CgSou
   pa.n_img = n_img; pa.srcs = d_srcs; pa.n_src = h_src_off[n_fields]; pa.items = nullptr; pa.n_items = n_items;
   pa.default_flags = CG_ITEM_FLUX_BAND; pa.implicit_mode = 3; pa.bound_cap = bound_cap;
   pa.max_patch_px = max_patch_px; pa.hdr = (ItemHdr*)(base + L.hdr); pa.tab = base + L.tab;
-  pa.worklist = g_field_fused ? nullptr : (int2*)(base + L.worklist); pa.worklist_cap = L.worklist_cap; pa.cnt = cnt;
+  pa.worklist = nullptr; pa.worklist_cap = 0; pa.cnt = cnt;     // rendered by image bin, not by work list
   pa.filters = g_d_filters;
   pa.tile_count = (int*)(base + L.tile_count); pa.tile_list = (int*)(base + L.tile_list);
-  const int max_bins = max_tiles * BINS_PER_TILE;      // 16 x 16 bins of the fused path
-  pa.max_tiles = g_field_fused ? max_bins : max_tiles;
-  pa.bin_w = g_field_fused ? BIN_W : TILE_W; pa.bin_h = g_field_fused ? BIN_H : TILE_H;
-  pa.bin_cap = g_field_fused ? BIN_CAP : TILE_LIST_CAP;
+  const int max_bins = max_tiles * BINS_PER_TILE;
+  pa.max_tiles = max_bins;
+  pa.bin_w = BIN_W; pa.bin_h = BIN_H; pa.bin_cap = BIN_CAP;
   rc = run_prepare<float>(pa, st);
   if (rc) return rc;
-  RenderArgs ra;
-  memset(&ra, 0, sizeof ra);
-  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.worklist_cap = pa.worklist_cap; ra.cull = g_cull; ra.logtab = g_d_logtab; ra.cnt = cnt;
-  ra.patches = (float*)(base + L.patches); ra.max_patch_px = max_patch_px;
-  if (!g_field_fused) {
-    rc = run_render<float, MODE_PATCH>(ra, n_items, st);
-    if (rc) return rc;
-  }
-  fa.imgs = pa.imgs; fa.n_img = n_img; fa.hdr = pa.hdr;
-  fa.patches = ra.patches; fa.max_patch_px = max_patch_px;
-  fa.tile_count = pa.tile_count; fa.tile_list = pa.tile_list; fa.done = (int*)(base + L.done);
-  const int blocks_per_img = (2 * max_tiles + FR_WARPS - 1) / FR_WARPS;
-  fa.block_partials = (double*)(base + L.tiles); fa.max_tiles = max_tiles; fa.ll = d_ll;
-  fa.blocks_per_img = blocks_per_img; fa.logtab = g_d_logtab;
+  fa.imgs = pa.imgs; fa.n_img = n_img; fa.hdr = pa.hdr; fa.tab = (const float*)pa.tab;
+  fa.tile_count = pa.tile_count; fa.tile_list = pa.tile_list;
+  fa.order = (int2*)(base + L.order); fa.sched = (int*)(base + L.done);
+  fa.block_partials = (double*)(base + L.tiles); fa.ll = d_ll;
+  fa.max_tiles = max_bins; fa.tiles_total = max_bins * n_img;
+  fa.logtab = g_d_logtab; fa.cnt = cnt; fa.cull = g_cull;
   if (h_d_model) {
     bool any = false;
     for (int i = 0; i < n_img; ++i) any = any || h_d_model[i];
@@ -2628,27 +2392,14 @@ int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off, const CgSou
       fa.model = (float* const*)(base + L.model_ptrs);
     }
   }
-  if (g_field_fused) {
-    fa.tab = (const float*)pa.tab; fa.order = (int2*)(base + L.order); fa.sched = fa.done;
-    fa.cnt = cnt; fa.cull = g_cull; fa.max_tiles = max_bins; fa.tiles_total = max_bins * n_img;
-    static int per_sm = 0;
-    if (!per_sm && (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, field_tile_kernel, FT_THREADS, 0) !=
-                        cudaSuccess || per_sm < 1))
-      per_sm = 8;
-    bin_order_kernel<<<(fa.tiles_total + 255) / 256, 256, 0, st>>>(fa);
-    LAUNCH_CHECK();
-    const bool prof = prof_begin(st);
-    field_tile_kernel<<<g_sm_count * per_sm, FT_THREADS, 0, st>>>(fa);
-    prof_end(prof, st);
-    LAUNCH_CHECK();
-    field_tile_final_kernel<<<n_img, 1024, 0, st>>>(fa);
-    LAUNCH_CHECK();
-  } else {
-    field_reduce_kernel<<<dim3(blocks_per_img, n_img), FR_WARPS * 32, 0, st>>>(fa);
-    LAUNCH_CHECK();
-    field_final_kernel<<<n_img, 256, 0, st>>>(fa);
-    LAUNCH_CHECK();
-  }
+  bin_order_kernel<<<(fa.tiles_total + 255) / 256, 256, 0, st>>>(fa);
+  LAUNCH_CHECK();
+  const bool prof = prof_begin(st);
+  field_tile_kernel<<<g_sm_count * 3, FT_THREADS, 0, st>>>(fa);      // persistent: 3 CTAs per SM (launch bounds)
+  prof_end(prof, st);
+  LAUNCH_CHECK();
+  field_tile_final_kernel<<<n_img, 1024, 0, st>>>(fa);
+  LAUNCH_CHECK();
   g_last_counters = cnt;
   return CG_OK;
 }
@@ -2665,7 +2416,6 @@ int cg_field_loglik(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs,
 int cg_set_option(int32_t option, int32_t value) {
   switch (option) {
     case CG_OPT_CULL: g_cull = value ? 1 : 0; return CG_OK;
-    case CG_OPT_FIELD_FUSED: g_field_fused = value ? 1 : 0; return CG_OK;
     default: return fail(CG_EINVAL, "unknown option %d", option);
   }
 }

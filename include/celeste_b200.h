@@ -209,9 +209,6 @@ int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off,
  * components whose largest value over the warp's pixels is below 2^-27 of a
  * lower bound of the mixture there (bounded relative error K*2^-27 on a rate). */
 #define CG_OPT_CULL 1
-/* CG_OPT_FIELD_FUSED (default 1): cg_field(s)_loglik renders by image tile with
- * lambda kept in registers (field_tile_kernel); 0 = render patches, then gather. */
-#define CG_OPT_FIELD_FUSED 2
 int cg_set_option(int32_t option, int32_t value);
 
 /* Likelihood modes of cg_items_loglik */
