@@ -237,6 +237,8 @@ def main():
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     engine.init(local)
+    if os.environ.get("CG_CULL"):
+        engine.set_option(1, int(os.environ["CG_CULL"]))
     dev = engine.device()
     F = args.fields_per_gpu
 

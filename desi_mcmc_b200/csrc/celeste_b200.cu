@@ -868,7 +868,7 @@ struct FieldArgs {
   const ItemHdr* hdr;
   const float* tab;        // component tables, n_items * TAB_STRIDE
   const int* tile_count;   // [n_img][max_tiles] sources listed per 16 x 16 bin
-  const int* tile_list;    // [n_img][max_tiles][BIN_CAP] entries item * 64 + K, unordered
+  int* tile_list;          // [n_img][max_tiles][BIN_CAP] entries item * 64 + K (put in source order by bin_order_kernel)
   int2* order;             // [FT_BUCKETS][tiles_total] (bin id, list length) by weight class
   int* sched;              // [FT_BUCKETS] class sizes, [FT_BUCKETS] work counter (zero on entry)
   double* block_partials;  // [n_img][max_tiles] per-bin sums
@@ -936,8 +936,17 @@ __global__ void __launch_bounds__(256) bin_order_kernel(FieldArgs a) {
       if (cnt > BIN_CAP) {
         b = FT_BUCKETS - 1;
       } else {
+        // weigh the bin and put its (atomically appended, hence unordered) list
+        // into source order: the tile kernel then takes the entries as they lie
+        int* lst = a.tile_list + (long long)g * BIN_CAP;
         int w = 0;
-        for (int j = 0; j < cnt; ++j) w += a.tile_list[(long long)g * BIN_CAP + j] & 63;
+        for (int j = 0; j < cnt; ++j) {
+          const int key = lst[j];
+          w += key & 63;
+          int k = j - 1;
+          while (k >= 0 && lst[k] > key) { lst[k + 1] = lst[k]; --k; }
+          lst[k + 1] = key;
+        }
         b = ft_bucket(w);
       }
     }
@@ -1241,11 +1250,7 @@ __global__ void __launch_bounds__(FT_THREADS, 3) field_tile_kernel(FieldArgs a) 
         }
         const unsigned vm = __ballot_sync(0xffffffffu, valid);
         const int nv = __popc(vm);
-        int rk = __popc(vm & ((1u << lane) - 1u));               // scan: lane order = source order
-        if (!scan && nv > 1) {
-          rk = 0;
-          for (int j = 0; j < nv; ++j) rk += (__shfl_sync(0xffffffffu, e, j) < e);
-        }
+        const int rk = __popc(vm & ((1u << lane) - 1u));         // lane order = source order (sorted list / scan)
         for (int r = 0; r < nv; ++r) {
           const unsigned m = __ballot_sync(0xffffffffu, valid && rk == r);
           const int sl = __ffs(m) - 1;
