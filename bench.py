@@ -228,6 +228,11 @@ def main():
         run_reference(args, rank)
         return
 
+    # rank 0 prints exactly ONE line on stdout: library banners (NCCL's version
+    # line goes to fd 1) are diverted to stderr for the whole run
+    out = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
     import torch
     import torch.distributed as dist
     from desi_mcmc_b200 import engine, synth, _ffi
@@ -275,15 +280,20 @@ def main():
     stats = torch.zeros(64, dtype=torch.float64, device=dev)     # [sum ll, n_star, ...]
     n_star = float(sum(1 for fld in fields for s in fld["sources"] if s["a"] == 0))
 
-    sweep = engine.FieldSweep(sets, n_streams=args.streams)
+    # one float64 all-reduce per step (global log-likelihood + counts), enqueued
+    # behind the field sets and captured into the step's CUDA graph with them
+    template = torch.zeros(64, dtype=torch.float64, device=dev)
+    template[1] = n_star
+
+    def exchange():
+        stats.copy_(template)
+        stats[0:1] = torch.stack([fs.ll.sum() for fs in sets]).sum(0, keepdim=True)
+        dist.all_reduce(stats)
+
+    sweep = engine.FieldSweep(sets, n_streams=args.streams, after=exchange if world > 1 else None)
 
     def step_device():
         sweep.run()
-        if world > 1:
-            stats.zero_()
-            stats[0] = sum(fs.ll.sum() for fs in sets)
-            stats[1] = n_star
-            dist.all_reduce(stats)
 
     # evaluations per step (constant): count once per set
     evals_step, issued_step = 0, 0
@@ -328,7 +338,13 @@ def main():
 
     # ---- device-resident leg (the headline `value`): the captured step
     if not args.no_graph:
-        sweep.capture()
+        try:
+            sweep.capture()
+        except Exception as exc:                      # e.g. a collective that cannot be captured
+            sys.stderr.write("CUDA graph capture failed (%s); launching kernel by kernel\n" % exc)
+            sweep.graph = None
+            args.no_graph = True
+            torch.cuda.synchronize()
     for _ in range(args.warmup):
         step_device()
     barrier()
@@ -350,11 +366,6 @@ def main():
         sweep.run()
         for fs in sets:
             fs.h_ll.copy_(fs.ll, non_blocking=True)
-        if world > 1:
-            stats.zero_()
-            stats[0] = sum(fs.ll.sum() for fs in sets)
-            stats[1] = n_star
-            dist.all_reduce(stats)
         torch.cuda.current_stream().synchronize()
         return float(sum(fs.h_ll.sum() for fs in sets))
 
@@ -432,7 +443,8 @@ def main():
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = {k: v for k, v in cpu_baseline(fields[0], args.cpu_seconds).items()
                                     if k not in ("evals", "seconds")}
-        print(json.dumps(line))
+        out.write(json.dumps(line) + "\n")
+        out.flush()
     if world > 1:
         dist.destroy_process_group()
 

@@ -673,8 +673,12 @@ class FieldSweep(object):
     into the captured launches: call ``capture()`` again after ``set_sources``
     changed a count (parameter VALUES may change freely)."""
 
-    def __init__(self, sets: Sequence["FieldSet"], n_streams: int = 2):
+    def __init__(self, sets: Sequence["FieldSet"], n_streams: int = 2, after=None):
+        """after: optional callable enqueued on the current stream after the sets
+        of a step (e.g. the all-reduce of the sweep statistics); it is captured
+        into the graph with them."""
         self.sets = list(sets)
+        self.after = after
         self.n_streams = max(1, min(int(n_streams), len(self.sets)))
         self._side = [torch.cuda.Stream(device=device()) for _ in range(self.n_streams)] \
             if self.n_streams > 1 else []
@@ -685,6 +689,8 @@ class FieldSweep(object):
         if not self._side:
             for fs in self.sets:
                 fs.loglik_device()
+            if self.after is not None:
+                self.after()
             return
         cur = torch.cuda.current_stream()
         for s in self._side:
@@ -694,6 +700,8 @@ class FieldSweep(object):
                 fs.loglik_device()
         for s in self._side:
             cur.wait_stream(s)
+        if self.after is not None:
+            self.after()
 
     def capture(self):
         self._enqueue()                      # warm-up outside the capture (lazy occupancy queries)
