@@ -12,4 +12,8 @@ fast path; these exist so reference-side callers run unchanged.
   celeste_galaxy_conditionals <- CelestePy/celeste_galaxy_conditionals.py
   sources         <- CelestePy/sources.py (likelihood closures)
   planck          <- CelestePy/planck.py
+  celeste_sample_sources <- CelestePy/celeste_sample_sources.pyx (device photon allocation)
+  celeste_mcmc    <- CelestePy/celeste_mcmc.py (photon allocation entry point, star / galaxy conditionals)
+  models          <- CelestePy/models.py (CelesteBase / Celeste / Field: the live Gibbs sweep)
+  slicesample, hmc<- CelestePy/util/infer/{slicesample,hmc}.py (host control flow, device likelihoods)
 """

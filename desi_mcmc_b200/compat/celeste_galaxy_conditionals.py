@@ -87,11 +87,13 @@ def _cond_items(th, images, n_variants):
     return rec
 
 
-def galaxy_source_like_batch(ths, Z_s, images):
+def galaxy_source_like_batch(ths, Z_s, images, use_fp64=False):
     """galaxy_source_like (:15-42) for every row of ths in ONE launch: the
     conditional Poisson log-likelihood sum_n sum_m z log(lam) - lam with
     lam = flux_n (theta f_exp + (1-theta) f_dev) on the truncated footprint
-    of the Cython route.  Z_s[n] must be shaped like that footprint."""
+    of the Cython route.  Z_s[n] must be shaped like that footprint.
+    use_fp64: float64 tables / exp / log on the device -- needed when the values
+    are differenced at delta 1e-5 (galaxy_source_like_grad)."""
     ths = np.atleast_2d(np.asarray(ths, dtype=np.float64))
     P, n_img = ths.shape[0], len(images)
     rec = _cond_items(ths, images, P)
@@ -104,7 +106,7 @@ def galaxy_source_like_batch(ths, Z_s, images):
     offs[1:] = np.cumsum([z.size for z in zs])[:-1]
     aux = torch.from_numpy(np.concatenate(zs)).to(engine.device())
     ll, boxes = engine.items_loglik(images, rec, items, mode=_ffi.CG_LL_CONDITIONAL_SUM, aux=aux,
-                                    aux_offsets=offs)
+                                    aux_offsets=offs, use_fp64=use_fp64)
     for n in range(n_img):
         b = boxes[n]
         if (b["y1"] - b["y0"]) * (b["x1"] - b["x0"]) != zs[n].size:
@@ -141,6 +143,53 @@ def galaxy_source_like_grad(th, Z_s, images, check_overlap=True, unconstrained=F
         de = np.zeros(th.shape)
         de[th_i] = 1e-5
         variants += [th + de, th - de]
-    lls = galaxy_source_like_batch(np.array(variants), Z_s, images)
+    # float64 on the device: an fp32 likelihood of ~1e5 carries ~1e-2 of rounding noise,
+    # i.e. +-500 after division by 2e-5
+    lls = galaxy_source_like_batch(np.array(variants), Z_s, images, use_fp64=True)
     grad_RU = (lls[0::2] - lls[1::2]) / (2. * 1e-5)
     return np.concatenate([[grad_theta_s], grad_RU, np.array([grad_bs[b] for b in BANDS])])
+
+
+def gen_galaxy_prof_psf_image_bound(prof_type, R, u, img, ERROR=.01):
+    """:236-256: bounding radius of one profile convolved with the image PSF."""
+    from . import celeste_fast, mixture_profiles
+    from .bounding_box import calc_bounding_radius
+    prof = {'exp': mixture_profiles.get_exp_mixture(), 'dev': mixture_profiles.get_dev_mixture()}
+    assert prof_type in prof, "unknown galaxy profile type"
+    v_s = np.asarray(img.equa2pixel(u), dtype=np.float64)
+    R = np.asarray(R, dtype=np.float64)
+    weights, means, covars = celeste_fast.gen_galaxy_prof_psf_mixture_params(
+        W=np.dot(R, R.T), v_s=v_s, image_ws=img.weights, image_means=img.means,
+        image_covars=img.covars, gal_prof_amp=prof[prof_type].amp,
+        gal_prof_sigs=prof[prof_type].var[:, 0, 0])
+    return calc_bounding_radius(weights, means, covars, ERROR, center=v_s)
+
+
+# ---- drop-in prior probability functions (:262-275, util/like/like_list.py:18-27) ----
+def fast_inv_gamma_lnpdf(x, a0, b0):
+    if x <= 0.:
+        return -np.inf
+    return (-a0 - 1.) * np.log(x) - b0 / x
+
+
+def galaxy_shape_prior_unconstrained(logit_theta, log_sig, logit_phi, logit_rho):
+    return -(1. / 50.) * (logit_theta * logit_theta + log_sig * log_sig +
+                          logit_phi * logit_phi + logit_rho * logit_rho)
+
+
+def galaxy_shape_prior_constrained(theta, sig, phi, rho):
+    if theta <= 0. or theta >= 1. or sig <= 0. or phi <= 0. or phi >= np.pi or rho <= 0. or rho >= 1.:
+        return -np.inf
+    return fast_inv_gamma_lnpdf(sig * sig, a0=1., b0=1.)
+
+
+def constrain_params(th):
+    """:288-299."""
+    return 1. / (1. + np.exp(-th[0])), np.exp(th[1]), np.pi / (1. + np.exp(-th[2])), 1. / (1. + np.exp(-th[3]))
+
+
+def unconstrain_params(th_constrained):
+    """:301-313."""
+    return np.log(th_constrained[0] / (1. - th_constrained[0])), np.log(th_constrained[1]), \
+        np.log(th_constrained[2] / (np.pi - th_constrained[2])), \
+        np.log(th_constrained[3] / (1. - th_constrained[3]))

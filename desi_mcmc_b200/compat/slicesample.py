@@ -102,3 +102,68 @@ def slicesample(init_x, logprob, *logprob_args, **slice_sample_args):
     if scalar:
         return float(new_x[0]), new_llh
     return new_x, new_llh
+
+
+def slicesample_step_out(xx, llh_func, last_llh=None, step=1, step_out=True, x_l=None, x_r=None,
+                         lb=-np.inf, ub=np.inf):
+    """util/infer/slicesample.py:4-86: coordinate-wise slice sampler with
+    stepping out, dimensions in a random permutation.  Same draws from
+    numpy.random in the same order as the reference."""
+    xx = np.atleast_1d(np.asarray(xx, dtype=np.float64)).copy()
+    dims = xx.shape[0]
+    perm = list(range(dims))
+    np.random.shuffle(perm)
+    lb = np.broadcast_to(np.asarray(lb, dtype=np.float64), xx.shape)
+    ub = np.broadcast_to(np.asarray(ub, dtype=np.float64), xx.shape)
+    assert np.all(xx < ub), "xx (%s) >= ub (%s)" % (np.array_str(xx), np.array_str(ub))
+    assert np.all(xx > lb), "xx (%s) <= lb (%s)" % (np.array_str(xx), np.array_str(lb))
+    if np.isscalar(step):
+        step = np.tile(step, dims)
+    else:
+        step = np.asarray(step, dtype=np.float64)
+    if last_llh is None:
+        last_llh = llh_func(xx)
+    for d in perm:
+        llh0 = last_llh + np.log(np.random.rand())
+        rr = np.random.rand()
+        if x_l is None:
+            x_l = xx.copy()
+            x_l[d] = max(x_l[d] - rr * step[d], lb[d])
+        else:
+            x_l = np.atleast_1d(np.asarray(x_l, dtype=np.float64)).copy()
+            assert x_l.shape == xx.shape
+            assert np.all(x_l <= xx)
+        if x_r is None:
+            x_r = xx.copy()
+            x_r[d] = min(x_r[d] + (1 - rr) * step[d], ub[d])
+        else:
+            x_r = np.atleast_1d(np.asarray(x_r, dtype=np.float64)).copy()
+            assert x_r.shape == xx.shape
+            assert np.all(x_r >= xx)
+        if step_out:
+            llh_l = llh_func(x_l)
+            while llh_l > llh0 and x_l[d] > lb[d]:
+                x_l[d] = max(x_l[d] - step[d], lb[d])
+                llh_l = llh_func(x_l)
+            llh_r = llh_func(x_r)
+            while llh_r > llh0 and x_r[d] < ub[d]:
+                x_r[d] = min(x_r[d] + step[d], ub[d])
+                llh_r = llh_func(x_r)
+        assert np.isfinite(llh0)
+        x_cur = xx.copy()
+        while True:
+            xd = np.random.rand() * (x_r[d] - x_l[d]) + x_l[d]
+            x_cur[d] = xd
+            last_llh = llh_func(x_cur)
+            if last_llh > llh0:
+                xx[d] = xd
+                break
+            elif xd > xx[d]:
+                x_r[d] = xd
+            elif xd < xx[d]:
+                x_l[d] = xd
+            else:
+                raise Exception("Slice sampler shrank too far.")
+    if not np.isfinite(last_llh):
+        raise Exception("Likelihood is not finite at sampled point")
+    return xx, last_llh
