@@ -76,6 +76,12 @@ class CelesteBase(object):
         for src in self.srcs:
             src.resample()
 
+    def resample_sources_batched(self, seed=0):
+        """resample_sources with the likelihood evaluations of ALL sources in
+        one launch per slice-sampler round (sources.resample_sources_batched)."""
+        from .sources import resample_sources_batched
+        return resample_sources_batched(self.srcs, seed=seed)
+
     # ---- model image / likelihood (:88-108) -----------------------------------
     def render_model_image(self, fimg, xlim=None, ylim=None, exclude=None):
         """epsilon + sum of the sources' model patches on fimg (full frame, or

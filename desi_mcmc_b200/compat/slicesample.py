@@ -1,13 +1,22 @@
 """CelestePy/util/infer/slicesample.py:89-247: the slice sampler's control
 flow (host), drawing from numpy.random in the reference's order so that a
-seeded chain reproduces; `logprob` is a device likelihood."""
+seeded chain reproduces; `logprob` is a device likelihood.  The sampler is
+written once as a generator (slicesample_gen) so that many chains can be
+advanced in lock-step with one batched launch per round (run_lockstep)."""
 from __future__ import annotations
 
 import numpy as np
 import numpy.random as npr
 
 
-def slicesample(init_x, logprob, *logprob_args, **slice_sample_args):
+def slicesample_gen(init_x, **slice_sample_args):
+    """The sampler of slicesample() as a generator: it YIELDS every point whose
+    log-probability it needs and is SENT the value, and returns (new_x, new_llh).
+    One code path serves the sequential driver (slicesample) and the lock-step
+    driver (run_lockstep: many chains, one batched device launch per round).
+    `rng` (keyword) supplies rand / randn / shuffle; default numpy.random, the
+    reference's global stream."""
+    rng = slice_sample_args.get('rng', None) or npr
     sigma = slice_sample_args.get('sigma', 1.0)
     step_out = slice_sample_args.get('step_out', True)
     max_steps_out = slice_sample_args.get('max_steps_out', 1000)
@@ -18,8 +27,8 @@ def slicesample(init_x, logprob, *logprob_args, **slice_sample_args):
     lower_bound = slice_sample_args.get('lower_bound', -np.inf)
 
     def direction_slice(direction, init_x):
-        def dir_logprob(z):
-            return logprob(direction * z + init_x, *logprob_args)
+        def at(z):
+            return direction * z + init_x
 
         def acceptable(z, llh_s, L, U):
             while (U - L) > 1.1 * sigma:
@@ -29,39 +38,45 @@ def slicesample(init_x, logprob, *logprob_args, **slice_sample_args):
                     U = middle
                 else:
                     L = middle
-                if splits and llh_s >= dir_logprob(U) and llh_s >= dir_logprob(L):
-                    return False
+                if splits:                       # `and` chain of the reference, short-circuit kept
+                    if llh_s >= (yield at(U)):
+                        if llh_s >= (yield at(L)):
+                            return False
             return True
 
-        upper = sigma * npr.rand()
+        upper = sigma * rng.rand()
         lower = upper - sigma
-        llh_s = np.log(npr.rand()) + dir_logprob(0.0)
+        llh_s = np.log(rng.rand()) + (yield at(0.0))
         l_steps_out = 0
         u_steps_out = 0
         if step_out:
             if doubling_step:
-                while (dir_logprob(lower) > llh_s or dir_logprob(upper) > llh_s) and \
-                        (l_steps_out + u_steps_out) < max_steps_out:
-                    if npr.rand() < 0.5:
+                while True:
+                    out = (yield at(lower)) > llh_s
+                    if not out:
+                        out = (yield at(upper)) > llh_s
+                    if not (out and (l_steps_out + u_steps_out) < max_steps_out):
+                        break
+                    if rng.rand() < 0.5:
                         l_steps_out += 1
                         lower -= (upper - lower)
                     else:
                         u_steps_out += 1
                         upper += (upper - lower)
             else:
-                while dir_logprob(lower) > llh_s and l_steps_out < max_steps_out:
+                while (yield at(lower)) > llh_s and l_steps_out < max_steps_out:
                     l_steps_out += 1
                     lower -= sigma
-                while dir_logprob(upper) > llh_s and u_steps_out < max_steps_out:
+                while (yield at(upper)) > llh_s and u_steps_out < max_steps_out:
                     u_steps_out += 1
                     upper += sigma
         start_upper, start_lower = upper, lower
         while True:
-            new_z = (upper - lower) * npr.rand() + lower
-            new_llh = dir_logprob(new_z)
+            new_z = (upper - lower) * rng.rand() + lower
+            new_llh = yield at(new_z)
             if np.isnan(new_llh):
                 raise Exception("Slice sampler got a NaN")
-            if new_llh > llh_s and acceptable(new_z, llh_s, start_lower, start_upper):
+            if new_llh > llh_s and (yield from acceptable(new_z, llh_s, start_lower, start_upper)):
                 break
             elif new_z < 0:
                 lower = new_z
@@ -87,21 +102,61 @@ def slicesample(init_x, logprob, *logprob_args, **slice_sample_args):
     dims = init_x.shape[0]
     if compwise:
         ordering = list(range(dims))
-        npr.shuffle(ordering)
+        rng.shuffle(ordering)
         new_x = init_x.copy()
         for d in ordering:
             direction = np.zeros((dims))
             direction[d] = 1.0
-            new_x, new_llh = direction_slice(direction, new_x)
+            new_x, new_llh = yield from direction_slice(direction, new_x)
     else:
         new_x = init_x
         for d in range(numdir):
-            direction = npr.randn(dims)
+            direction = rng.randn(dims)
             direction = direction / np.sqrt(np.sum(direction ** 2))
-            new_x, new_llh = direction_slice(direction, new_x)
+            new_x, new_llh = yield from direction_slice(direction, new_x)
     if scalar:
         return float(new_x[0]), new_llh
     return new_x, new_llh
+
+
+def slicesample(init_x, logprob, *logprob_args, **slice_sample_args):
+    """util/infer/slicesample.py:89-247, same signature and keyword set."""
+    gen = slicesample_gen(init_x, **slice_sample_args)
+    try:
+        x = next(gen)
+        while True:
+            x = gen.send(logprob(x, *logprob_args))
+    except StopIteration as done:
+        return done.value
+
+
+def run_lockstep(gens, batch_logprob):
+    """Advance many sampler generators together: each round collects the point
+    every live chain is waiting on and evaluates them in ONE call
+    batch_logprob(indices, points) -> log-probabilities (a single device
+    launch for all chains of a field instead of one per chain).  Every chain
+    sees exactly the values, and draws exactly the random numbers, it would
+    see when driven alone.  Returns the generators' return values."""
+    results = [None] * len(gens)
+    pending = {}
+    for i, g in enumerate(gens):
+        try:
+            pending[i] = next(g)
+        except StopIteration as done:
+            results[i] = done.value
+    rounds = 0
+    while pending:
+        idx = sorted(pending)
+        lls = batch_logprob(idx, [pending[i] for i in idx])
+        rounds += 1
+        for i, ll in zip(idx, lls):
+            try:
+                pending[i] = gens[i].send(float(ll))
+            except StopIteration as done:
+                results[i] = done.value
+                del pending[i]
+    run_lockstep.last_rounds = rounds
+    return results
 
 
 def slicesample_step_out(xx, llh_func, last_llh=None, step=1, step_out=True, x_l=None, x_r=None,

@@ -158,10 +158,12 @@ class Source(object):
         return float(ll.sum().item())
 
     # ---- resampling ----------------------------------------------------------
-    def resample(self):
+    def resample(self, rng=None):
+        """:242-245.  rng: optional numpy RandomState for this source's draws
+        (default: the global numpy.random stream, as in the reference)."""
         assert len(self.sample_image_list) != 0, "resample source needs sampled images"
-        self.resample_fluxes()
-        self.resample_location()
+        self.resample_fluxes(rng=rng)
+        self.resample_location(rng=rng)
 
     def resample_type(self, proposal_fun=None):
         proposal_fun = self.propose_other_type_prior if proposal_fun is None else proposal_fun
@@ -195,31 +197,40 @@ class Source(object):
         return float(delta[0]) + (prop_logprior - curr_logprior) + \
             (logprob_reverse - logprob_proposal) + logdet
 
-    def resample_location(self, u=None):
+    def _location_slice_args(self, rng=None):
+        return dict(step=self.du / 5, step_out=False, upper_bound=self.u_upper,
+                    lower_bound=self.u_lower, rng=rng)
+
+    def resample_location(self, u=None, rng=None):
         """:308-319."""
         if u is None:
             u = self.params.u.copy()
         u, ll = slicesample(init_x=u, logprob=lambda u: self.location_likelihood(u),
-                            step=self.du / 5, step_out=False,
-                            upper_bound=self.u_upper, lower_bound=self.u_lower)
+                            **self._location_slice_args(rng))
         self.params.u = u
         return u
 
     def resample_shape(self):
         return
 
-    def resample_fluxes(self):
-        """:327-350: gamma conditional of the five fluxes."""
+    def resample_fluxes(self, rng=None, psf_sums_by_image=None):
+        """:327-350: gamma conditional of the five fluxes.  psf_sums_by_image:
+        optional precomputed sum of the unit-flux patch on every sample image
+        (resample_sources_batched renders them for all sources in one launch)."""
         a_0, b_0 = 5., .005
         band_counts = {b: 0 for b in BANDS}
         psf_sums = {b: 0 for b in BANDS}
-        for src_img, fits_img, pixel_grid in self.sample_image_list:
+        for k, (src_img, fits_img, pixel_grid) in enumerate(self.sample_image_list):
             band_counts[fits_img.band] += np.sum(np.array(src_img.data))
-            psf_ns, ylim, xlim = self.compute_scatter_on_pixels(fits_img)
-            psf_sums[fits_img.band] += np.sum(psf_ns) * fits_img.kappa / fits_img.calib
+            if psf_sums_by_image is None:
+                psf_ns, ylim, xlim = self.compute_scatter_on_pixels(fits_img)
+                tot = np.sum(psf_ns)
+            else:
+                tot = psf_sums_by_image[k]
+            psf_sums[fits_img.band] += tot * fits_img.kappa / fits_img.calib
         a_n = a_0 + np.array([band_counts[b] for b in BANDS])
         b_n = b_0 + np.array([psf_sums[b] for b in BANDS])
-        self.params.fluxes = np.random.gamma(a_n, 1. / b_n)
+        self.params.fluxes = (rng or np.random).gamma(a_n, 1. / b_n)
 
     def compute_scatter_on_pixels(self, fits_image, u=None, shape=None, xlim=None, ylim=None,
                                   pixel_grid=None, force_type=None):
@@ -285,3 +296,101 @@ def generate_background_patch(source, source_list, image):
     patches, _ = engine.render_patches([image], recs, items=items)
     bg = patches[:, :h * w].sum(dim=0).cpu().numpy().astype(np.float64).reshape(h, w)
     return bg + image.epsilon
+
+
+# ---------------------------------------------------------------------------
+# all sources of a model at once (no reference analogue: models.py:81-83 loops
+# `for src in srcs: src.resample()`, one likelihood launch per slice evaluation
+# per source; here every round of the lock-step slice samplers is ONE launch)
+# ---------------------------------------------------------------------------
+class BatchedConditional(object):
+    """Source.log_likelihood (:134-183) of MANY sources in one cg_items_loglik
+    launch.  Built once per sweep from the sources' sample_image_list."""
+
+    def __init__(self, srcs):
+        self.srcs = list(srcs)
+        imgs, index = [], {}
+        src_idx, img_idx, boxes, zs = [], [], [], []
+        for s, src in enumerate(self.srcs):
+            for samp_img, fits_img, _ in src.sample_image_list:
+                if id(fits_img) not in index:
+                    index[id(fits_img)] = len(imgs)
+                    imgs.append(fits_img)
+                src_idx.append(s)
+                img_idx.append(index[id(fits_img)])
+                boxes.append((int(samp_img.x0), int(samp_img.x1), int(samp_img.y0), int(samp_img.y1)))
+                zs.append(np.ascontiguousarray(np.asarray(samp_img.data), dtype=np.float32).ravel())
+        if len(imgs) > _ffi.CG_MAX_IMAGES:
+            raise ValueError("more than %d distinct images: batch field by field" % _ffi.CG_MAX_IMAGES)
+        self.imgs = imgs
+        self.src_idx = np.asarray(src_idx, dtype=np.int64)
+        n = len(zs)
+        self.offs = np.zeros(n, dtype=np.int64)
+        if n:
+            self.offs[1:] = np.cumsum([z.size for z in zs])[:-1]
+        self.aux = torch.from_numpy(np.concatenate(zs)).to(engine.device()) if n else None
+        self.items = engine.make_items(self.src_idx, np.asarray(img_idx), box=boxes, aux=np.arange(n)) \
+            if n else None
+        self.max_patch_px = max([z.size for z in zs] + [1])
+
+    def records(self, u=None):
+        """CgSource records of all sources; u: optional {source index: location}."""
+        recs = []
+        for s, src in enumerate(self.srcs):
+            recs.append(src._record(u=None if u is None or s not in u else u[s]))
+        return np.concatenate(recs)
+
+    def loglik(self, live, us):
+        """log_likelihood(u=us[k]) of source live[k], all in one launch."""
+        if self.items is None:
+            return np.zeros(len(live))
+        over = {s: np.asarray(x, dtype=np.float64) for s, x in zip(live, us)}
+        for s in live:
+            f = fluxes_of(self.srcs[s].params)
+            assert np.all(~np.isnan(f)), 'passing in NAN fluxes.'
+        recs = self.records(over)
+        sel = np.isin(self.src_idx, np.asarray(live))
+        ll, _ = engine.items_loglik(self.imgs, recs, self.items[sel], mode=_ffi.CG_LL_CONDITIONAL,
+                                    aux=self.aux, aux_offsets=self.offs, max_patch_px=self.max_patch_px)
+        per_src = np.bincount(self.src_idx[sel], weights=ll.cpu().numpy(), minlength=len(self.srcs))
+        return per_src[np.asarray(live)]
+
+    def unit_patch_sums(self):
+        """sum of the unit-flux patch of every (source, sample image) pair on
+        its natural footprint (compute_scatter_on_pixels with no limits), one
+        render launch; returned per source in sample_image_list order."""
+        if self.items is None:
+            return [[] for _ in self.srcs]
+        items = self.items.copy()
+        items["flags"] = _ffi.CG_ITEM_FLUX_UNIT
+        items["aux"] = -1
+        cap = min(max(im.shape[0] * im.shape[1] for im in self.imgs), 203 * 203)
+        patches, boxes = engine.render_patches(self.imgs, self.records(), items=items, max_patch_px=cap)
+        tot = patches.double().sum(dim=1).cpu().numpy()
+        out = [[] for _ in self.srcs]
+        for k, s in enumerate(self.src_idx):
+            out[s].append(float(tot[k]))
+        return out
+
+
+def resample_sources_batched(srcs, seed=0):
+    """Source.resample() for every source, with the likelihood evaluations of
+    all sources batched: one render launch for the flux conditionals, then the
+    location slice samplers advance in lock-step (slicesample.run_lockstep), one
+    cg_items_loglik launch per round.  Source s draws from RandomState(seed + s);
+    the result equals `src.resample(rng=RandomState(seed + s))` source by source."""
+    from .slicesample import run_lockstep, slicesample_gen
+    srcs = list(srcs)
+    for src in srcs:
+        assert len(src.sample_image_list) != 0, "resample source needs sampled images"
+    rngs = [np.random.RandomState(seed + s) for s in range(len(srcs))]
+    bc = BatchedConditional(srcs)
+    sums = bc.unit_patch_sums()
+    for src, rng, ps in zip(srcs, rngs, sums):
+        src.resample_fluxes(rng=rng, psf_sums_by_image=ps)
+    gens = [slicesample_gen(src.params.u.copy(), **src._location_slice_args(rng))
+            for src, rng in zip(srcs, rngs)]
+    res = run_lockstep(gens, bc.loglik)
+    for src, (u, ll) in zip(srcs, res):
+        src.params.u = u
+    return run_lockstep.last_rounds

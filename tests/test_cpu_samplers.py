@@ -59,3 +59,25 @@ def test_slicesample_direction_sampler_seeded():
     np.random.seed(7)
     b, lb = slicesample(np.array([.1, .2]), llh)
     assert np.array_equal(a, b) and la == lb == llh(a)
+
+
+def test_lockstep_equals_sequential_chains():
+    """run_lockstep (one batched evaluation per round for all chains) gives
+    every chain exactly the trace it has when driven alone with the same RNG."""
+    from desi_mcmc_b200.compat.slicesample import run_lockstep, slicesample_gen
+    mu, sd = np.array([.3, -1., 2.]), np.array([.2, 1.5, .7])
+    f = lambda x: float(-.5 * np.sum(((x - mu) / sd) ** 2))
+    calls = []
+
+    def batch(idx, xs):
+        calls.append(len(idx))
+        return [f(x) for x in xs]
+
+    for kw in (dict(), dict(compwise=False, numdir=3), dict(step_out=False, upper_bound=np.full(3, 9.),
+                                                          lower_bound=np.full(3, -9.))):
+        gens = [slicesample_gen(np.zeros(3), rng=np.random.RandomState(10 + i), **kw) for i in range(9)]
+        res = run_lockstep(gens, batch)
+        for i in range(9):
+            x, l = slicesample(np.zeros(3), f, rng=np.random.RandomState(10 + i), **kw)
+            assert np.array_equal(x, res[i][0]) and l == res[i][1]
+    assert max(calls) == 9 and len(calls) < sum(calls) / 3      # rounds are shared by the chains

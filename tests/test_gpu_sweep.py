@@ -159,3 +159,34 @@ def test_hmc_galaxy_step_runs_on_device_gradients(engine, oracle):
     assert p.shape == (11,) and np.all(np.isfinite(p))
     th1 = np.concatenate(([g.theta, g.sigma, g.phi, g.rho], g.u, [g.fluxes[b] for b in "ugriz"]))
     assert np.all(np.isfinite(th1)) and np.isfinite(gal.galaxy_source_like(th1, Z, gimgs)) and np.isfinite(ll0)
+
+
+def test_batched_resample_equals_per_source_resample(engine, oracle):
+    """All sources advanced in lock-step (one launch per slice round) end in the
+    state the reference's per-source loop reaches with the same per-source RNG."""
+    from desi_mcmc_b200.compat import models
+    from desi_mcmc_b200.compat.slicesample import run_lockstep
+
+    def build():
+        field = synth.make_field(91, H=96, W=128, n_src=12, star_frac=.5, margin=12)
+        nelec = hp.simulate_nelec(oracle, field, 9)
+        gimgs = hp.gpu_images(engine, field, nelec)
+        m = models.Celeste()
+        m.add_field({im.band: im for im in gimgs})
+        m.initialize_sources(init_src_params=hp.gpu_sources(engine, field))
+        m.field_list[0].resample_photons(m.srcs, random_state=np.random.RandomState(21))
+        return m
+
+    a, b = build(), build()
+    for s, src in enumerate(a.srcs):
+        src.resample(rng=np.random.RandomState(100 + s))
+    engine.launch_count(reset=True)
+    rounds = b.resample_sources_batched(seed=100)
+    launches = engine.launch_count()
+    for sa, sb in zip(a.srcs, b.srcs):
+        assert np.allclose(sa.params.fluxes, sb.params.fluxes, rtol=1e-12, atol=0)
+        assert np.allclose(sa.params.u, sb.params.u, rtol=0, atol=1e-13)
+        assert not np.array_equal(sb.params.u, sb.u_lower + .0025)     # the chain moved
+    # 12 chains shared their rounds: far fewer launches than 12 separate samplers need
+    assert rounds == run_lockstep.last_rounds and launches <= 4 * (rounds + 2)
+    print("lock-step rounds", rounds, "kernel launches", launches)
