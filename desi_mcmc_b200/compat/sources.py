@@ -333,22 +333,32 @@ class BatchedConditional(object):
             if n else None
         self.max_patch_px = max([z.size for z in zs] + [1])
 
+    def refresh(self):
+        """Re-pack the sources' current parameters (call after they changed)."""
+        self._base = np.concatenate([src._record() for src in self.srcs])
+        return self._base
+
     def records(self, u=None):
-        """CgSource records of all sources; u: optional {source index: location}."""
-        recs = []
-        for s, src in enumerate(self.srcs):
-            recs.append(src._record(u=None if u is None or s not in u else u[s]))
-        return np.concatenate(recs)
+        """CgSource records of all sources; u: optional {source index: location}.
+        Only the location column differs from the packed base, as in
+        Source._record(u=...)."""
+        base = getattr(self, "_base", None)
+        if base is None:
+            base = self.refresh()
+        if not u:
+            return base
+        recs = base.copy()
+        idx = np.fromiter(u.keys(), dtype=np.int64, count=len(u))
+        recs["u"][idx] = np.asarray(list(u.values()), dtype=np.float64)
+        return recs
 
     def loglik(self, live, us):
         """log_likelihood(u=us[k]) of source live[k], all in one launch."""
         if self.items is None:
             return np.zeros(len(live))
         over = {s: np.asarray(x, dtype=np.float64) for s, x in zip(live, us)}
-        for s in live:
-            f = fluxes_of(self.srcs[s].params)
-            assert np.all(~np.isnan(f)), 'passing in NAN fluxes.'
         recs = self.records(over)
+        assert np.all(~np.isnan(recs["flux"])), 'passing in NAN fluxes.'   # :140
         sel = np.isin(self.src_idx, np.asarray(live))
         ll, _ = engine.items_loglik(self.imgs, recs, self.items[sel], mode=_ffi.CG_LL_CONDITIONAL,
                                     aux=self.aux, aux_offsets=self.offs, max_patch_px=self.max_patch_px)
@@ -388,6 +398,7 @@ def resample_sources_batched(srcs, seed=0):
     sums = bc.unit_patch_sums()
     for src, rng, ps in zip(srcs, rngs, sums):
         src.resample_fluxes(rng=rng, psf_sums_by_image=ps)
+    bc.refresh()
     gens = [slicesample_gen(src.params.u.copy(), **src._location_slice_args(rng))
             for src, rng in zip(srcs, rngs)]
     res = run_lockstep(gens, bc.loglik)

@@ -905,7 +905,12 @@ struct FieldArgs {
 #define BIN_H 16
 #define BIN_CAP 32
 #define BINS_PER_TILE ((TILE_W / BIN_W) * (TILE_H / BIN_H))
+#ifndef FT_THREADS
 #define FT_THREADS 256
+#endif
+#ifndef FT_MINB
+#define FT_MINB 3
+#endif
 #define FT_CHUNK 8
 #define FT_LIGHT 2          // classes below this are latency-bound (no galaxy in the bin)
 // bins per claimed work unit by weight class: heavy bins one at a time (balance), sky in bulk
@@ -1014,33 +1019,53 @@ __device__ __forceinline__ int ft_cull(const float* gtab, int K, int lane, float
 }
 
 // evaluate the compacted mixture (8 floats per component in the warp's shared
-// table: one 16-byte + one 8-byte load) at the lane's pixels: two rows / one row
+// table: one 16-byte + one 8-byte load) at the lane's pixels: two rows / one row.
+// The table entry of component k+1 is loaded before component k is evaluated
+// (the table has one spare row, so the last prefetch needs no predicate).
 __device__ __forceinline__ void ft_eval2(const float* tb, int n, float y0l, float y1l,
                                          const float (&xl)[4], float (&acc0)[4], float (&acc1)[4]) {
+  float4 t0 = *reinterpret_cast<const float4*>(tb);      // A, B, C, b10
+  float2 t1 = *reinterpret_cast<const float2*>(tb + 4);  // c01, c00
 #pragma unroll 2
-  for (int k = 0; k < n; ++k, tb += 8) {
-    const float4 t0 = *reinterpret_cast<const float4*>(tb);      // A, B, C, b10
-    const float2 t1 = *reinterpret_cast<const float2*>(tb + 4);  // c01, c00
+  for (int k = 0; k < n; ++k) {
+    tb += 8;
+    const float4 n0 = *reinterpret_cast<const float4*>(tb);
+    const float2 n1 = *reinterpret_cast<const float2*>(tb + 4);
     const float b1a = fmaf(t0.y, y0l, t0.w), b1b = fmaf(t0.y, y1l, t0.w);
     const float c1a = fmaf(fmaf(t0.z, y0l, t1.x), y0l, t1.y);
     const float c1b = fmaf(fmaf(t0.z, y1l, t1.x), y1l, t1.y);
+    float q[8];
 #pragma unroll
     for (int p = 0; p < 4; ++p) {
-      acc0[p] += ex2_approx(fmaf(fmaf(t0.x, xl[p], b1a), xl[p], c1a));
-      acc1[p] += ex2_approx(fmaf(fmaf(t0.x, xl[p], b1b), xl[p], c1b));
+      q[p] = fmaf(fmaf(t0.x, xl[p], b1a), xl[p], c1a);
+      q[4 + p] = fmaf(fmaf(t0.x, xl[p], b1b), xl[p], c1b);
     }
+#pragma unroll
+    for (int p = 0; p < 8; ++p) q[p] = ex2_approx(q[p]);
+#pragma unroll
+    for (int p = 0; p < 4; ++p) { acc0[p] += q[p]; acc1[p] += q[4 + p]; }
+    t0 = n0; t1 = n1;
   }
 }
 __device__ __forceinline__ void ft_eval1(const float* tb, int n, float yl,
                                          const float (&xl)[4], float (&acc)[4]) {
-#pragma unroll 4
-  for (int k = 0; k < n; ++k, tb += 8) {
-    const float4 t0 = *reinterpret_cast<const float4*>(tb);
-    const float2 t1 = *reinterpret_cast<const float2*>(tb + 4);
+  float4 t0 = *reinterpret_cast<const float4*>(tb);
+  float2 t1 = *reinterpret_cast<const float2*>(tb + 4);
+#pragma unroll 2
+  for (int k = 0; k < n; ++k) {
+    tb += 8;
+    const float4 n0 = *reinterpret_cast<const float4*>(tb);
+    const float2 n1 = *reinterpret_cast<const float2*>(tb + 4);
     const float b1 = fmaf(t0.y, yl, t0.w);
     const float c1 = fmaf(fmaf(t0.z, yl, t1.x), yl, t1.y);
+    float q[4];
 #pragma unroll
-    for (int p = 0; p < 4; ++p) acc[p] += ex2_approx(fmaf(fmaf(t0.x, xl[p], b1), xl[p], c1));
+    for (int p = 0; p < 4; ++p) q[p] = fmaf(fmaf(t0.x, xl[p], b1), xl[p], c1);
+#pragma unroll
+    for (int p = 0; p < 4; ++p) q[p] = ex2_approx(q[p]);
+#pragma unroll
+    for (int p = 0; p < 4; ++p) acc[p] += q[p];
+    t0 = n0; t1 = n1;
   }
 }
 
@@ -1095,8 +1120,8 @@ __device__ __forceinline__ void ft_source(const FieldArgs& a, int item, int K, i
 }
 
 // 3 CTAs x 8 warps per SM at 80 registers (no spills; 4 CTAs at 64 registers spill the pixel counts and measured slower)
-__global__ void __launch_bounds__(FT_THREADS, 3) field_tile_kernel(FieldArgs a) {
-  __shared__ __align__(16) float s_wtab[FT_THREADS / 32][CG_MAX_COMP * 8];
+__global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldArgs a) {
+  __shared__ __align__(16) float s_wtab[FT_THREADS / 32][(CG_MAX_COMP + 1) * 8];   // + the prefetch row
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float* const wtab = s_wtab[warp];
   const LogTable* const logt = a.logtab;
@@ -2400,7 +2425,7 @@ int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off, const CgSou
   bin_order_kernel<<<(fa.tiles_total + 255) / 256, 256, 0, st>>>(fa);
   LAUNCH_CHECK();
   const bool prof = prof_begin(st);
-  field_tile_kernel<<<g_sm_count * 3, FT_THREADS, 0, st>>>(fa);      // persistent: 3 CTAs per SM (launch bounds)
+  field_tile_kernel<<<g_sm_count * FT_MINB, FT_THREADS, 0, st>>>(fa);      // persistent: FT_MINB CTAs per SM (launch bounds)
   prof_end(prof, st);
   LAUNCH_CHECK();
   field_tile_final_kernel<<<n_img, 1024, 0, st>>>(fa);
