@@ -110,6 +110,8 @@ PROTOTYPES = {
     "cg_binomial_draws": (C.c_int, [_i64, _dbl, C.c_uint64, _i64, _vp, _vp]),
     "cg_planck_fluxes": (C.c_int, [_vp, _vp, _i64, _vp, _vp]),
     "cg_eigen_fluxes": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp]),
+    "cg_mog_logpdf": (C.c_int, [_vp, _i64, _i32, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp]),
+    "cg_prior_stats": (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _vp]),
     "cg_launch_count": (_i64, [C.c_int]),
     "cg_last_eval_count": (_i64, [_vp]),
     "cg_last_issued_count": (_i64, [_vp]),

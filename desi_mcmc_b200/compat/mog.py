@@ -65,9 +65,18 @@ class MixtureOfGaussians(object):
 
     def logpdf(self, x):
         x = np.asarray(x, dtype=np.float64)
+        if self.D != 2:
+            # priors (D = 1, 3, 5): float64 mog_loglike on the device, :61-63 -> :5-21
+            return engine.mog_logpdf(x, self.means, self.icovs, self.dets, self.pis)
         with np.errstate(divide="ignore"):
             lp = np.log(_gmm_device(np.atleast_2d(x), self.pis, self.means, self.covs))
         return lp[0] if x.ndim == 1 else lp
+
+    def responsibilities(self, x):
+        """logpdf and r_nk = p(k | x_n) (device tensor [N, K]) -- the E-step of
+        the prior refit, whose sufficient statistics go into the sweep all-reduce."""
+        return engine.mog_logpdf(np.asarray(x, dtype=np.float64), self.means, self.icovs, self.dets,
+                                 self.pis, return_resp=True)
 
     def pdf(self, x):
         x = np.asarray(x, dtype=np.float64)

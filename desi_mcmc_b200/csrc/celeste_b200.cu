@@ -1583,6 +1583,97 @@ __global__ void __launch_bounds__(256) sum_partials_kernel(const double* partial
 }
 
 // ---------------------------------------------------------------------------
+// N3: empirical priors (util/dists/mog.py:5-21, flux_prior.py) and their
+// sufficient statistics
+// ---------------------------------------------------------------------------
+// one warp per point; lane k (and k + 32, ...) owns mixture component k
+__global__ void __launch_bounds__(128) mog_logpdf_kernel(const double* x, long long N, int D,
+                                                         const double* means, const double* icovs,
+                                                         const double* dets, const double* pis, int K,
+                                                         double* logp, double* resp) {
+  const int lane = threadIdx.x & 31;
+  const long long n = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (n >= N) return;
+  double xv[CG_MOG_MAX_DIM];
+  for (int d = 0; d < D; ++d) xv[d] = x[n * D + d];
+  double mx = -INFINITY;
+  for (int k = lane; k < K; k += 32) {
+    double c[CG_MOG_MAX_DIM];
+    for (int d = 0; d < D; ++d) c[d] = xv[d] - means[k * D + d];
+    double q = 0.0;                       // solved_m = sum_j icov[j][m] c_j ; q = sum_m solved_m c_m (mog.py:15-16)
+    for (int m = 0; m < D; ++m) {
+      double sm = 0.0;
+      for (int j = 0; j < D; ++j) sm += icovs[((long long)k * D + j) * D + m] * c[j];
+      q += sm * c[m];
+    }
+    const double lp = -0.5 * q - LOG2PI_D - 0.5 * log(dets[k]) + log(pis[k]);
+    if (resp) resp[n * K + k] = lp;       // finished below
+    mx = fmax(mx, lp);
+  }
+  mx = warp_max(mx);
+  double se = 0.0;
+  // second pass: exp(lp - max); lp is recomputed from resp when stored, else from scratch
+  for (int k = lane; k < K; k += 32) {
+    double lp;
+    if (resp) {
+      lp = resp[n * K + k];
+    } else {
+      double c[CG_MOG_MAX_DIM];
+      for (int d = 0; d < D; ++d) c[d] = xv[d] - means[k * D + d];
+      double q = 0.0;
+      for (int m = 0; m < D; ++m) {
+        double sm = 0.0;
+        for (int j = 0; j < D; ++j) sm += icovs[((long long)k * D + j) * D + m] * c[j];
+        q += sm * c[m];
+      }
+      lp = -0.5 * q - LOG2PI_D - 0.5 * log(dets[k]) + log(pis[k]);
+    }
+    se += (mx == -INFINITY) ? 0.0 : exp(lp - mx);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) se += __shfl_xor_sync(0xffffffffu, se, o);
+  const double lse = (mx == -INFINITY) ? -INFINITY : mx + log(se);
+  if (lane == 0) logp[n] = lse;
+  if (resp)
+    for (int k = lane; k < K; k += 32) resp[n * K + k] = exp(resp[n * K + k] - lse);
+}
+
+// one block per output entry e of [K | K*D | K*D(D+1)/2]: fixed-shape tree over the points
+__global__ void __launch_bounds__(256) prior_stats_kernel(const double* resp, const double* c, long long N,
+                                                          int K, int D, double* out) {
+  const int T = D * (D + 1) / 2;
+  const int e = blockIdx.x;
+  int k, a = -1, b = -1;
+  if (e < K) {
+    k = e;
+  } else if (e < K + K * D) {
+    k = (e - K) / D; a = (e - K) % D;
+  } else {
+    const int r = e - K - K * D;
+    k = r / T;
+    int t = r % T;
+    a = 0;
+    while (t >= D - a) { t -= D - a; ++a; }      // upper triangle, row-major (np.triu_indices)
+    b = a + t;
+  }
+  double s = 0.0;
+  for (long long n = threadIdx.x; n < N; n += 256) {
+    double v = resp[n * K + k];
+    if (a >= 0) v *= c[n * D + a];
+    if (b >= 0) v *= c[n * D + b];
+    s += v;
+  }
+  __shared__ double s_red[256];
+  s_red[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) s_red[threadIdx.x] += s_red[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[e] = s_red[0];
+}
+
+// ---------------------------------------------------------------------------
 // N1: photon allocation (celeste_sample_sources.pyx:61-156)
 // ---------------------------------------------------------------------------
 // Counter-based generator (Philox-4x32, 10 rounds; Salmon et al. 2011): every
@@ -2695,6 +2786,28 @@ int cg_eigen_fluxes(const double* d_z, const double* d_w, const double* d_m, con
 }
 
 // ---- instrumentation -------------------------------------------------------------
+int cg_mog_logpdf(const double* d_x, int64_t N, int32_t D, const double* d_means, const double* d_icovs,
+                  const double* d_dets, const double* d_pis, int32_t K, double* d_logp, double* d_resp,
+                  void* stream) {
+  NEED_INIT();
+  if (N < 0 || K < 1 || D < 1 || D > CG_MOG_MAX_DIM) return fail(CG_EINVAL, "cg_mog_logpdf: need N >= 0, K >= 1, 1 <= D <= %d", CG_MOG_MAX_DIM);
+  if (N == 0) return CG_OK;
+  mog_logpdf_kernel<<<(unsigned)((N + 3) / 4), 128, 0, (cudaStream_t)stream>>>(d_x, N, D, d_means, d_icovs, d_dets,
+                                                                              d_pis, K, d_logp, d_resp);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
+int cg_prior_stats(const double* d_resp, const double* d_c, int64_t N, int32_t K, int32_t D, double* d_out,
+                   void* stream) {
+  NEED_INIT();
+  if (N < 0 || K < 1 || D < 1 || D > CG_MOG_MAX_DIM) return fail(CG_EINVAL, "cg_prior_stats: need N >= 0, K >= 1, 1 <= D <= %d", CG_MOG_MAX_DIM);
+  const int entries = K * (1 + D + D * (D + 1) / 2);
+  prior_stats_kernel<<<entries, 256, 0, (cudaStream_t)stream>>>(d_resp, d_c, N, K, D, d_out);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
 int cg_profile_render(int enable) {
   NEED_INIT();
   if (enable && g_prof_ev.empty()) {

@@ -92,6 +92,14 @@ class SweepStats(object):
         o = 8 + which * self.block
         self.vec[o:o + self.block] += torch.from_numpy(flat).to(self.vec.device)
 
+    def add_prior_stats_device(self, which: int, block: torch.Tensor):
+        """block: engine.prior_sufficient_stats(resp, colors) -- the same
+        [s0 | s1 | s2] layout, computed on the device (cg_prior_stats)."""
+        if block.numel() != self.block:
+            raise ValueError("prior block has %d entries, expected %d" % (block.numel(), self.block))
+        o = 8 + which * self.block
+        self.vec[o:o + self.block] += block.to(self.vec.device)
+
     def prior_stats(self, which: int):
         o = 8 + which * self.block
         v = self.vec[o:o + self.block].cpu().numpy()

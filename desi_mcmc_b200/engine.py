@@ -888,3 +888,43 @@ def eigen_fluxes(z, w, m, B, lam0, fluxes=None, fluxes_ivar=None):
                                 d_iv.data_ptr() if d_iv is not None else None,
                                 mu.data_ptr(), ll.data_ptr() if ll is not None else None, stream_ptr()))
     return mu.cpu().numpy(), (ll.cpu().numpy() if ll is not None else None)
+
+
+# ---------------------------------------------------------------------------
+# N3: empirical priors (util/dists/mog.py, flux_prior.py) on the device
+# ---------------------------------------------------------------------------
+def mog_logpdf(x, means, icovs, dets, pis, return_resp: bool = False):
+    """mog_loglike (util/dists/mog.py:5-21) for D-dimensional points, float64.
+    x [N, D] (or [D]); returns log-densities [N] (and responsibilities [N, K])."""
+    x = np.asarray(x, dtype=np.float64)
+    one = x.ndim == 1
+    xx = np.atleast_2d(x)
+    means = np.ascontiguousarray(means, dtype=np.float64)
+    K, D = means.shape
+    if xx.shape[1] != D:
+        raise ValueError("x and means disagree on the dimension")
+    dev = device()
+    d = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(dev)
+    d_x, d_m, d_i, d_d, d_p = d(xx), d(means), d(icovs), d(dets), d(pis)
+    N = xx.shape[0]
+    logp = torch.zeros(max(N, 1), dtype=torch.float64, device=dev)
+    resp = torch.zeros((max(N, 1), K), dtype=torch.float64, device=dev) if return_resp else None
+    check(lib().cg_mog_logpdf(d_x.data_ptr(), N, D, d_m.data_ptr(), d_i.data_ptr(), d_d.data_ptr(),
+                              d_p.data_ptr(), K, logp.data_ptr(),
+                              resp.data_ptr() if resp is not None else None, stream_ptr()))
+    out = logp[:N].cpu().numpy()
+    if one:
+        out = out[0]
+    return (out, resp[:N]) if return_resp else out
+
+
+def prior_sufficient_stats(resp: torch.Tensor, colors) -> torch.Tensor:
+    """[sum r_k | sum r_k c | sum r_k c c^T (upper triangle)] over the points:
+    the block of dist.SweepStats a rank contributes for one prior (device tensor)."""
+    dev = device()
+    c = torch.from_numpy(np.ascontiguousarray(np.atleast_2d(colors), dtype=np.float64)).to(dev)
+    N, K = resp.shape
+    D = c.shape[1]
+    out = torch.zeros(K * (1 + D + D * (D + 1) // 2), dtype=torch.float64, device=dev)
+    check(lib().cg_prior_stats(resp.data_ptr(), c.data_ptr(), N, K, D, out.data_ptr(), stream_ptr()))
+    return out

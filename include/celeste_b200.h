@@ -289,6 +289,24 @@ int cg_eigen_fluxes(const double* d_z, const double* d_w, const double* d_m,
                     const double* d_fluxes, const double* d_fluxes_ivar,
                     double* d_mu, double* d_ll, void* stream);
 
+/* ---- N3: empirical priors, util/dists/mog.py:5-21,38-67, flux_prior.py:4-93 - */
+#define CG_MOG_MAX_DIM 8
+/* logp[n] = logsumexp_k( -0.5 (x_n-mu_k)^T icov_k (x_n-mu_k) - log(2 pi)
+ *                        - 0.5 log(det_k) + log(pi_k) )      (mog_loglike, as written:
+ * the -log(2 pi) term does not scale with D).  x [N][D], means [K][D], icovs
+ * [K][D][D], dets [K], pis [K]; D <= CG_MOG_MAX_DIM; float64 device arrays.
+ * d_resp (optional, [N][K]) receives the responsibilities exp(logprob_nk - logp_n). */
+int cg_mog_logpdf(const double* d_x, int64_t N, int32_t D,
+                  const double* d_means, const double* d_icovs, const double* d_dets,
+                  const double* d_pis, int32_t K, double* d_logp, double* d_resp, void* stream);
+/* Sufficient statistics of a MoG prior over the sources of this rank -- the
+ * vector dist.SweepStats all-reduces (the M-step inputs of
+ * experiments/empirical_priors/make_source_priors.py:76-110):
+ *   out = [ sum_n r_nk (K) | sum_n r_nk c_n (K x D) | sum_n r_nk c_n c_n^T (K x D(D+1)/2, upper triangle) ]
+ * resp [N][K], c [N][D].  Fixed-shape float64 tree per entry (bitwise reproducible). */
+int cg_prior_stats(const double* d_resp, const double* d_c, int64_t N, int32_t K, int32_t D,
+                   double* d_out, void* stream);
+
 /* ---- instrumentation ------------------------------------------------------ */
 /* Number of kernels launched by this library since cg_init (or last reset). */
 int64_t cg_launch_count(int reset);

@@ -851,3 +851,51 @@ def galaxy_source_like_grad(th, Z_s, images):
         dell = galaxy_source_like(th + de, Z_s, images) - galaxy_source_like(th - de, Z_s, images)
         grad_RU[i] = dell / (2. * de[th_i])
     return np.concatenate([[grad_theta_s], grad_RU, np.array([grad_bs[b] for b in BANDS])])
+
+
+# --------------------------------------------------------------------------
+# util/dists/flux_prior.py:4-93 and the prior refit's sufficient statistics
+# (experiments/empirical_priors/make_source_priors.py:76-110)
+# --------------------------------------------------------------------------
+FLUX_COLOR_A = np.zeros((5, 5))
+FLUX_COLOR_A[0, 0] = FLUX_COLOR_A[1, 1] = FLUX_COLOR_A[3, 2] = FLUX_COLOR_A[4, 3] = 1.
+FLUX_COLOR_A[2, :] = -1
+FLUX_COLOR_A[2, -1] = 1.
+
+
+def mog_params(covs):
+    """MixtureOfGaussians.update_params, util/dists/mog.py:55-56."""
+    return (np.array([np.linalg.inv(c) for c in covs]), np.array([np.linalg.det(c) for c in covs]))
+
+
+def flux_color_logpdf(log_fluxes, means, covs, pis):
+    """FluxColorMoG.logpdf, flux_prior.py:39-40."""
+    icovs, dets = mog_params(covs)
+    return mog_loglike(np.dot(log_fluxes, FLUX_COLOR_A), means, icovs, dets, pis)
+
+
+def gal_shape_unconstrained(x):
+    """GalShapeMoG.to_unconstrained, flux_prior.py:49-54."""
+    sigma, ab, phi = x[0], x[1], x[2]
+    return np.array([np.log(sigma), np.log(ab) - np.log(1. - ab), np.log(phi) - np.log(np.pi - phi)])
+
+
+def mog_responsibilities(x, means, covs, pis):
+    icovs, dets = mog_params(covs)
+    xx = np.atleast_2d(x)
+    centered = xx[:, :, np.newaxis] - means.T[np.newaxis, :, :]
+    solved = np.einsum('ijk,lji->lki', icovs, centered)
+    logprobs = (-0.5 * np.sum(solved * centered, axis=1) - np.log(2 * np.pi)
+                - 0.5 * np.log(dets) + np.log(pis))
+    return np.exp(logprobs - logsumexp(logprobs, axis=1)[:, None])
+
+
+def prior_sufficient_stats(resp, colors):
+    """[sum r_k | sum r_k c | sum r_k c c^T (upper triangle, np.triu_indices order)]."""
+    D = colors.shape[1]
+    iu = np.triu_indices(D)
+    s0 = resp.sum(axis=0)
+    s1 = resp.T @ colors
+    s2 = resp.T @ (colors[:, iu[0]] * colors[:, iu[1]])
+    return np.concatenate([s0, s1.ravel(), s2.ravel()])
+

@@ -171,3 +171,34 @@ def test_oracle_sample_source_counts_conserves_photons():
     assert noise2 == noise and np.array_equal(again[1].data, samp[1].data)
     # test_celeste_sample_sources.py:4-8
     assert ref.sample_multinomial(914, np.array([6.29379e-16, 1.]), np.random.RandomState(0))[0] == 0
+
+
+def test_oracle_prior_restatement_vs_scipy():
+    """util/dists/mog.py:5-21 for D = 5 against scipy's multivariate normal (the
+    reference's -log(2 pi) does not scale with D: a constant offset of
+    (D/2 - 1) log(2 pi)), and the sufficient-statistics layout."""
+    from scipy.stats import multivariate_normal
+    from scipy.special import logsumexp
+    from oracle import ref_cpu as ref
+    rng = np.random.RandomState(3)
+    K, D = 6, 5
+    means = rng.normal(size=(K, D))
+    A = rng.normal(size=(K, D, D))
+    covs = np.einsum('kij,klj->kil', A, A) + .5 * np.eye(D)
+    pis = rng.dirichlet(np.ones(K))
+    x = rng.normal(size=(50, D))
+    icovs, dets = ref.mog_params(covs)
+    got = ref.mog_loglike(x, means, icovs, dets, pis)
+    want = logsumexp(np.stack([np.log(pis[k]) + multivariate_normal(means[k], covs[k]).logpdf(x)
+                               for k in range(K)], 1), axis=1)
+    assert np.allclose(got - want, (D / 2. - 1.) * np.log(2 * np.pi), atol=1e-10)
+    r = ref.mog_responsibilities(x, means, covs, pis)
+    st = ref.prior_sufficient_stats(r, x)
+    assert st.shape == (K * (1 + D + 15),) and abs(st[:K].sum() - 50.) < 1e-10
+    k = 2
+    assert np.allclose(st[K + k * D:K + (k + 1) * D], (r[:, k:k + 1] * x).sum(0))
+    outer = np.einsum('n,ni,nj->ij', r[:, k], x, x)
+    assert np.allclose(st[K + K * D + k * 15:K + K * D + (k + 1) * 15], outer[np.triu_indices(D)])
+    lf = rng.normal(2., .5, size=(4, 5))
+    c = np.dot(lf, ref.FLUX_COLOR_A)
+    assert np.allclose(c[:, 4], lf[:, 2]) and np.allclose(c[:, 0], lf[:, 0] - lf[:, 2])
