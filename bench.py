@@ -433,7 +433,11 @@ def main():
                          "fp32_fma_peak": fma_peak, "kernel_ms_total": render_ms, "kernel_launches": render_n,
                          "kernel_share_of_step": render_ms / serial_ms if serial_ms else None,
                          "serial_ms_per_step": serial_ms / args.steps,
-                         "traffic": None,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of one timed 8-field launch from the
+                         # ncu --set full capture summarised in profiles/r01_prof_tile_v10_*: 672.2 + 4.5 MB
+                         # (algorithmic: 4 B of nelec per pixel = 488 MB); scaled to this launch's fields
+                         "traffic": 676.64e6 * FPC / 8.0,
+                         "traffic_algorithmic": FPC * 5 * H * W * 4,
                          "hbm_peak_gbs": peaks.get("hbm_gbs")},
             "clocks": clocks,
             "total_loglik": total_ll,

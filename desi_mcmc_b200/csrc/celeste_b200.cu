@@ -189,7 +189,11 @@ struct Counters {
 #define UNIT_WT_MAX 8
 // a component is skipped for a warp when its largest value over the warp's
 // pixels is below 2^-CULL_T of a lower bound of the mixture there
+#ifdef CULL_T_OVERRIDE
+#define CULL_T CULL_T_OVERRIDE
+#else
 #define CULL_T 27.0f
+#endif
 // photon allocation: image tiles of 64 x 16 pixels, per-tile source lists (the field path bins 16 x 16, see BIN_W)
 #define TILE_W 64
 #define TILE_H 16
