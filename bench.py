@@ -450,7 +450,17 @@ def main():
         out.write(json.dumps(line) + "\n")
         out.flush()
     if world > 1:
+        # Tear-down: the step graph holds the captured NCCL all-reduce and must go
+        # before the communicator.  The result is already printed; a watchdog ends
+        # the process if NCCL's tear-down stalls (seen once with a live graph).
+        wd = threading.Timer(20.0, lambda: os._exit(0))
+        wd.daemon = True
+        wd.start()
+        sweep.graph = None
+        torch.cuda.synchronize()
+        dist.barrier()
         dist.destroy_process_group()
+        wd.cancel()
 
 
 if __name__ == "__main__":
