@@ -644,6 +644,26 @@ class FieldSet(object):
         self.d_srcs[:o].copy_(self.h_srcs[:o], non_blocking=True)
         return o
 
+    def pinned_sources(self, f: int, n: int | None = None) -> np.ndarray:
+        """A CgSource view INTO the pinned staging buffer for field f (n sources,
+        default n_src_max[f]; fields are packed back to back, so set the counts
+        of fields 0..f-1 first).  A sampler that keeps its state here pays no
+        host copy per step: upload() is the only per-step host work."""
+        n = int(self.n_src_max[f]) if n is None else int(n)
+        if n > self.n_src_max[f]:
+            raise ValueError("field %d: more sources than n_src_max" % f)
+        start = int(self.src_off[f])
+        self.src_off[f + 1:] = np.maximum(self.src_off[f + 1:], start + n)
+        self.src_off[f + 1] = start + n
+        b0 = start * SRC_DTYPE.itemsize
+        return self.h_np[b0:b0 + n * SRC_DTYPE.itemsize].view(SRC_DTYPE)
+
+    def upload(self) -> int:
+        """Pinned staging buffer -> device (async on the current stream); returns bytes."""
+        o = int(self.src_off[len(self.fields)]) * SRC_DTYPE.itemsize
+        self.d_srcs[:o].copy_(self.h_srcs[:o], non_blocking=True)
+        return o
+
     def loglik_device(self) -> torch.Tensor:
         """Sources already resident (set_sources called before); nothing synchronises."""
         check(self.L.cg_fields_loglik(self.harr, self.img_off.ctypes.data, self.d_srcs.data_ptr(),
@@ -673,12 +693,16 @@ class FieldSweep(object):
     into the captured launches: call ``capture()`` again after ``set_sources``
     changed a count (parameter VALUES may change freely)."""
 
-    def __init__(self, sets: Sequence["FieldSet"], n_streams: int = 2, after=None):
+    def __init__(self, sets: Sequence["FieldSet"], n_streams: int = 2, after=None, io: bool = False):
         """after: optional callable enqueued on the current stream after the sets
         of a step (e.g. the all-reduce of the sweep statistics); it is captured
-        into the graph with them."""
+        into the graph with them.  io=True makes the step self-contained end to
+        end: it starts with every set's upload() (pinned source stage -> device)
+        and ends with the copy of the per-image log-likelihoods to the pinned
+        h_ll, so that a replay is ONE driver call including the transfers."""
         self.sets = list(sets)
         self.after = after
+        self.io = bool(io)
         self.n_streams = max(1, min(int(n_streams), len(self.sets)))
         self._side = [torch.cuda.Stream(device=device()) for _ in range(self.n_streams)] \
             if self.n_streams > 1 else []
@@ -686,6 +710,15 @@ class FieldSweep(object):
         self._counts = None
 
     def _enqueue(self):
+        if self.io:
+            for fs in self.sets:
+                fs.upload()
+        self._enqueue_compute()
+        if self.io:
+            for fs in self.sets:
+                fs.h_ll.copy_(fs.ll, non_blocking=True)
+
+    def _enqueue_compute(self):
         if not self._side:
             for fs in self.sets:
                 fs.loglik_device()

@@ -275,6 +275,24 @@ def test_fields_batch_matches_single_calls(engine, oracle):
     for b, img in enumerate(oimgs):
         want = oracle.celeste_likelihood(osrcs, img)
         assert abs(got[10 + b] - want) <= LL_RTOL * abs(want)
+    # the same through the pinned views + CUDA-graph replay (FieldSweep): a sampler
+    # that keeps its state in the staging buffer, one driver call per step
+    fs2 = engine.FieldSet(gimgs, [max(1, p.shape[0]) for p in packed])
+    for f, pk in enumerate(packed):
+        fs2.pinned_sources(f, pk.shape[0])[:] = pk
+    fs2.upload()
+    sweep = engine.FieldSweep([fs2], n_streams=1).capture()
+    sweep.run()
+    assert np.array_equal(fs2.ll.cpu().numpy(), got)
+    v = fs2.pinned_sources(2, packed[2].shape[0])
+    v["flux"] *= 1.5                                   # new parameter values, same counts: replay is valid
+    fs2.upload()
+    sweep.run()
+    moved = fs2.ll.cpu().numpy()
+    assert np.array_equal(moved[:10], got[:10]) and np.all(moved[10:] != got[10:])
+    pk2 = packed[2].copy()
+    pk2["flux"] *= 1.5
+    assert np.array_equal(moved[10:], engine.field_loglik(gimgs[2], pk2).cpu().numpy())
 
 
 def test_component_culling_error_bound(engine):
