@@ -407,6 +407,7 @@ def main():
     if rank == 0:
         xu_peak = engine.pipe_probe(0)
         fma_peak = engine.pipe_probe(1)
+        mix_peak = engine.pipe_probe(2)         # the inner-loop instruction mix in isolation, 24 warps/SM
         achieved = evals_step * args.steps / (render_ms * 1e-3) if render_ms > 0 else None
         sm = engine.sm_count()
         nominal = sm * 16 * (clocks["sm_mhz"] or 0) * 1e6
@@ -440,6 +441,10 @@ def main():
                          "issued_frac": (issued_step * args.steps / (render_ms * 1e-3) / xu_peak) if render_ms > 0 else None,
                          "note": "achieved = algorithmic evals (footprint pixels x components, SURVEY 8d) / kernel time; "
                                  "issued = MUFU.EX2 lane-operations actually executed after per-warp component culling",
+                         "mix_ceiling": {"value": mix_peak, "frac_of_peak": mix_peak / xu_peak,
+                                         "note": "MUFU.EX2 lane-ops/s the kernel's inner loop (2 LDS + 6 row-term FFMA per "
+                                                 "component, then 2 FFMA + MUFU + FADD per pixel) reaches in isolation "
+                                                 "(cg_pipe_probe(2): no global memory, every lane busy); compare with `issued`"},
                          "fp32_fma_peak": fma_peak, "kernel_ms_total": render_ms, "kernel_launches": render_n,
                          "kernel_share_of_step": render_ms / serial_ms if serial_ms else None,
                          "serial_ms_per_step": serial_ms / args.steps,

@@ -1991,6 +1991,81 @@ __global__ void __launch_bounds__(256) fma_probe_kernel(float* out, int iters) {
   if (s == 123.456f) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// Instruction-mix probes: the inner loop of field_tile_kernel / render_kernel in
+// isolation (no global memory, every lane busy), to measure what fraction of
+// the MUFU peak this MIX can reach on the device.  VAR 2: the full loop (table
+// entry from shared memory, 6 row-term FFMA, then 2 FFMA + MUFU.EX2 + FADD per
+// pixel, 8 pixels); 3: the same with the table in registers (no LDS); 4: no row
+// terms either; 5: 1 FFMA + MUFU + FADD per pixel.  Result: MUFU lane-ops/s.
+template <int VAR>
+__global__ void __launch_bounds__(256) mix_probe_kernel(float* out, int iters) {
+  __shared__ __align__(16) float s_tab[48 * 8];
+  for (int i = threadIdx.x; i < 48 * 8; i += 256) s_tab[i] = -1e-3f * (float)(1 + (i % 7));
+  __syncthreads();
+  const float* tb0 = s_tab + (threadIdx.x >> 5) * 8;
+  float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
+  float xl[4];
+#pragma unroll
+  for (int p = 0; p < 4; ++p) xl[p] = 0.25f * (float)((threadIdx.x & 3) * 4 + p);
+  const float y0l = 0.125f * (float)((threadIdx.x & 31) >> 2), y1l = y0l + 1.f;
+  float4 t0 = *reinterpret_cast<const float4*>(tb0);
+  float2 t1 = *reinterpret_cast<const float2*>(tb0 + 4);
+  for (int i = 0; i < iters; ++i) {
+    const float* tb = tb0;
+#pragma unroll 2
+    for (int k = 0; k < 32; ++k) {
+      float b1a, b1b, c1a, c1b;
+      if (VAR == 2) {
+        tb += 8;
+        const float4 n0 = *reinterpret_cast<const float4*>(tb);
+        const float2 n1 = *reinterpret_cast<const float2*>(tb + 4);
+        b1a = fmaf(t0.y, y0l, t0.w); b1b = fmaf(t0.y, y1l, t0.w);
+        c1a = fmaf(fmaf(t0.z, y0l, t1.x), y0l, t1.y);
+        c1b = fmaf(fmaf(t0.z, y1l, t1.x), y1l, t1.y);
+        float q[8];
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          q[p] = fmaf(fmaf(t0.x, xl[p], b1a), xl[p], c1a);
+          q[4 + p] = fmaf(fmaf(t0.x, xl[p], b1b), xl[p], c1b);
+        }
+#pragma unroll
+        for (int p = 0; p < 8; ++p) q[p] = ex2_approx(q[p]);
+#pragma unroll
+        for (int p = 0; p < 4; ++p) { acc0[p] += q[p]; acc1[p] += q[4 + p]; }
+        t0 = n0; t1 = n1;
+      } else {
+        if (VAR == 3) {
+          b1a = fmaf(t0.y, y0l, t0.w); b1b = fmaf(t0.y, y1l, t0.w);
+          c1a = fmaf(fmaf(t0.z, y0l, t1.x), y0l, t1.y);
+          c1b = fmaf(fmaf(t0.z, y1l, t1.x), y1l, t1.y);
+        } else {
+          b1a = t0.y; b1b = t0.w; c1a = t1.x; c1b = t1.y;
+        }
+        float q[8];
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          if (VAR == 5) {
+            q[p] = fmaf(t0.x, xl[p], c1a + acc0[p] * 1e-30f);
+            q[4 + p] = fmaf(t0.x, xl[p], c1b + acc1[p] * 1e-30f);
+          } else {
+            q[p] = fmaf(fmaf(t0.x, xl[p], b1a), xl[p], c1a);
+            q[4 + p] = fmaf(fmaf(t0.x, xl[p], b1b), xl[p], c1b);
+          }
+        }
+#pragma unroll
+        for (int p = 0; p < 8; ++p) q[p] = ex2_approx(q[p]);
+#pragma unroll
+        for (int p = 0; p < 4; ++p) { acc0[p] += q[p]; acc1[p] += q[4 + p]; }
+        t0.y += 1e-7f;          // keep the row terms loop-variant
+      }
+    }
+  }
+  float sacc = 0.f;
+#pragma unroll
+  for (int p = 0; p < 4; ++p) sacc += acc0[p] + acc1[p];
+  if (sacc == 123.456f) out[blockIdx.x * blockDim.x + threadIdx.x] = sacc;
+}
+
 // per-launch CUDA-event timing of render_kernel (bench.py's roofline leg)
 #define PROF_MAX 8192
 static bool g_prof_on = false;
@@ -2840,7 +2915,10 @@ int cg_profile_render_read(double* total_ms, int64_t* launches) {
 int cg_pipe_probe(int which, double* ops_per_s, void* stream) {
   NEED_INIT();
   cudaStream_t st = (cudaStream_t)stream;
-  const int iters = 4096, blocks = g_sm_count * 8, threads = 256;
+  // which: 0 MUFU.EX2, 1 FFMA; 2..5 instruction-mix probes at 3 CTAs/SM (24 warps, the tile
+  // kernel's residency), 12..15 the same mixes at 8 CTAs/SM (64 warps)
+  const int var = which % 10;
+  const int iters = var >= 2 ? 128 : 4096, blocks = g_sm_count * ((which >= 2 && which < 10) ? 3 : 8), threads = 256;
   float* d_out = nullptr;
   CUDA_TRY(cudaMalloc(&d_out, sizeof(float) * blocks * threads));
   cudaEvent_t e0, e1;
@@ -2850,7 +2928,11 @@ int cg_pipe_probe(int which, double* ops_per_s, void* stream) {
   for (int rep = 0; rep < 6; ++rep) {
     CUDA_TRY(cudaEventRecord(e0, st));
     if (which == 0) xu_probe_kernel<<<blocks, threads, 0, st>>>(d_out, iters);
-    else fma_probe_kernel<<<blocks, threads, 0, st>>>(d_out, iters);
+    else if (which == 1) fma_probe_kernel<<<blocks, threads, 0, st>>>(d_out, iters);
+    else if (var == 2) mix_probe_kernel<2><<<blocks, threads, 0, st>>>(d_out, iters);
+    else if (var == 3) mix_probe_kernel<3><<<blocks, threads, 0, st>>>(d_out, iters);
+    else if (var == 4) mix_probe_kernel<4><<<blocks, threads, 0, st>>>(d_out, iters);
+    else mix_probe_kernel<5><<<blocks, threads, 0, st>>>(d_out, iters);
     CUDA_TRY(cudaEventRecord(e1, st));
     LAUNCH_CHECK();
     CUDA_TRY(cudaEventSynchronize(e1));
@@ -2861,7 +2943,7 @@ int cg_pipe_probe(int which, double* ops_per_s, void* stream) {
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   cudaFree(d_out);
-  if (ops_per_s) *ops_per_s = (double)blocks * threads * 8.0 * iters / (best * 1e-3);
+  if (ops_per_s) *ops_per_s = (double)blocks * threads * 8.0 * iters * (var >= 2 ? 32.0 : 1.0) / (best * 1e-3);
   return CG_OK;
 }
 

@@ -323,7 +323,10 @@ int64_t cg_last_issued_count(void* stream);
 int cg_profile_render(int enable);
 int cg_profile_render_read(double* h_total_ms, int64_t* h_launches);
 /* Measured pipe throughput on this device: which = 0 MUFU.EX2 results/s (the
- * XU roofline of render_kernel), 1 = FP32 FMA instructions/s.  Synchronises. */
+ * XU roofline of the render kernels), 1 = FP32 FMA instructions/s, 2..5 / 12..15 =
+ * MUFU.EX2 results/s of the kernels' inner-loop instruction MIX in isolation at 24 /
+ * 64 warps per SM (2 full loop with shared-memory table, 3 table in registers,
+ * 4 without row terms, 5 one FFMA per exp).  Synchronises. */
 int cg_pipe_probe(int which, double* h_ops_per_s, void* stream);
 
 #ifdef __cplusplus
