@@ -899,3 +899,30 @@ def prior_sufficient_stats(resp, colors):
     s2 = resp.T @ (colors[:, iu[0]] * colors[:, iu[1]])
     return np.concatenate([s0, s1.ravel(), s2.ravel()])
 
+
+
+# --------------------------------------------------------------------------
+# fits_image.py:48-155 (file route) and util/data/get_data.py:38-42,89-136
+# --------------------------------------------------------------------------
+def fits_image_from_header(band, img, header):
+    """FitsImage.__init__ for a frame/stamp whose header carries CALIB, SKY, GAIN,
+    CRPIX/CRVAL/CD and PSF_P0..17: dn = img / CALIB + SKY, nelec = round(dn * GAIN)
+    (:85-87), rho_n = CRPIX - 1 (:99), psf vector layout (:126-138)."""
+    dn = np.asarray(img, dtype=np.float64) / header["CALIB"] + header["SKY"]
+    nelec = np.round(dn * header["GAIN"])
+    psfvec = np.array([header["PSF_P%d" % i] for i in range(18)])
+    cv = psfvec[9:].reshape(3, 3)
+    covars = np.zeros((3, 2, 2))
+    for i in range(3):
+        covars[i] = np.array([[cv[i, 0], cv[i, 2]], [cv[i, 2], cv[i, 1]]])
+    return SyntheticImage(band=band, nelec=nelec, calib=header["CALIB"], gain=header["GAIN"],
+                          sky=header["SKY"],
+                          rho_n=np.array([header["CRPIX1"], header["CRPIX2"]]) - 1,
+                          phi_n=np.array([header["CRVAL1"], header["CRVAL2"]]),
+                          Ups_n=np.array([[header["CD1_1"], header["CD1_2"]],
+                                          [header["CD2_1"], header["CD2_2"]]]),
+                          psf_weights=psfvec[0:3], psf_means=psfvec[3:9].reshape(3, 2), psf_covars=covars)
+
+
+def mags2nanomaggies(mags):
+    return np.power(10., (mags - 22.5) / -2.5)

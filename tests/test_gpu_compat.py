@@ -281,3 +281,30 @@ def test_compat_sample_source_counts(engine, oracle):
     assert noise + samp[0].data.sum() + samp[1].data.sum() == nelec.sum()
     assert samp[0].data[1:, 1:].sum() > 0 and np.all(samp[0].data[0] == 0) and np.all(samp[1].data[:, 0] == 0)
     assert css.sample_binomial(914, 6.29379e-16, np.random.RandomState(0)) == 0
+
+
+def test_fits_image_from_real_stamp(engine, oracle):
+    """N4: compat.fits_image.FitsImage on the stamp the reference ships (fixture
+    tests/golden/stamp_r_253.npz): same fields as the oracle's restatement of
+    fits_image.py:85-155, and a star rendered with the stamp's REAL PSF."""
+    import os
+    from desi_mcmc_b200.compat import celeste, fits_image as fi
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "stamp_r_253.npz"))
+    img, hdr = z["img"], {str(k): float(v) for k, v in zip(z["keys"], z["values"])}
+    g = fi.FitsImage("r", img=img, header=hdr)
+    o = oracle.fits_image_from_header("r", img, hdr)
+    assert np.array_equal(g.nelec.cpu().numpy().astype(np.float64), o.nelec)
+    assert g.epsilon == o.epsilon == g.epsilon0 and g.kappa == o.kappa and g.calib == o.calib
+    assert np.array_equal(g.rho_n, o.rho_n) and np.array_equal(g.Ups_n, o.Ups_n)
+    assert np.array_equal(g.weights, o.weights) and np.array_equal(g.covars, o.covars)
+    assert abs(g.R - o.R) <= 1e-12 * o.R
+    u = o.pixel2equa(np.array([24.3, 26.8]))
+    patch, ylim, xlim = celeste.gen_point_source_psf_image(u, g)
+    want, wyl, wxl = oracle.gen_point_source_psf_image(u, o)
+    assert (tuple(ylim), tuple(xlim)) == (tuple(wyl), tuple(wxl)) and patch.shape == want.shape
+    assert hp.rel_err(patch, want, 1e-7 * want.max()) < 1e-5
+    src = engine.SrcParams(u, a=0, fluxes=[8., 9., 10., 11., 12.])
+    osrc = oracle.SrcParams(u=u, a=0, fluxes=[8., 9., 10., 11., 12.])
+    got = celeste.celeste_likelihood([src], g)
+    ref_ll = oracle.celeste_likelihood([osrc], o)
+    assert abs(got - ref_ll) <= 1e-6 * abs(ref_ll)
