@@ -43,7 +43,7 @@ WORKLOAD = ("C2 full-field log-likelihood: synthetic Stripe-82 frame 2048x1489 x
 
 class ClockSampler(threading.Thread):
     """SM clock + throttle reasons during the timed region: NVML in-process
-    (a sample every ~2 ms), nvidia-smi as the fallback."""
+    (a sample every ~10 ms), nvidia-smi as the fallback."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -99,7 +99,7 @@ class ClockSampler(threading.Thread):
                     self._sample_smi()
             except Exception:
                 pass
-            self._stop_ev.wait(0.002 if self.nv is not None else 0.1)
+            self._stop_ev.wait(0.01 if self.nv is not None else 0.1)
 
     def stop(self):
         self._stop_ev.set()
