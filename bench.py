@@ -244,6 +244,8 @@ def main():
     engine.init(local)
     if os.environ.get("CG_CULL"):
         engine.set_option(1, int(os.environ["CG_CULL"]))
+    if os.environ.get("CG_RECUR"):                       # A/B switch of the row recurrence (CG_OPT_ROW_RECURRENCE)
+        engine.set_option(2, int(os.environ["CG_RECUR"]))
     dev = engine.device()
     F = args.fields_per_gpu
 

@@ -60,6 +60,7 @@ class CgBox(C.Structure):
 
 
 CG_OPT_CULL = 1
+CG_OPT_ROW_RECURRENCE = 2
 CG_MAX_FIELDS = 16
 
 # numpy mirrors of the POD arrays that cross the boundary in bulk

@@ -171,6 +171,10 @@ struct Counters {
 //   (half-widths^2 of the level-set bounding box per unit of log2 drop) and
 //   sl = log2(e) / (2 lambda_min(Sigma)) (steepest log2 drop per squared pixel).
 #define TAB_W 12
+#ifndef FT_RECUR
+#define FT_RECUR 1          // row recurrence compiled in (run-time switch: CG_OPT_ROW_RECURRENCE)
+#endif
+#define FT_RECUR_DMAX 96.f   // largest |log2 ratio of neighbouring pixels| the row recurrence is used for
 #define TAB_STRIDE (CG_MAX_COMP * TAB_W)
 
 #define STRIP_THREADS 256
@@ -186,6 +190,7 @@ struct Counters {
 #define TILE_CW 4
 #define TILE_R 8
 #define WT_PIX (32 * 2 * PIX_PER_THREAD)
+static_assert(PIX_PER_THREAD == 4, "recur_row4 and the float4 pixel groups assume 4 pixels per lane");
 #define UNIT_WT_MAX 8
 // a component is skipped for a warp when its largest value over the warp's
 // pixels is below 2^-CULL_T of a lower bound of the mixture there
@@ -249,6 +254,18 @@ __device__ __forceinline__ float rexp2(float x) { return ex2_approx(x); }
 __device__ __forceinline__ double rexp2(double x) { return exp2(x); }
 __device__ __forceinline__ float rfma(float a, float b, float c) { return fmaf(a, b, c); }
 __device__ __forceinline__ double rfma(double a, double b, double c) { return fma(a, b, c); }
+// four consecutive pixels of a row from the first value e, the neighbour ratio g and the
+// ratio of ratios h (see "Row recurrence" at ft_eval2r)
+template <typename T>
+__device__ __forceinline__ void recur_row4(T e, T g, T h, T (&acc)[4]) {
+  acc[0] += e;
+  e *= g; g *= h;
+  acc[1] += e;
+  e *= g; g *= h;
+  acc[2] += e;
+  e *= g;
+  acc[3] += e;
+}
 
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
@@ -658,19 +675,26 @@ __device__ __forceinline__ void unit_decode(int q, int cpr, int hp, float r_band
 //   the rectangle is below 2^-CULL_T of the mixture everywhere in it.
 // Survivors are compacted (component order preserved) into the warp's table
 // of 8-float entries; returns their number.
-__device__ __forceinline__ int cull_components(const float* s_tab, int K, int lane, float xa,
-                                               float xb, float ya, float yb, float* wtab) {
+// The row pair (h, k8) = (2^(2A), 2^(8B)) of each surviving component feeds the
+// row recurrence of ft_eval2r/ft_eval1r; *recur_ok says whether that recurrence is
+// safe for every survivor on this rectangle (see FT_RECUR below).
+// LDG: the table is read from global memory through the read-only path (field kernel: L2)
+// or from shared memory (render_kernel).  xext: pixels a lane may start left of the rectangle.
+template <bool LDG>
+__device__ __forceinline__ int cull_components(const float* gtab, int K, int lane, float xa, float xb,
+                                               float ya, float yb, float xext, float* wtab, bool* recur_ok) {
   float lb = -INFINITY;
   float4 e0[2], e1[2];
-  float qs[2], kx[2], ky[2], dx2[2], dy2[2];
+  float qs[2], kx[2], ky[2], dx2[2], dy2[2], dmx[2];
 #pragma unroll
   for (int r = 0; r < 2; ++r) {
     const int k = lane + 32 * r;
-    qs[r] = -INFINITY; kx[r] = ky[r] = 0.f; dx2[r] = dy2[r] = 0.f;
+    qs[r] = -INFINITY; kx[r] = ky[r] = 0.f; dx2[r] = dy2[r] = 0.f; dmx[r] = 0.f;
     if (k < K) {
-      e0[r] = *reinterpret_cast<const float4*>(s_tab + k * TAB_W);
-      e1[r] = *reinterpret_cast<const float4*>(s_tab + k * TAB_W + 4);
-      const float4 e2 = *reinterpret_cast<const float4*>(s_tab + k * TAB_W + 8);
+      const float4* t4 = reinterpret_cast<const float4*>(gtab + k * TAB_W);
+      e0[r] = LDG ? __ldg(t4) : t4[0];
+      e1[r] = LDG ? __ldg(t4 + 1) : t4[1];
+      const float4 e2 = LDG ? __ldg(t4 + 2) : t4[2];
       const float mx = e1[r].z, my = e1[r].w;
       qs[r] = e2.x; kx[r] = e2.y; ky[r] = e2.z;
       const float fx = fmaxf(fabsf(xa - mx), fabsf(xb - mx)), fy = fmaxf(fabsf(ya - my), fabsf(yb - my));
@@ -678,16 +702,18 @@ __device__ __forceinline__ int cull_components(const float* s_tab, int K, int la
       if (l == l) lb = fmaxf(lb, l);
       const float dx = fmaxf(0.f, fmaxf(xa - mx, mx - xb)), dy = fmaxf(0.f, fmaxf(ya - my, my - yb));
       dx2[r] = dx * dx; dy2[r] = dy * dy;
+      // bound of |q(x+1,y) - q(x,y)| = |2A(x-mx) + B(y-my) + A| over the rectangle widened
+      // by the xext pixels a lane's group of 4 may start to the left of it; 8|B| bounds k8
+      dmx[r] = fmaxf(fmaf(fabsf(e0[r].x), 2.f * (fx + xext) + 1.f, fabsf(e0[r].y) * fy), 8.f * fabsf(e0[r].y));
     }
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) lb = fmaxf(lb, __shfl_xor_sync(0xffffffffu, lb, o));
-  const float thr = lb - (CULL_T + 0.5f);       // 0.5: fp32 slack of the bounds
+  const float thr = lb - (CULL_T + 0.5f);
   bool keep[2];
 #pragma unroll
   for (int r = 0; r < 2; ++r) {
     const float rho = (qs[r] - thr) * 1.0001f;
-    // !(a > b) keeps the component when a bound is NaN (degenerate component)
     keep[r] = (lane + 32 * r < K) && !(rho < 0.f) && !(dx2[r] > rho * kx[r]) && !(dy2[r] > rho * ky[r]);
   }
   const unsigned m0 = __ballot_sync(0xffffffffu, keep[0]);
@@ -696,13 +722,14 @@ __device__ __forceinline__ int cull_components(const float* s_tab, int K, int la
   if (keep[0]) {
     float* d = wtab + __popc(m0 & lt) * 8;
     *reinterpret_cast<float4*>(d) = e0[0];
-    *reinterpret_cast<float2*>(d + 4) = make_float2(e1[0].x, e1[0].y);
+    *reinterpret_cast<float4*>(d + 4) = make_float4(e1[0].x, e1[0].y, ex2_approx(2.f * e0[0].x), ex2_approx(8.f * e0[0].y));
   }
   if (keep[1]) {
     float* d = wtab + (__popc(m0) + __popc(m1 & lt)) * 8;
     *reinterpret_cast<float4*>(d) = e0[1];
-    *reinterpret_cast<float2*>(d + 4) = make_float2(e1[1].x, e1[1].y);
+    *reinterpret_cast<float4*>(d + 4) = make_float4(e1[1].x, e1[1].y, ex2_approx(2.f * e0[1].x), ex2_approx(8.f * e0[1].y));
   }
+  *recur_ok = !__any_sync(0xffffffffu, (keep[0] && !(dmx[0] <= FT_RECUR_DMAX)) || (keep[1] && !(dmx[1] <= FT_RECUR_DMAX)));
   __syncwarp();
   return __popc(m0) + __popc(m1);
 }
@@ -761,15 +788,17 @@ __global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
       int n = h.K;
       const real* tb = s_tab;
       int stride = TAB_W;
-      if (sizeof(real) == 4 && a.cull && n > 1) {
+      bool recur = false;
+      if (sizeof(real) == 4 && (a.cull & 1) && n > 1) {
         const int rmin = __reduce_min_sync(0xffffffffu, active ? row0 : 0x7fffffff);
         const int rmax = __reduce_max_sync(0xffffffffu, active ? (two ? row1 : row0) : -1);
         const int cmin = __reduce_min_sync(0xffffffffu, active ? cx : 0x7fffffff);
         const int cmax = __reduce_max_sync(0xffffffffu, active ? cx + npx - 1 : -1);
         __syncwarp();             // the warp is done reading the culled table of the previous tile
-        n = cull_components(reinterpret_cast<const float*>(s_tab), n, lane,
-                            (float)(h.x0 + cmin - h.ox), (float)(h.x0 + cmax - h.ox),
-                            (float)(h.y0 + rmin - h.oy), (float)(h.y0 + rmax - h.oy), s_wtab);
+        n = cull_components<false>(reinterpret_cast<const float*>(s_tab), n, lane,
+                                   (float)(h.x0 + cmin - h.ox), (float)(h.x0 + cmax - h.ox),
+                                   (float)(h.y0 + rmin - h.oy), (float)(h.y0 + rmax - h.oy), 0.f, s_wtab, &recur);
+        recur = recur && FT_RECUR && !(a.cull & 2);
         tb = reinterpret_cast<const real*>(s_wtab);
         stride = 8;
       }
@@ -784,6 +813,23 @@ __global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
         real xl[PIX_PER_THREAD];
 #pragma unroll
         for (int p = 0; p < PIX_PER_THREAD; ++p) xl[p] = xl0 + (real)p;
+        if (sizeof(real) == 4 && recur) {
+          // row recurrence: 2 exp2 per row of 4 pixels (the rows of a lane are not a fixed
+          // distance apart here, so each row takes its own neighbour ratio)
+          const real tx = (real)2 * xl0 + (real)1;
+#pragma unroll 2
+          for (int k = 0; k < n; ++k, tb += 8) {
+            const real A = tb[0], B = tb[1], C = tb[2], b10 = tb[3], c01 = tb[4], c00 = tb[5], hh = tb[6];
+            const real b1a = rfma(B, y0l, b10), b1b = rfma(B, y1l, b10);
+            const real c1a = rfma(rfma(C, y0l, c01), y0l, c00);
+            const real c1b = rfma(rfma(C, y1l, c01), y1l, c00);
+            const real ea = rexp2(rfma(rfma(A, xl0, b1a), xl0, c1a)), ga = rexp2(rfma(A, tx, b1a));
+            const real eb = rexp2(rfma(rfma(A, xl0, b1b), xl0, c1b)), gb = rexp2(rfma(A, tx, b1b));
+            recur_row4(ea, ga, hh, acc0);
+            recur_row4(eb, gb, hh, acc1);
+          }
+          n = 0;
+        }
 #pragma unroll 2
         for (int k = 0; k < n; ++k, tb += stride) {
           const real A = tb[0], B = tb[1], C = tb[2], b10 = tb[3], c01 = tb[4], c00 = tb[5];
@@ -972,56 +1018,6 @@ __global__ void __launch_bounds__(256) bin_order_kernel(FieldArgs a) {
   }
 }
 
-// cull_components with the table read from global memory (L2), 2 components per lane
-__device__ __forceinline__ int ft_cull(const float* gtab, int K, int lane, float xa, float xb,
-                                       float ya, float yb, float* wtab) {
-  float lb = -INFINITY;
-  float4 e0[2], e1[2];
-  float qs[2], kx[2], ky[2], dx2[2], dy2[2];
-#pragma unroll
-  for (int r = 0; r < 2; ++r) {
-    const int k = lane + 32 * r;
-    qs[r] = -INFINITY; kx[r] = ky[r] = 0.f; dx2[r] = dy2[r] = 0.f;
-    if (k < K) {
-      const float4* t4 = reinterpret_cast<const float4*>(gtab + k * TAB_W);
-      e0[r] = __ldg(t4);
-      e1[r] = __ldg(t4 + 1);
-      const float4 e2 = __ldg(t4 + 2);
-      const float mx = e1[r].z, my = e1[r].w;
-      qs[r] = e2.x; kx[r] = e2.y; ky[r] = e2.z;
-      const float fx = fmaxf(fabsf(xa - mx), fabsf(xb - mx)), fy = fmaxf(fabsf(ya - my), fabsf(yb - my));
-      const float l = qs[r] - e2.w * (fx * fx + fy * fy);
-      if (l == l) lb = fmaxf(lb, l);
-      const float dx = fmaxf(0.f, fmaxf(xa - mx, mx - xb)), dy = fmaxf(0.f, fmaxf(ya - my, my - yb));
-      dx2[r] = dx * dx; dy2[r] = dy * dy;
-    }
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) lb = fmaxf(lb, __shfl_xor_sync(0xffffffffu, lb, o));
-  const float thr = lb - (CULL_T + 0.5f);
-  bool keep[2];
-#pragma unroll
-  for (int r = 0; r < 2; ++r) {
-    const float rho = (qs[r] - thr) * 1.0001f;
-    keep[r] = (lane + 32 * r < K) && !(rho < 0.f) && !(dx2[r] > rho * kx[r]) && !(dy2[r] > rho * ky[r]);
-  }
-  const unsigned m0 = __ballot_sync(0xffffffffu, keep[0]);
-  const unsigned m1 = __ballot_sync(0xffffffffu, keep[1]);
-  const unsigned lt = (1u << lane) - 1u;
-  if (keep[0]) {
-    float* d = wtab + __popc(m0 & lt) * 8;
-    *reinterpret_cast<float4*>(d) = e0[0];
-    *reinterpret_cast<float2*>(d + 4) = make_float2(e1[0].x, e1[0].y);
-  }
-  if (keep[1]) {
-    float* d = wtab + (__popc(m0) + __popc(m1 & lt)) * 8;
-    *reinterpret_cast<float4*>(d) = e0[1];
-    *reinterpret_cast<float2*>(d + 4) = make_float2(e1[1].x, e1[1].y);
-  }
-  __syncwarp();
-  return __popc(m0) + __popc(m1);
-}
-
 // evaluate the compacted mixture (8 floats per component in the warp's shared
 // table: one 16-byte + one 8-byte load) at the lane's pixels: two rows / one row.
 // The table entry of component k+1 is loaded before component k is evaluated
@@ -1073,6 +1069,54 @@ __device__ __forceinline__ void ft_eval1(const float* tb, int n, float yl,
   }
 }
 
+// Row recurrence (FT_RECUR): along a row the component is exp2 of a quadratic in x, so
+// its values at x0..x0+3 are e0, e0*g0, e0*g0*(g0*h), ... with g0 = 2^(q(x0+1)-q(x0))
+// and h = 2^(2A): TWO exp2 and five multiplies for four pixels instead of four exp2
+// and six FMAs; the second row's g0 is the first row's times k8 = 2^(8B).  3 MUFU.EX2
+// per component for the lane's 8 pixels instead of 8: the XU pipe stops being the
+// bound and the loop becomes issue-bound (35 instructions per 8 pixels, was 40).
+// Every product stays the true pixel value times roundings (6 roundings + 3 exp2 at
+// the fourth pixel, ~1.5e-6 relative); it is taken only when cull_components proved
+// |q(x+1)-q(x)| <= FT_RECUR_DMAX on the lanes that count (no overflow of g, and a
+// flushed e0 stands for values below 2^(-126+96) of a unit-flux profile, the culling
+// tolerance), otherwise ft_eval2/1.
+__device__ __forceinline__ void ft_eval2r(const float* tb, int n, float y0l, float y1l,
+                                          float x0, float (&acc0)[4], float (&acc1)[4]) {
+  const float tx = 2.f * x0 + 1.f;
+  float4 t0 = *reinterpret_cast<const float4*>(tb);      // A, B, C, b10
+  float4 t1 = *reinterpret_cast<const float4*>(tb + 4);  // c01, c00, h, k8
+#pragma unroll 2
+  for (int k = 0; k < n; ++k) {
+    tb += 8;
+    const float4 n0 = *reinterpret_cast<const float4*>(tb);
+    const float4 n1 = *reinterpret_cast<const float4*>(tb + 4);
+    const float b1a = fmaf(t0.y, y0l, t0.w), b1b = fmaf(t0.y, y1l, t0.w);
+    const float c1a = fmaf(fmaf(t0.z, y0l, t1.x), y0l, t1.y);
+    const float c1b = fmaf(fmaf(t0.z, y1l, t1.x), y1l, t1.y);
+    const float ea = ex2_approx(fmaf(fmaf(t0.x, x0, b1a), x0, c1a));
+    const float eb = ex2_approx(fmaf(fmaf(t0.x, x0, b1b), x0, c1b));
+    const float ga = ex2_approx(fmaf(t0.x, tx, b1a));
+    recur_row4(ea, ga, t1.z, acc0);
+    recur_row4(eb, ga * t1.w, t1.z, acc1);
+    t0 = n0; t1 = n1;
+  }
+}
+__device__ __forceinline__ void ft_eval1r(const float* tb, int n, float yl, float x0, float (&acc)[4]) {
+  const float tx = 2.f * x0 + 1.f;
+  float4 t0 = *reinterpret_cast<const float4*>(tb);
+  float4 t1 = *reinterpret_cast<const float4*>(tb + 4);
+#pragma unroll 2
+  for (int k = 0; k < n; ++k) {
+    tb += 8;
+    const float4 n0 = *reinterpret_cast<const float4*>(tb);
+    const float4 n1 = *reinterpret_cast<const float4*>(tb + 4);
+    const float b1 = fmaf(t0.y, yl, t0.w);
+    const float c1 = fmaf(fmaf(t0.z, yl, t1.x), yl, t1.y);
+    recur_row4(ex2_approx(fmaf(fmaf(t0.x, x0, b1), x0, c1)), ex2_approx(fmaf(t0.x, tx, b1)), t1.z, acc);
+    t0 = n0; t1 = n1;
+  }
+}
+
 struct FtGeom { int X0, Y0, x, yA, yB; };
 
 // one source on the warp's bin: cull, evaluate, add the rates inside the footprint
@@ -1084,10 +1128,12 @@ __device__ __forceinline__ void ft_source(const FieldArgs& a, int item, int K, i
   if (ix0 >= ix1 || iy0 >= iy1 || K <= 0) return;                // warp-uniform
   const float* gtab = a.tab + (long long)item * TAB_STRIDE;
   int n = K;
+  bool recur = false;
   __syncwarp();                       // the warp is done reading its previous table
-  if (a.cull && n > 1) {
-    n = ft_cull(gtab, n, lane, (float)(ix0 - o.x), (float)(ix1 - 1 - o.x), (float)(iy0 - o.y),
-                (float)(iy1 - 1 - o.y), wtab);
+  if ((a.cull & 1) && n > 1) {
+    n = cull_components<true>(gtab, n, lane, (float)(ix0 - o.x), (float)(ix1 - 1 - o.x), (float)(iy0 - o.y),
+                              (float)(iy1 - 1 - o.y), 3.f, wtab, &recur);
+    recur = recur && FT_RECUR && !(a.cull & 2);
   } else {
     // no culling: copy the quadratics as they are (the eval loops read shared memory only)
     for (int k = lane; k < n; k += 32) {
@@ -1105,13 +1151,16 @@ __device__ __forceinline__ void ft_source(const FieldArgs& a, int item, int K, i
   const bool doA = iy0 < q.Y0 + 8, doB = iy1 > q.Y0 + 8;         // which row halves the footprint reaches
   float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
   if (doA && doB) {
-    ft_eval2(tb, n, (float)(q.yA - o.y), (float)(q.yB - o.y), xl, acc0, acc1);
+    if (recur) ft_eval2r(tb, n, (float)(q.yA - o.y), (float)(q.yB - o.y), xl[0], acc0, acc1);
+    else ft_eval2(tb, n, (float)(q.yA - o.y), (float)(q.yB - o.y), xl, acc0, acc1);
     if (lane == 0) issued += (unsigned long long)n * 256;
   } else if (doA) {
-    ft_eval1(tb, n, (float)(q.yA - o.y), xl, acc0);
+    if (recur) ft_eval1r(tb, n, (float)(q.yA - o.y), xl[0], acc0);
+    else ft_eval1(tb, n, (float)(q.yA - o.y), xl, acc0);
     if (lane == 0) issued += (unsigned long long)n * 128;
   } else {
-    ft_eval1(tb, n, (float)(q.yB - o.y), xl, acc1);
+    if (recur) ft_eval1r(tb, n, (float)(q.yB - o.y), xl[0], acc1);
+    else ft_eval1(tb, n, (float)(q.yB - o.y), xl, acc1);
     if (lane == 0) issued += (unsigned long long)n * 128;
   }
   const bool inA = q.yA >= bx.z && q.yA < bx.w, inB = q.yB >= bx.z && q.yB < bx.w;
@@ -2428,6 +2477,7 @@ static int fill_imgs(CgImage* const* imgs, int n_img, ImgPtrs* out) {
 }  // extern "C"
 
 static int g_cull = 1;
+static int g_recur = 1;   // CG_OPT_ROW_RECURRENCE
 
 // persistent grid: one CTA per resident slot
 template <typename real, int MODE>
@@ -2514,7 +2564,7 @@ int cg_render_patches(CgImage* const* imgs, int32_t n_img, const CgSource* d_src
   if (rc) return rc;
   RenderArgs ra;
   memset(&ra, 0, sizeof ra);
-  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.worklist_cap = pa.worklist_cap; ra.cull = g_cull; ra.logtab = g_d_logtab; ra.cnt = cnt;
+  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.worklist_cap = pa.worklist_cap; ra.cull = g_cull | (g_recur ? 0 : 2); ra.logtab = g_d_logtab; ra.cnt = cnt;
   ra.patches = d_patches; ra.max_patch_px = max_patch_px;
   rc = run_render<float, MODE_PATCH>(ra, n_items, st);
   g_last_counters = cnt;
@@ -2583,7 +2633,7 @@ int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off, const CgSou
   fa.order = (int2*)(base + L.order); fa.sched = (int*)(base + L.done);
   fa.block_partials = (double*)(base + L.tiles); fa.ll = d_ll;
   fa.max_tiles = max_bins; fa.tiles_total = max_bins * n_img;
-  fa.logtab = g_d_logtab; fa.cnt = cnt; fa.cull = g_cull;
+  fa.logtab = g_d_logtab; fa.cnt = cnt; fa.cull = g_cull | (g_recur ? 0 : 2);
   if (h_d_model) {
     bool any = false;
     for (int i = 0; i < n_img; ++i) any = any || h_d_model[i];
@@ -2616,6 +2666,7 @@ int cg_field_loglik(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs,
 int cg_set_option(int32_t option, int32_t value) {
   switch (option) {
     case CG_OPT_CULL: g_cull = value ? 1 : 0; return CG_OK;
+    case CG_OPT_ROW_RECURRENCE: g_recur = value ? 1 : 0; return CG_OK;
     default: return fail(CG_EINVAL, "unknown option %d", option);
   }
 }
@@ -2651,7 +2702,7 @@ int cg_items_loglik(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs,
   pa.cnt = cnt; pa.out_boxes = d_boxes; pa.filters = g_d_filters;
   RenderArgs ra;
   memset(&ra, 0, sizeof ra);
-  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.worklist_cap = pa.worklist_cap; ra.cull = g_cull; ra.logtab = g_d_logtab; ra.cnt = cnt;
+  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.worklist_cap = pa.worklist_cap; ra.cull = g_cull | (g_recur ? 0 : 2); ra.logtab = g_d_logtab; ra.cnt = cnt;
   ra.aux = d_aux; ra.aux_offsets = (const long long*)d_aux_offsets;
   ra.partials = (double*)(base + L.partials);
   ra.cond_sum = (mode == CG_LL_CONDITIONAL_SUM);
@@ -2717,7 +2768,7 @@ int cg_score_proposals(CgImage* const* imgs, int32_t n_img, const CgSource* d_sr
   if (rc) return rc;
   RenderArgs ra;
   memset(&ra, 0, sizeof ra);
-  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.worklist_cap = pa.worklist_cap; ra.cull = g_cull; ra.logtab = g_d_logtab; ra.cnt = cnt;
+  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.worklist_cap = pa.worklist_cap; ra.cull = g_cull | (g_recur ? 0 : 2); ra.logtab = g_d_logtab; ra.cnt = cnt;
   ra.aux = d_bg; ra.aux_offsets = d_off; ra.partials = (double*)(base + L.partials);
   rc = run_render<float, MODE_POISSON>(ra, n_items, st);
   if (rc) return rc;

@@ -209,6 +209,11 @@ int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off,
  * components whose largest value over the warp's pixels is below 2^-27 of a
  * lower bound of the mixture there (bounded relative error K*2^-27 on a rate). */
 #define CG_OPT_CULL 1
+/* CG_OPT_ROW_RECURRENCE (default 1): the full-frame kernel evaluates a component at
+ * the 4 consecutive pixels of a lane from 2 exp2 and the geometric recurrence
+ * e(x+1) = e(x) g(x), g(x+1) = g(x) 2^(2A) (about 1.5e-6 relative on a rate) where
+ * that is provably safe; 0 = one exp2 per pixel everywhere. */
+#define CG_OPT_ROW_RECURRENCE 2
 int cg_set_option(int32_t option, int32_t value);
 
 /* Likelihood modes of cg_items_loglik */

@@ -303,6 +303,7 @@ def test_component_culling_error_bound(engine):
     gimgs = hp.gpu_images(engine, field, zeros)
     gs = hp.gpu_sources(engine, field)
     try:
+        engine.set_option(_ffi.CG_OPT_ROW_RECURRENCE, 0)      # culling alone: one exp2 per pixel on both sides
         engine.set_option(_ffi.CG_OPT_CULL, 0)
         full, boxes = engine.render_patches(gimgs, gs)
         issued_full = engine.last_issued_count()
@@ -311,6 +312,7 @@ def test_component_culling_error_bound(engine):
         issued_cull = engine.last_issued_count()
     finally:
         engine.set_option(_ffi.CG_OPT_CULL, 1)
+        engine.set_option(_ffi.CG_OPT_ROW_RECURRENCE, 1)
     assert np.array_equal(boxes, boxes2)
     full, culled = full.cpu().numpy().astype(np.float64), culled.cpu().numpy().astype(np.float64)
     assert np.all(culled <= full * (1 + 1e-6))
@@ -319,6 +321,63 @@ def test_component_culling_error_bound(engine):
     print("culling: max relative deficit %.3g, issued %.3g -> %.3g lane-evals" % (rel, issued_full, issued_cull))
     assert rel <= 42 * 2.0 ** -27 + 2.5e-7          # + fp32 summation-order slack
     assert issued_cull < issued_full
+
+
+def test_row_recurrence_error_bound(engine):
+    """CG_OPT_ROW_RECURRENCE: 2 exp2 + the geometric recurrence along 4 pixels instead
+    of 4 exp2.  Against the one-exp2-per-pixel path of the same kernels a rate moves
+    by a few fp32 roundings: below 5e-6 relative wherever the pixel matters, below the
+    north star's 1e-5 down to 1e-12 of the patch peak (the error grows with the log2
+    ratio of neighbouring pixels, i.e. in the far tail of narrow components), in
+    render_kernel and in the fused field kernel alike."""
+    from desi_mcmc_b200 import _ffi
+    field = synth.make_field(84, H=220, W=260, n_src=12, star_frac=.3)
+    gimgs = hp.gpu_images(engine, field, [np.zeros((220, 260))] * 5)
+    gs = hp.gpu_sources(engine, field)
+    try:
+        engine.set_option(_ffi.CG_OPT_ROW_RECURRENCE, 0)
+        exact, boxes = engine.render_patches(gimgs, gs)
+        ll0, m0 = engine.field_loglik(gimgs, gs, return_model=True)
+        engine.set_option(_ffi.CG_OPT_ROW_RECURRENCE, 1)
+        recur, boxes2 = engine.render_patches(gimgs, gs)
+        ll1, m1 = engine.field_loglik(gimgs, gs, return_model=True)
+    finally:
+        engine.set_option(_ffi.CG_OPT_ROW_RECURRENCE, 1)
+    assert np.array_equal(boxes, boxes2)
+    exact, recur = exact.cpu().numpy().astype(np.float64), recur.cpu().numpy().astype(np.float64)
+    assert np.all(np.isfinite(recur))
+    assert not np.array_equal(exact, recur)               # the recurrence path did run
+    # per patch, like the oracle parity tests: values below RATE_FLOOR x peak compared absolutely
+    peak = exact.max(axis=1, keepdims=True)
+    err = np.abs(recur - exact)
+    rel_p = np.max(err / np.maximum(exact, RATE_FLOOR * np.maximum(peak, 1e-300)))
+    # where a pixel holds more than 2^-27 of its patch's peak (the culling tolerance)
+    rel_core = np.max(np.where(exact > peak * 2.0 ** -27, err / np.maximum(exact, 1e-300), 0.0))
+    rel_m = max(hp.rel_err(b.cpu().numpy(), a.cpu().numpy(), 0.0) for a, b in zip(m0, m1))
+    print("row recurrence: max relative change: patches %.3g (above 2^-27 of the peak %.3g), model image %.3g"
+          % (rel_p, rel_core, rel_m))
+    assert rel_p < RATE_RTOL and rel_core < 5e-6 and rel_m < 4e-6
+    assert np.all(np.abs((ll1 - ll0).cpu().numpy()) <= 1e-7 * np.abs(ll0.cpu().numpy()))
+
+
+def test_row_recurrence_falls_back_on_steep_components(engine, oracle):
+    """A PSF far narrower than a pixel makes neighbouring pixels differ by more than
+    2^96: the recurrence must not be used there (no inf/NaN), and the result still
+    matches the oracle."""
+    field = synth.make_stamp(87, size=48, n_star=2, n_gal=1)
+    for m in field["images"]:
+        m["psf_covars"] = np.asarray(m["psf_covars"]) * 0.004          # sigma ~ 0.06-0.1 px
+    nelec = hp.simulate_nelec(oracle, field, 8)
+    gimgs = hp.gpu_images(engine, field, nelec)
+    oimgs = hp.oracle_images(oracle, field, nelec)
+    ll, models = engine.field_loglik(gimgs, hp.gpu_sources(engine, field), return_model=True)
+    osrcs = hp.oracle_sources(oracle, field)
+    for i, img in enumerate(oimgs):
+        got = models[i].cpu().numpy()
+        assert np.all(np.isfinite(got))
+        assert hp.rel_err(got, oracle.gen_model_image(osrcs, img), 1.0) < RATE_RTOL
+    patches, _ = engine.render_patches(gimgs, hp.gpu_sources(engine, field))
+    assert np.all(np.isfinite(patches.cpu().numpy()))
 
 
 def test_field_loglik_crowded_tile_overflow(engine, oracle):
