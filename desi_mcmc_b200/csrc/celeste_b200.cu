@@ -962,6 +962,9 @@ struct FieldArgs {
 #define FT_MINB 3
 #endif
 #define FT_CHUNK 8
+#ifndef FT_SMALLK
+#define FT_SMALLK 4         // mixtures up to this size are evaluated whole (no culling)
+#endif
 #define FT_LIGHT 2          // classes below this are latency-bound (no galaxy in the bin)
 // bins per claimed work unit by weight class: heavy bins one at a time (balance), sky in bulk
 __device__ __forceinline__ constexpr int ft_chunk(int cls) {
@@ -1014,7 +1017,14 @@ __global__ void __launch_bounds__(256) bin_order_kernel(FieldArgs a) {
     int base = 0;
     if ((int)lane == leader) base = atomicAdd(&a.sched[b], __popc(peers));
     base = __shfl_sync(peers, base, leader);
-    a.order[(long long)b * a.tiles_total + base + __popc(peers & ((1u << lane) - 1u))] = make_int2(g, cnt);
+    // descriptor: image (8 bits) | bin column (12) | bin row (12), list length -- the tile
+    // kernel then needs no division to place the bin
+    const int img = g / a.max_tiles, t = g - img * a.max_tiles;
+    int bx;
+    bins_of(*a.imgs.p[img], &bx);
+    const int by = t / bx;
+    a.order[(long long)b * a.tiles_total + base + __popc(peers & ((1u << lane) - 1u))] =
+        make_int2((img << 24) | ((t - by * bx) << 12) | by, cnt);
   }
 }
 
@@ -1130,7 +1140,22 @@ __device__ __forceinline__ void ft_source(const FieldArgs& a, int item, int K, i
   int n = K;
   bool recur = false;
   __syncwarp();                       // the warp is done reading its previous table
-  if ((a.cull & 1) && n > 1) {
+  if ((a.cull & 1) && n > 1 && n <= FT_SMALLK) {
+    // a star's PSF mixture: culling would cost more than the few evaluations it can save;
+    // copy the quadratics, add (h, k8) and the recurrence range check of cull_components
+    const float xa = (float)(ix0 - o.x), xb = (float)(ix1 - 1 - o.x), ya = (float)(iy0 - o.y), yb = (float)(iy1 - 1 - o.y);
+    float dmx = 0.f;
+    if (lane < n) {
+      const float4* t4 = reinterpret_cast<const float4*>(gtab + lane * TAB_W);
+      const float4 e0 = __ldg(t4), e1 = __ldg(t4 + 1);
+      const float fx = fmaxf(fabsf(xa - e1.z), fabsf(xb - e1.z)), fy = fmaxf(fabsf(ya - e1.w), fabsf(yb - e1.w));
+      dmx = fmaxf(fmaf(fabsf(e0.x), 2.f * (fx + 3.f) + 1.f, fabsf(e0.y) * fy), 8.f * fabsf(e0.y));
+      *reinterpret_cast<float4*>(wtab + lane * 8) = e0;
+      *reinterpret_cast<float4*>(wtab + lane * 8 + 4) = make_float4(e1.x, e1.y, ex2_approx(2.f * e0.x), ex2_approx(8.f * e0.y));
+    }
+    recur = !__any_sync(0xffffffffu, !(dmx <= FT_RECUR_DMAX)) && FT_RECUR && !(a.cull & 2);
+    __syncwarp();
+  } else if ((a.cull & 1) && n > 1) {
     n = cull_components<true>(gtab, n, lane, (float)(ix0 - o.x), (float)(ix1 - 1 - o.x), (float)(iy0 - o.y),
                               (float)(iy1 - 1 - o.y), 3.f, wtab, &recur);
     recur = recur && FT_RECUR && !(a.cull & 2);
@@ -1162,6 +1187,14 @@ __device__ __forceinline__ void ft_source(const FieldArgs& a, int item, int K, i
     if (recur) ft_eval1r(tb, n, (float)(q.yB - o.y), xl[0], acc1);
     else ft_eval1(tb, n, (float)(q.yB - o.y), xl, acc1);
     if (lane == 0) issued += (unsigned long long)n * 128;
+  }
+  if (ix1 - ix0 == BIN_W && iy1 - iy0 == BIN_H) {                 // the footprint covers the bin: no masks
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      lam[0][p] += acc0[p] * fl;
+      lam[1][p] += acc1[p] * fl;
+    }
+    return;
   }
   const bool inA = q.yA >= bx.z && q.yA < bx.w, inB = q.yB >= bx.z && q.yB < bx.w;
 #pragma unroll
@@ -1237,14 +1270,15 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
     if (c1 < total) dnext = load_unit(c1);
 
    for (int cj = 0; cj < FT_CHUNK; ++cj) {
-    const int g = __shfl_sync(0xffffffffu, dcur.x, cj), cnt = __shfl_sync(0xffffffffu, dcur.y, cj);
-    if (g < 0) break;
-    const int img = g / a.max_tiles, bin = g - img * a.max_tiles;
+    const int dsc = __shfl_sync(0xffffffffu, dcur.x, cj), cnt = __shfl_sync(0xffffffffu, dcur.y, cj);
+    if (dsc < 0) break;
+    const int img = dsc >> 24;
     const DevImage& im = *a.imgs.p[img];
     const int H = im.H, W = im.W;
     const int bins_x = (W + BIN_W - 1) / BIN_W;
     FtGeom q;
-    q.X0 = (bin % bins_x) * BIN_W; q.Y0 = (bin / bins_x) * BIN_H;
+    q.X0 = ((dsc >> 12) & 0xfff) * BIN_W; q.Y0 = (dsc & 0xfff) * BIN_H;
+    const int g = img * a.max_tiles + (dsc & 0xfff) * bins_x + ((dsc >> 12) & 0xfff);
     q.x = q.X0 + (lane & 3) * 4; q.yA = q.Y0 + (lane >> 2); q.yB = q.yA + 8;
 
     // pixel counts: independent of the source list, issue the loads first
@@ -2610,6 +2644,8 @@ int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off, const CgSou
   for (int i = 0; i < n_img; ++i) {
     max_tiles = std::max(max_tiles, (int)cg_field_tiles(imgs[i]->h.H, imgs[i]->h.W));
     if (!imgs[i]->h.nelec) return fail(CG_EINVAL, "image %d has no nelec buffer", i);
+    if (imgs[i]->h.H > 4096 * BIN_H || imgs[i]->h.W > 4096 * BIN_W)       // 12-bit bin coordinates (bin_order_kernel)
+      return fail(CG_EINVAL, "image %d is larger than %d x %d pixels", i, 4096 * BIN_W, 4096 * BIN_H);
   }
   WsLayout L = ws_layout(std::max<long long>(n_items, 1), max_patch_px, 1, 0, (long long)max_tiles * n_img);
   if (L.total > ws_bytes) return fail(CG_ENOMEM, "workspace too small: need %zu bytes, have %zu", L.total, ws_bytes);
