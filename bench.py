@@ -409,7 +409,14 @@ def main():
     if rank == 0:
         xu_peak = engine.pipe_probe(0)
         fma_peak = engine.pipe_probe(1)
-        mix_peak = engine.pipe_probe(2)         # the inner-loop instruction mix in isolation, 24 warps/SM
+        mix_peak = engine.pipe_probe(6)         # the row-recurrence inner loop in isolation, 24 warps/SM
+        # Per component and lane (8 pixels) the loop issues 2 LDS + 30 FP32-pipe instructions
+        # (11 FFMA, 11 FMUL, 8 FADD) + 3 MUFU.EX2 = 35 issue slots: 4.375 per evaluation, of which
+        # 3.75 on the FP32 pipe and 0.375 on the XU pipe.  The FP32 pipe issues one warp
+        # instruction per SM sub-partition per clock, which is also the issue limit, so the
+        # bound is the measured FP32 rate / 4.375; the XU bound (xu_peak / 0.375) lies above it.
+        SLOTS_PER_EVAL, MUFU_PER_EVAL = 35.0 / 8.0, 3.0 / 8.0
+        issue_peak = fma_peak / SLOTS_PER_EVAL
         achieved = evals_step * args.steps / (render_ms * 1e-3) if render_ms > 0 else None
         sm = engine.sm_count()
         nominal = sm * 16 * (clocks["sm_mhz"] or 0) * 1e6
@@ -434,26 +441,34 @@ def main():
             "e2e": {"value": e2e_value, "unit": "evals/s", "ms_per_step": 1e3 * e2e_s / args.steps,
                     "h2d_bytes_per_step": F * N_SRC * _ffi.SRC_DTYPE.itemsize, "d2h_bytes_per_step": F * 5 * 8},
             "gpu_launches": launches,
-            "roofline": {"kernel": "field_tile_kernel", "bound": "xu",
-                         "achieved": achieved, "peak": xu_peak, "unit": "evals/s (1 eval = 1 MUFU.EX2 + 3 FP32)",
-                         "frac": (achieved / xu_peak) if achieved else None,
-                         "peak_source": "measured live: MUFU.EX2 probe kernel on this GPU (cg_pipe_probe); "
-                                        "nominal %d SMs x 16/clk x %.0f MHz = %.3g" % (sm, clocks["sm_mhz"] or 0, nominal),
+            "roofline": {"kernel": "field_tile_kernel", "bound": "fp32 issue",
+                         "achieved": achieved, "peak": issue_peak,
+                         "unit": "evals/s (1 eval = 1 component at 1 pixel = 4.375 issue slots: 3.75 FP32 + 0.375 MUFU.EX2 + 0.25 LDS)",
+                         "frac": (achieved / issue_peak) if achieved else None,
+                         "peak_source": "measured live on this GPU (cg_pipe_probe): FP32 FMA lane-instructions/s / 4.375; "
+                                        "nominal %d SMs x 128/clk x %.0f MHz / 4.375 = %.3g; the XU bound "
+                                        "(MUFU.EX2 probe / 0.375 = %.3g) lies above it" %
+                                        (sm, clocks["sm_mhz"] or 0, sm * 128 * (clocks["sm_mhz"] or 0) * 1e6 / SLOTS_PER_EVAL,
+                                         xu_peak / MUFU_PER_EVAL),
                          "issued": (issued_step * args.steps / (render_ms * 1e-3)) if render_ms > 0 else None,
-                         "issued_frac": (issued_step * args.steps / (render_ms * 1e-3) / xu_peak) if render_ms > 0 else None,
+                         "issued_frac": (issued_step * args.steps / (render_ms * 1e-3) / issue_peak) if render_ms > 0 else None,
                          "note": "achieved = algorithmic evals (footprint pixels x components, SURVEY 8d) / kernel time; "
-                                 "issued = MUFU.EX2 lane-operations actually executed after per-warp component culling",
-                         "mix_ceiling": {"value": mix_peak, "frac_of_peak": mix_peak / xu_peak,
-                                         "note": "MUFU.EX2 lane-ops/s the kernel's inner loop (2 LDS + 6 row-term FFMA per "
-                                                 "component, then 2 FFMA + MUFU + FADD per pixel) reaches in isolation "
-                                                 "(cg_pipe_probe(2): no global memory, every lane busy); compare with `issued`"},
+                                 "issued = lane-evaluations actually executed after per-warp component culling. "
+                                 "Up to v11 every eval cost one MUFU.EX2 and the bound was the XU pipe "
+                                 "(`xu_frac` = achieved / that peak, kept for comparison); the row recurrence "
+                                 "needs 0.375 MUFU.EX2 per eval and moved the bound to instruction issue",
+                         "xu_peak": xu_peak, "xu_frac": (achieved / xu_peak) if achieved else None,
+                         "mix_ceiling": {"value": mix_peak, "frac_of_peak": mix_peak / issue_peak,
+                                         "note": "evals/s the kernel's inner loop (ft_eval2r: 2 LDS + 11 FFMA + 11 FMUL + 8 FADD "
+                                                 "+ 3 MUFU.EX2 per component and lane) reaches in isolation "
+                                                 "(cg_pipe_probe(6): no global memory, every lane busy); compare with `issued`"},
                          "fp32_fma_peak": fma_peak, "kernel_ms_total": render_ms, "kernel_launches": render_n,
                          "kernel_share_of_step": render_ms / serial_ms if serial_ms else None,
                          "serial_ms_per_step": serial_ms / args.steps,
                          # dram__bytes_read.sum + dram__bytes_write.sum of one timed 8-field launch from the
-                         # ncu --set full capture summarised in profiles/r01_prof_tile_v10_*: 672.2 + 4.5 MB
+                         # ncu --set full capture summarised in profiles/r01_prof_tile_v12_*: 667.3 + 5.0 MB
                          # (algorithmic: 4 B of nelec per pixel = 488 MB); scaled to this launch's fields
-                         "traffic": 676.64e6 * FPC / 8.0,
+                         "traffic": 672.33e6 * FPC / 8.0,
                          "traffic_algorithmic": FPC * 5 * H * W * 4,
                          "hbm_peak_gbs": peaks.get("hbm_gbs")},
             "clocks": clocks,

@@ -962,6 +962,11 @@ struct FieldArgs {
 #define FT_MINB 3
 #endif
 #define FT_CHUNK 8
+#ifndef FT_UNROLL
+#define FT_UNROLL 2         // components per trip of the recurrence loops
+#endif
+#define FT_PRAGMA_(x) _Pragma(#x)
+#define FT_PRAGMA(x) FT_PRAGMA_(x)
 #ifndef FT_SMALLK
 #define FT_SMALLK 4         // mixtures up to this size are evaluated whole (no culling)
 #endif
@@ -1095,7 +1100,7 @@ __device__ __forceinline__ void ft_eval2r(const float* tb, int n, float y0l, flo
   const float tx = 2.f * x0 + 1.f;
   float4 t0 = *reinterpret_cast<const float4*>(tb);      // A, B, C, b10
   float4 t1 = *reinterpret_cast<const float4*>(tb + 4);  // c01, c00, h, k8
-#pragma unroll 2
+FT_PRAGMA(unroll FT_UNROLL)
   for (int k = 0; k < n; ++k) {
     tb += 8;
     const float4 n0 = *reinterpret_cast<const float4*>(tb);
@@ -1115,7 +1120,7 @@ __device__ __forceinline__ void ft_eval1r(const float* tb, int n, float yl, floa
   const float tx = 2.f * x0 + 1.f;
   float4 t0 = *reinterpret_cast<const float4*>(tb);
   float4 t1 = *reinterpret_cast<const float4*>(tb + 4);
-#pragma unroll 2
+FT_PRAGMA(unroll FT_UNROLL)
   for (int k = 0; k < n; ++k) {
     tb += 8;
     const float4 n0 = *reinterpret_cast<const float4*>(tb);
@@ -2149,6 +2154,29 @@ __global__ void __launch_bounds__(256) mix_probe_kernel(float* out, int iters) {
   if (sacc == 123.456f) out[blockIdx.x * blockDim.x + threadIdx.x] = sacc;
 }
 
+// which = 6 (16 at 8 CTAs/SM): the row-recurrence loop of the field kernel (ft_eval2r) on a
+// 32-component shared-memory table.  Result: component x pixel evaluations/s.
+__global__ void __launch_bounds__(256) recur_probe_kernel(float* out, int iters) {
+  __shared__ __align__(16) float s_tab[8][33 * 8];
+  float* tb = s_tab[threadIdx.x >> 5];
+  for (int i = threadIdx.x & 31; i < 33 * 8; i += 32) {
+    const int c = i & 7;
+    tb[i] = (c == 6) ? 0.998f : (c == 7) ? 1.001f : -1e-3f * (float)(1 + (i % 5));
+  }
+  __syncwarp();
+  float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
+  float x0 = 0.25f * (float)((threadIdx.x & 3) * 4);
+  const float y0l = 0.125f * (float)((threadIdx.x & 31) >> 2), y1l = y0l + 1.f;
+  for (int i = 0; i < iters; ++i) {
+    ft_eval2r(tb, 32, y0l, y1l, x0, acc0, acc1);
+    x0 += 1e-7f;            // keep the loop body loop-variant
+  }
+  float sacc = 0.f;
+#pragma unroll
+  for (int p = 0; p < 4; ++p) sacc += acc0[p] + acc1[p];
+  if (sacc == 123.456f) out[blockIdx.x * blockDim.x + threadIdx.x] = sacc;
+}
+
 // per-launch CUDA-event timing of render_kernel (bench.py's roofline leg)
 #define PROF_MAX 8192
 static bool g_prof_on = false;
@@ -3002,8 +3030,8 @@ int cg_profile_render_read(double* total_ms, int64_t* launches) {
 int cg_pipe_probe(int which, double* ops_per_s, void* stream) {
   NEED_INIT();
   cudaStream_t st = (cudaStream_t)stream;
-  // which: 0 MUFU.EX2, 1 FFMA; 2..5 instruction-mix probes at 3 CTAs/SM (24 warps, the tile
-  // kernel's residency), 12..15 the same mixes at 8 CTAs/SM (64 warps)
+  // which: 0 MUFU.EX2, 1 FFMA; 2..5 instruction-mix probes and 6 the row-recurrence loop at
+  // 3 CTAs/SM (24 warps, the tile kernel's residency), 12..16 the same at 8 CTAs/SM (64 warps)
   const int var = which % 10;
   const int iters = var >= 2 ? 128 : 4096, blocks = g_sm_count * ((which >= 2 && which < 10) ? 3 : 8), threads = 256;
   float* d_out = nullptr;
@@ -3019,7 +3047,8 @@ int cg_pipe_probe(int which, double* ops_per_s, void* stream) {
     else if (var == 2) mix_probe_kernel<2><<<blocks, threads, 0, st>>>(d_out, iters);
     else if (var == 3) mix_probe_kernel<3><<<blocks, threads, 0, st>>>(d_out, iters);
     else if (var == 4) mix_probe_kernel<4><<<blocks, threads, 0, st>>>(d_out, iters);
-    else mix_probe_kernel<5><<<blocks, threads, 0, st>>>(d_out, iters);
+    else if (var == 5) mix_probe_kernel<5><<<blocks, threads, 0, st>>>(d_out, iters);
+    else recur_probe_kernel<<<blocks, threads, 0, st>>>(d_out, iters);
     CUDA_TRY(cudaEventRecord(e1, st));
     LAUNCH_CHECK();
     CUDA_TRY(cudaEventSynchronize(e1));
