@@ -175,6 +175,7 @@ struct Counters {
 #define FT_RECUR 1          // row recurrence compiled in (run-time switch: CG_OPT_ROW_RECURRENCE)
 #endif
 #define FT_RECUR_DMAX 96.f   // largest |log2 ratio of neighbouring pixels| the row recurrence is used for
+#define FT_RECUR_FLOOR -64.f // log2 of the unit-flux rate below which a value lost to underflow does not count
 #define TAB_STRIDE (CG_MAX_COMP * TAB_W)
 
 #define STRIP_THREADS 256
@@ -254,6 +255,19 @@ __device__ __forceinline__ float rexp2(float x) { return ex2_approx(x); }
 __device__ __forceinline__ double rexp2(double x) { return exp2(x); }
 __device__ __forceinline__ float rfma(float a, float b, float c) { return fmaf(a, b, c); }
 __device__ __forceinline__ double rfma(double a, double b, double c) { return fma(a, b, c); }
+// Row recurrence, underflow side.  ex2.approx.ftz returns 0 below 2^-126, and a lane whose
+// first pixel x0 flushed carries 0 to its other three pixels.  Along a row the component is
+// 2^(qr - |A| t^2), t = distance to the row's peak, qr <= qs (its global peak).  A flushed
+// start means t > D = sqrt((qs + 124) / |A|); the largest value the lane can then lose is at
+// x0 + 3: qs - |A| (D - 3)^2 = -124 + 6 |A| D - 9 |A| (the peak itself if D < 3).  A
+// component is marked unsafe for the recurrence (prepare_kernel, sign of table entry 9) when
+// that exceeds FT_RECUR_FLOOR, i.e. for Gaussians narrower than about 0.8 pixel.
+__device__ __forceinline__ bool recur_flush_unsafe(double A, double qs) {
+  const double aA = fabs(A);
+  const double AD = sqrt(aA * fmax(qs + 124., 0.));               // |A| D
+  const double lost = (AD >= 3. * aA) ? (-124. + 6. * AD - 9. * aA) : qs;
+  return !(lost <= (double)FT_RECUR_FLOOR);
+}
 // four consecutive pixels of a row from the first value e, the neighbour ratio g and the
 // ratio of ratios h (see "Row recurrence" at ft_eval2r)
 template <typename T>
@@ -504,7 +518,8 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
     t[6] = (real)mx;
     t[7] = (real)my;
     t[8] = (real)k2;
-    t[9] = (real)(2. * s00 / LOG2E_D);
+    // the sign of t[9] carries recur_flush_unsafe (the value itself is positive)
+    t[9] = (real)(recur_flush_unsafe(A, k2) ? -(2. * s00 / LOG2E_D) : (2. * s00 / LOG2E_D));
     t[10] = (real)(2. * s11 / LOG2E_D);
     {
       const double dd = s00 - s11;
@@ -696,7 +711,7 @@ __device__ __forceinline__ int cull_components(const float* gtab, int K, int lan
       e1[r] = LDG ? __ldg(t4 + 1) : t4[1];
       const float4 e2 = LDG ? __ldg(t4 + 2) : t4[2];
       const float mx = e1[r].z, my = e1[r].w;
-      qs[r] = e2.x; kx[r] = e2.y; ky[r] = e2.z;
+      qs[r] = e2.x; kx[r] = fabsf(e2.y); ky[r] = e2.z;
       const float fx = fmaxf(fabsf(xa - mx), fabsf(xb - mx)), fy = fmaxf(fabsf(ya - my), fabsf(yb - my));
       const float l = qs[r] - e2.w * (fx * fx + fy * fy);
       if (l == l) lb = fmaxf(lb, l);
@@ -705,6 +720,7 @@ __device__ __forceinline__ int cull_components(const float* gtab, int K, int lan
       // bound of |q(x+1,y) - q(x,y)| = |2A(x-mx) + B(y-my) + A| over the rectangle widened
       // by the xext pixels a lane's group of 4 may start to the left of it; 8|B| bounds k8
       dmx[r] = fmaxf(fmaf(fabsf(e0[r].x), 2.f * (fx + xext) + 1.f, fabsf(e0[r].y) * fy), 8.f * fabsf(e0[r].y));
+      if (e2.y < 0.f) dmx[r] = INFINITY;                         // recur_flush_unsafe (prepare_kernel)
     }
   }
 #pragma unroll
@@ -1092,9 +1108,9 @@ __device__ __forceinline__ void ft_eval1(const float* tb, int n, float yl,
 // bound and the loop becomes issue-bound (35 instructions per 8 pixels, was 40).
 // Every product stays the true pixel value times roundings (6 roundings + 3 exp2 at
 // the fourth pixel, ~1.5e-6 relative); it is taken only when cull_components proved
-// |q(x+1)-q(x)| <= FT_RECUR_DMAX on the lanes that count (no overflow of g, and a
-// flushed e0 stands for values below 2^(-126+96) of a unit-flux profile, the culling
-// tolerance), otherwise ft_eval2/1.
+// |q(x+1)-q(x)| <= FT_RECUR_DMAX on the lanes that count (no overflow of g) and that a
+// first pixel flushed to zero cannot hide a value that counts (recur_flush_unsafe, decided per component in prepare_kernel),
+// otherwise ft_eval2/1.
 __device__ __forceinline__ void ft_eval2r(const float* tb, int n, float y0l, float y1l,
                                           float x0, float (&acc0)[4], float (&acc1)[4]) {
   const float tx = 2.f * x0 + 1.f;
@@ -1153,8 +1169,9 @@ __device__ __forceinline__ void ft_source(const FieldArgs& a, int item, int K, i
     if (lane < n) {
       const float4* t4 = reinterpret_cast<const float4*>(gtab + lane * TAB_W);
       const float4 e0 = __ldg(t4), e1 = __ldg(t4 + 1);
+      if (__ldg(gtab + lane * TAB_W + 9) < 0.f) dmx = INFINITY;    // recur_flush_unsafe (prepare_kernel)
       const float fx = fmaxf(fabsf(xa - e1.z), fabsf(xb - e1.z)), fy = fmaxf(fabsf(ya - e1.w), fabsf(yb - e1.w));
-      dmx = fmaxf(fmaf(fabsf(e0.x), 2.f * (fx + 3.f) + 1.f, fabsf(e0.y) * fy), 8.f * fabsf(e0.y));
+      dmx = fmaxf(dmx, fmaxf(fmaf(fabsf(e0.x), 2.f * (fx + 3.f) + 1.f, fabsf(e0.y) * fy), 8.f * fabsf(e0.y)));
       *reinterpret_cast<float4*>(wtab + lane * 8) = e0;
       *reinterpret_cast<float4*>(wtab + lane * 8 + 4) = make_float4(e1.x, e1.y, ex2_approx(2.f * e0.x), ex2_approx(8.f * e0.y));
     }

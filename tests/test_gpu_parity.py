@@ -380,6 +380,28 @@ def test_row_recurrence_falls_back_on_steep_components(engine, oracle):
     assert np.all(np.isfinite(patches.cpu().numpy()))
 
 
+@pytest.mark.parametrize("scale", [0.5, 0.15, 0.05])
+def test_row_recurrence_narrow_psf_parity(engine, oracle, scale):
+    """PSFs down to a fraction of a pixel wide: neighbouring pixels differ by large
+    factors, the regime where the recurrence's error is largest (and, for the
+    narrowest, where some warps fall back).  Rates still match the oracle to 1e-5."""
+    from desi_mcmc_b200 import _ffi
+    field = synth.make_stamp(88, size=40, n_star=2, n_gal=2)
+    for m in field["images"]:
+        m["psf_covars"] = np.asarray(m["psf_covars"]) * scale
+    assert _check_patches(engine, oracle, field, _ffi.CG_ITEM_FLUX_BAND, False) < RATE_RTOL
+    nelec = hp.simulate_nelec(oracle, field, 9)
+    gimgs = hp.gpu_images(engine, field, nelec)
+    oimgs = hp.oracle_images(oracle, field, nelec)
+    ll, models = engine.field_loglik(gimgs, hp.gpu_sources(engine, field), return_model=True)
+    ll = ll.cpu().numpy()
+    osrcs = hp.oracle_sources(oracle, field)
+    for i, img in enumerate(oimgs):
+        assert hp.rel_err(models[i].cpu().numpy(), oracle.gen_model_image(osrcs, img), 1.0) < RATE_RTOL
+        want = oracle.celeste_likelihood(osrcs, img)
+        assert abs(ll[i] - want) <= LL_RTOL * abs(want)
+
+
 def test_field_loglik_crowded_tile_overflow(engine, oracle):
     """More sources over one 64x16 image tile than a tile list holds (48): the
     gather falls back to scanning all sources; result still matches the oracle."""
