@@ -410,12 +410,12 @@ def main():
         xu_peak = engine.pipe_probe(0)
         fma_peak = engine.pipe_probe(1)
         mix_peak = engine.pipe_probe(6)         # the row-recurrence inner loop in isolation, 24 warps/SM
-        # Per component and lane (8 pixels) the loop issues 2 LDS + 30 FP32-pipe instructions
-        # (11 FFMA, 11 FMUL, 8 FADD) + 3 MUFU.EX2 = 35 issue slots: 4.375 per evaluation, of which
-        # 3.75 on the FP32 pipe and 0.375 on the XU pipe.  The FP32 pipe issues one warp
+        # Per component and lane (8 pixels) the loop issues 2 LDS + 28 FP32-pipe instructions
+        # (9 FFMA, 11 FMUL, 8 FADD) + 3 MUFU.EX2 = 33 issue slots: 4.125 per evaluation, of which
+        # 3.5 on the FP32 pipe and 0.375 on the XU pipe.  The FP32 pipe issues one warp
         # instruction per SM sub-partition per clock, which is also the issue limit, so the
-        # bound is the measured FP32 rate / 4.375; the XU bound (xu_peak / 0.375) lies above it.
-        SLOTS_PER_EVAL, MUFU_PER_EVAL = 35.0 / 8.0, 3.0 / 8.0
+        # bound is the measured FP32 rate / 4.125; the XU bound (xu_peak / 0.375) lies above it.
+        SLOTS_PER_EVAL, MUFU_PER_EVAL = 33.0 / 8.0, 3.0 / 8.0
         issue_peak = fma_peak / SLOTS_PER_EVAL
         achieved = evals_step * args.steps / (render_ms * 1e-3) if render_ms > 0 else None
         sm = engine.sm_count()
@@ -443,10 +443,10 @@ def main():
             "gpu_launches": launches,
             "roofline": {"kernel": "field_tile_kernel", "bound": "fp32 issue",
                          "achieved": achieved, "peak": issue_peak,
-                         "unit": "evals/s (1 eval = 1 component at 1 pixel = 4.375 issue slots: 3.75 FP32 + 0.375 MUFU.EX2 + 0.25 LDS)",
+                         "unit": "evals/s (1 eval = 1 component at 1 pixel = 4.125 issue slots: 3.5 FP32 + 0.375 MUFU.EX2 + 0.25 LDS)",
                          "frac": (achieved / issue_peak) if achieved else None,
-                         "peak_source": "measured live on this GPU (cg_pipe_probe): FP32 FMA lane-instructions/s / 4.375; "
-                                        "nominal %d SMs x 128/clk x %.0f MHz / 4.375 = %.3g; the XU bound "
+                         "peak_source": "measured live on this GPU (cg_pipe_probe): FP32 FMA lane-instructions/s / 4.125; "
+                                        "nominal %d SMs x 128/clk x %.0f MHz / 4.125 = %.3g; the XU bound "
                                         "(MUFU.EX2 probe / 0.375 = %.3g) lies above it" %
                                         (sm, clocks["sm_mhz"] or 0, sm * 128 * (clocks["sm_mhz"] or 0) * 1e6 / SLOTS_PER_EVAL,
                                          xu_peak / MUFU_PER_EVAL),
@@ -459,7 +459,7 @@ def main():
                                  "needs 0.375 MUFU.EX2 per eval and moved the bound to instruction issue",
                          "xu_peak": xu_peak, "xu_frac": (achieved / xu_peak) if achieved else None,
                          "mix_ceiling": {"value": mix_peak, "frac_of_peak": mix_peak / issue_peak,
-                                         "note": "evals/s the kernel's inner loop (ft_eval2r: 2 LDS + 11 FFMA + 11 FMUL + 8 FADD "
+                                         "note": "evals/s the kernel's inner loop (ft_eval2r: 2 LDS + 9 FFMA + 11 FMUL + 8 FADD "
                                                  "+ 3 MUFU.EX2 per component and lane) reaches in isolation "
                                                  "(cg_pipe_probe(6): no global memory, every lane busy); compare with `issued`"},
                          "fp32_fma_peak": fma_peak, "kernel_ms_total": render_ms, "kernel_launches": render_n,

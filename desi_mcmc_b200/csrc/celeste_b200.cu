@@ -978,6 +978,9 @@ struct FieldArgs {
 #define FT_MINB 3
 #endif
 #define FT_CHUNK 8
+#ifndef FT_ROWDELTA
+#define FT_ROWDELTA 1        // second row's exponent from the first's (ft_eval2r)
+#endif
 #ifndef FT_UNROLL
 #define FT_UNROLL 2         // components per trip of the recurrence loops
 #endif
@@ -1105,7 +1108,7 @@ __device__ __forceinline__ void ft_eval1(const float* tb, int n, float yl,
 // and h = 2^(2A): TWO exp2 and five multiplies for four pixels instead of four exp2
 // and six FMAs; the second row's g0 is the first row's times k8 = 2^(8B).  3 MUFU.EX2
 // per component for the lane's 8 pixels instead of 8: the XU pipe stops being the
-// bound and the loop becomes issue-bound (35 instructions per 8 pixels, was 40).
+// bound and the loop becomes issue-bound (33 instructions per 8 pixels, was 40).
 // Every product stays the true pixel value times roundings (6 roundings + 3 exp2 at
 // the fourth pixel, ~1.5e-6 relative); it is taken only when cull_components proved
 // |q(x+1)-q(x)| <= FT_RECUR_DMAX on the lanes that count (no overflow of g) and that a
@@ -1114,6 +1117,7 @@ __device__ __forceinline__ void ft_eval1(const float* tb, int n, float yl,
 __device__ __forceinline__ void ft_eval2r(const float* tb, int n, float y0l, float y1l,
                                           float x0, float (&acc0)[4], float (&acc1)[4]) {
   const float tx = 2.f * x0 + 1.f;
+  const float ysum = y0l + y1l;                          // y1l = y0l + 8 (rows r and r + 8 of the bin)
   float4 t0 = *reinterpret_cast<const float4*>(tb);      // A, B, C, b10
   float4 t1 = *reinterpret_cast<const float4*>(tb + 4);  // c01, c00, h, k8
 FT_PRAGMA(unroll FT_UNROLL)
@@ -1121,11 +1125,18 @@ FT_PRAGMA(unroll FT_UNROLL)
     tb += 8;
     const float4 n0 = *reinterpret_cast<const float4*>(tb);
     const float4 n1 = *reinterpret_cast<const float4*>(tb + 4);
-    const float b1a = fmaf(t0.y, y0l, t0.w), b1b = fmaf(t0.y, y1l, t0.w);
+    const float b1a = fmaf(t0.y, y0l, t0.w);
     const float c1a = fmaf(fmaf(t0.z, y0l, t1.x), y0l, t1.y);
-    const float c1b = fmaf(fmaf(t0.z, y1l, t1.x), y1l, t1.y);
-    const float ea = ex2_approx(fmaf(fmaf(t0.x, x0, b1a), x0, c1a));
-    const float eb = ex2_approx(fmaf(fmaf(t0.x, x0, b1b), x0, c1b));
+    const float qa = fmaf(fmaf(t0.x, x0, b1a), x0, c1a);
+#if FT_ROWDELTA
+    // q(x0, y + 8) - q(x0, y) = 8 (B x0 + C (2y + 8) + c01): 3 FFMA instead of the 5 of a second (b1, c1, q)
+    const float qb = fmaf(8.f, fmaf(t0.y, x0, fmaf(t0.z, ysum, t1.x)), qa);
+#else
+    const float b1b = fmaf(t0.y, y1l, t0.w);
+    const float qb = fmaf(fmaf(t0.x, x0, b1b), x0, fmaf(fmaf(t0.z, y1l, t1.x), y1l, t1.y));
+#endif
+    const float ea = ex2_approx(qa);
+    const float eb = ex2_approx(qb);
     const float ga = ex2_approx(fmaf(t0.x, tx, b1a));
     recur_row4(ea, ga, t1.z, acc0);
     recur_row4(eb, ga * t1.w, t1.z, acc1);
