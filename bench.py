@@ -410,13 +410,20 @@ def main():
         xu_peak = engine.pipe_probe(0)
         fma_peak = engine.pipe_probe(1)
         mix_peak = engine.pipe_probe(6)         # the row-recurrence inner loop in isolation, 24 warps/SM
-        # Per component and lane (8 pixels) the loop issues 2 LDS + 28 FP32-pipe instructions
-        # (9 FFMA, 11 FMUL, 8 FADD) + 3 MUFU.EX2 = 33 issue slots: 4.125 per evaluation, of which
-        # 3.5 on the FP32 pipe and 0.375 on the XU pipe.  The FP32 pipe issues one warp
-        # instruction per SM sub-partition per clock, which is also the issue limit, so the
-        # bound is the measured FP32 rate / 4.125; the XU bound (xu_peak / 0.375) lies above it.
-        SLOTS_PER_EVAL, MUFU_PER_EVAL = 33.0 / 8.0, 3.0 / 8.0
-        issue_peak = fma_peak / SLOTS_PER_EVAL
+        fma2_peak = engine.pipe_probe(7)        # FP32 FMA operations/s issued as packed FFMA2
+        # Per component and lane (8 pixels) the packed row-recurrence loop (ft_eval2r, SASS of
+        # recur_probe_kernel) issues 1 FFMA + 6 FFMA2 + 1 FMUL + 4 FMUL2 + 3 FADD2 (28 FP32
+        # operations per lane in 15 instructions) + 3 MUFU.EX2 + 2 LDS.128 + 2 MOV = 22 issue slots.
+        # Three ceilings, all from live probes on this GPU: the FP32 pipe (operations/s, the better
+        # of the FFMA and FFMA2 probes, / 3.5 per evaluation), the XU pipe (MUFU.EX2/s / 0.375) and
+        # instruction issue (one warp instruction per SM sub-partition per clock = the FFMA probe's
+        # instruction rate, / 2.75 slots per evaluation).  The lowest one is the roofline.
+        FP32_PER_EVAL, SLOTS_PER_EVAL, MUFU_PER_EVAL = 28.0 / 8.0, 22.0 / 8.0, 3.0 / 8.0
+        bounds = {"fp32 pipe": max(fma_peak, fma2_peak) / FP32_PER_EVAL,
+                  "xu pipe": xu_peak / MUFU_PER_EVAL,
+                  "instruction issue": fma_peak / SLOTS_PER_EVAL}
+        bound_name = min(bounds, key=bounds.get)
+        issue_peak = bounds[bound_name]
         achieved = evals_step * args.steps / (render_ms * 1e-3) if render_ms > 0 else None
         sm = engine.sm_count()
         nominal = sm * 16 * (clocks["sm_mhz"] or 0) * 1e6
@@ -441,28 +448,31 @@ def main():
             "e2e": {"value": e2e_value, "unit": "evals/s", "ms_per_step": 1e3 * e2e_s / args.steps,
                     "h2d_bytes_per_step": F * N_SRC * _ffi.SRC_DTYPE.itemsize, "d2h_bytes_per_step": F * 5 * 8},
             "gpu_launches": launches,
-            "roofline": {"kernel": "field_tile_kernel", "bound": "fp32 issue",
+            "roofline": {"kernel": "field_tile_kernel", "bound": bound_name,
                          "achieved": achieved, "peak": issue_peak,
-                         "unit": "evals/s (1 eval = 1 component at 1 pixel = 4.125 issue slots: 3.5 FP32 + 0.375 MUFU.EX2 + 0.25 LDS)",
+                         "unit": "evals/s (1 eval = 1 component at 1 pixel = 3.5 FP32 operations (1.875 instructions, "
+                                 "packed FFMA2/FMUL2/FADD2) + 0.375 MUFU.EX2 + 0.25 LDS.128 + 0.25 MOV: 2.75 issue slots)",
                          "frac": (achieved / issue_peak) if achieved else None,
-                         "peak_source": "measured live on this GPU (cg_pipe_probe): FP32 FMA lane-instructions/s / 4.125; "
-                                        "nominal %d SMs x 128/clk x %.0f MHz / 4.125 = %.3g; the XU bound "
-                                        "(MUFU.EX2 probe / 0.375 = %.3g) lies above it" %
-                                        (sm, clocks["sm_mhz"] or 0, sm * 128 * (clocks["sm_mhz"] or 0) * 1e6 / SLOTS_PER_EVAL,
-                                         xu_peak / MUFU_PER_EVAL),
+                         "bounds": bounds,
+                         "peak_source": "measured live on this GPU (cg_pipe_probe 0, 1, 7): FP32 operations/s "
+                                        "(FFMA %.4g, as FFMA2 %.4g) / 3.5, MUFU.EX2/s / 0.375, FFMA instructions/s / 2.75; "
+                                        "the lowest is the peak.  Nominal FP32: %d SMs x 128/clk x %.0f MHz / 3.5 = %.3g" %
+                                        (fma_peak, fma2_peak, sm, clocks["sm_mhz"] or 0,
+                                         sm * 128 * (clocks["sm_mhz"] or 0) * 1e6 / FP32_PER_EVAL),
                          "issued": (issued_step * args.steps / (render_ms * 1e-3)) if render_ms > 0 else None,
                          "issued_frac": (issued_step * args.steps / (render_ms * 1e-3) / issue_peak) if render_ms > 0 else None,
                          "note": "achieved = algorithmic evals (footprint pixels x components, SURVEY 8d) / kernel time; "
                                  "issued = lane-evaluations actually executed after per-warp component culling. "
                                  "Up to v11 every eval cost one MUFU.EX2 and the bound was the XU pipe "
                                  "(`xu_frac` = achieved / that peak, kept for comparison); the row recurrence "
-                                 "needs 0.375 MUFU.EX2 per eval and moved the bound to instruction issue",
+                                 "needs 0.375 MUFU.EX2 per eval; v13 packs the two rows of a lane into FP32x2 "
+                                 "instructions (same operations, 15 instead of 28 FP32 issue slots per component and lane)",
                          "xu_peak": xu_peak, "xu_frac": (achieved / xu_peak) if achieved else None,
                          "mix_ceiling": {"value": mix_peak, "frac_of_peak": mix_peak / issue_peak,
-                                         "note": "evals/s the kernel's inner loop (ft_eval2r: 2 LDS + 9 FFMA + 11 FMUL + 8 FADD "
-                                                 "+ 3 MUFU.EX2 per component and lane) reaches in isolation "
+                                         "note": "evals/s the kernel's inner loop (ft_eval2r: 2 LDS.128 + 1 FFMA + 6 FFMA2 + 1 FMUL + 4 FMUL2 "
+                                                 "+ 3 FADD2 + 3 MUFU.EX2 + 2 MOV per component and lane) reaches in isolation "
                                                  "(cg_pipe_probe(6): no global memory, every lane busy); compare with `issued`"},
-                         "fp32_fma_peak": fma_peak, "kernel_ms_total": render_ms, "kernel_launches": render_n,
+                         "fp32_fma_peak": fma_peak, "fp32_fma2_peak": fma2_peak, "kernel_ms_total": render_ms, "kernel_launches": render_n,
                          "kernel_share_of_step": render_ms / serial_ms if serial_ms else None,
                          "serial_ms_per_step": serial_ms / args.steps,
                          # dram__bytes_read.sum + dram__bytes_write.sum of one timed 8-field launch from the

@@ -281,6 +281,49 @@ __device__ __forceinline__ void recur_row4(T e, T g, T h, T (&acc)[4]) {
   acc[3] += e;
 }
 
+#ifndef FT_PACKED
+#define FT_PACKED 1          // FMUL2 / FADD2 row pairs in the row-recurrence loops (ft_eval2r, render_kernel)
+#endif
+#ifndef FT_PACKQ
+#define FT_PACKQ 1           // ... and FFMA2 for the two rows' quadratics in ft_eval2r
+#endif
+// packed FP32 pairs (sm_100 FMUL2 / FADD2): one issue slot for the same operation on two
+// floats held in an aligned register pair, each half rounded exactly like the scalar op
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpk2(f32x2 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+// recur_row4 on two rows at once: e = (row r, row r + 8), likewise g and acc; h the same on both
+__device__ __forceinline__ void recur_row4x2(f32x2 e, f32x2 g, f32x2 h, f32x2 (&acc)[4]) {
+  acc[0] = add2(acc[0], e);
+  e = mul2(e, g); g = mul2(g, h);
+  acc[1] = add2(acc[1], e);
+  e = mul2(e, g); g = mul2(g, h);
+  acc[2] = add2(acc[2], e);
+  e = mul2(e, g);
+  acc[3] = add2(acc[3], e);
+}
+
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
@@ -833,6 +876,11 @@ __global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
           // row recurrence: 2 exp2 per row of 4 pixels (the rows of a lane are not a fixed
           // distance apart here, so each row takes its own neighbour ratio)
           const real tx = (real)2 * xl0 + (real)1;
+#if FT_PACKED
+          f32x2 pacc[PIX_PER_THREAD];         // (row0, row1) pairs: FMUL2 / FADD2, see ft_eval2r
+#pragma unroll
+          for (int p = 0; p < PIX_PER_THREAD; ++p) pacc[p] = pk2(0.f, 0.f);
+#endif
 #pragma unroll 2
           for (int k = 0; k < n; ++k, tb += 8) {
             const real A = tb[0], B = tb[1], C = tb[2], b10 = tb[3], c01 = tb[4], c00 = tb[5], hh = tb[6];
@@ -841,9 +889,21 @@ __global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
             const real c1b = rfma(rfma(C, y1l, c01), y1l, c00);
             const real ea = rexp2(rfma(rfma(A, xl0, b1a), xl0, c1a)), ga = rexp2(rfma(A, tx, b1a));
             const real eb = rexp2(rfma(rfma(A, xl0, b1b), xl0, c1b)), gb = rexp2(rfma(A, tx, b1b));
+#if FT_PACKED
+            recur_row4x2(pk2((float)ea, (float)eb), pk2((float)ga, (float)gb), pk2((float)hh, (float)hh), pacc);
+#else
             recur_row4(ea, ga, hh, acc0);
             recur_row4(eb, gb, hh, acc1);
+#endif
           }
+#if FT_PACKED
+#pragma unroll
+          for (int p = 0; p < PIX_PER_THREAD; ++p) {
+            float lo, hi;
+            unpk2(pacc[p], lo, hi);
+            acc0[p] = (real)lo; acc1[p] = (real)hi;
+          }
+#endif
           n = 0;
         }
 #pragma unroll 2
@@ -978,9 +1038,6 @@ struct FieldArgs {
 #define FT_MINB 3
 #endif
 #define FT_CHUNK 8
-#ifndef FT_ROWDELTA
-#define FT_ROWDELTA 1        // second row's exponent from the first's (ft_eval2r)
-#endif
 #ifndef FT_UNROLL
 #define FT_UNROLL 2         // components per trip of the recurrence loops
 #endif
@@ -1108,7 +1165,11 @@ __device__ __forceinline__ void ft_eval1(const float* tb, int n, float yl,
 // and h = 2^(2A): TWO exp2 and five multiplies for four pixels instead of four exp2
 // and six FMAs; the second row's g0 is the first row's times k8 = 2^(8B).  3 MUFU.EX2
 // per component for the lane's 8 pixels instead of 8: the XU pipe stops being the
-// bound and the loop becomes issue-bound (33 instructions per 8 pixels, was 40).
+// bound and the loop becomes issue-bound (35 instructions per 8 pixels, was 40; 22 with
+// the rows packed into FP32x2 instructions, FT_PACKED).
+// Rejected: the second row's exponent as q(x0, y) + 8 (B x0 + C (2y + 8) + c01) -- 2 FFMA fewer,
+// 1.5 % faster, but the error of the difference is multiplied by 8: worst model-image error
+// 1.36e-6 instead of 4.5e-7 against the float64 oracle, linearity test failed at 1e-6.
 // Every product stays the true pixel value times roundings (6 roundings + 3 exp2 at
 // the fourth pixel, ~1.5e-6 relative); it is taken only when cull_components proved
 // |q(x+1)-q(x)| <= FT_RECUR_DMAX on the lanes that count (no overflow of g) and that a
@@ -1117,31 +1178,51 @@ __device__ __forceinline__ void ft_eval1(const float* tb, int n, float yl,
 __device__ __forceinline__ void ft_eval2r(const float* tb, int n, float y0l, float y1l,
                                           float x0, float (&acc0)[4], float (&acc1)[4]) {
   const float tx = 2.f * x0 + 1.f;
-  const float ysum = y0l + y1l;                          // y1l = y0l + 8 (rows r and r + 8 of the bin)
   float4 t0 = *reinterpret_cast<const float4*>(tb);      // A, B, C, b10
   float4 t1 = *reinterpret_cast<const float4*>(tb + 4);  // c01, c00, h, k8
+#if FT_PACKED
+  // Packed FP32 (FT_PACKED): the two rows of a lane run as (row r, row r + 8) register pairs.
+  // They share every ratio update -- 5 FMUL2 + 4 FADD2 instead of 10 FMUL + 8 FADD per
+  // component -- and, with FT_PACKQ, the row terms and the first exponent too (5 FFMA2
+  // instead of 10 FFMA).  Each half rounds as the scalar operation does (ptxas contracts the
+  // last multiply-add of a row into one FFMA2: one rounding fewer, never more).
+  f32x2 pacc[4];
+#pragma unroll
+  for (int p = 0; p < 4; ++p) pacc[p] = pk2(acc0[p], acc1[p]);
+  const f32x2 yy = pk2(y0l, y1l), xx = pk2(x0, x0);
+#endif
 FT_PRAGMA(unroll FT_UNROLL)
   for (int k = 0; k < n; ++k) {
     tb += 8;
     const float4 n0 = *reinterpret_cast<const float4*>(tb);
     const float4 n1 = *reinterpret_cast<const float4*>(tb + 4);
-    const float b1a = fmaf(t0.y, y0l, t0.w);
-    const float c1a = fmaf(fmaf(t0.z, y0l, t1.x), y0l, t1.y);
-    const float qa = fmaf(fmaf(t0.x, x0, b1a), x0, c1a);
-#if FT_ROWDELTA
-    // q(x0, y + 8) - q(x0, y) = 8 (B x0 + C (2y + 8) + c01): 3 FFMA instead of the 5 of a second (b1, c1, q)
-    const float qb = fmaf(8.f, fmaf(t0.y, x0, fmaf(t0.z, ysum, t1.x)), qa);
+#if FT_PACKED && FT_PACKQ
+    const f32x2 b1 = fma2(pk2(t0.y, t0.y), yy, pk2(t0.w, t0.w));
+    const f32x2 c1 = fma2(fma2(pk2(t0.z, t0.z), yy, pk2(t1.x, t1.x)), yy, pk2(t1.y, t1.y));
+    const f32x2 q = fma2(fma2(pk2(t0.x, t0.x), xx, b1), xx, c1);
+    float qa, qb, b1a, b1b;
+    unpk2(q, qa, qb);
+    unpk2(b1, b1a, b1b);
 #else
-    const float b1b = fmaf(t0.y, y1l, t0.w);
+    const float b1a = fmaf(t0.y, y0l, t0.w), b1b = fmaf(t0.y, y1l, t0.w);
+    const float qa = fmaf(fmaf(t0.x, x0, b1a), x0, fmaf(fmaf(t0.z, y0l, t1.x), y0l, t1.y));
     const float qb = fmaf(fmaf(t0.x, x0, b1b), x0, fmaf(fmaf(t0.z, y1l, t1.x), y1l, t1.y));
 #endif
     const float ea = ex2_approx(qa);
     const float eb = ex2_approx(qb);
     const float ga = ex2_approx(fmaf(t0.x, tx, b1a));
+#if FT_PACKED
+    recur_row4x2(pk2(ea, eb), pk2(ga, ga * t1.w), pk2(t1.z, t1.z), pacc);
+#else
     recur_row4(ea, ga, t1.z, acc0);
     recur_row4(eb, ga * t1.w, t1.z, acc1);
+#endif
     t0 = n0; t1 = n1;
   }
+#if FT_PACKED
+#pragma unroll
+  for (int p = 0; p < 4; ++p) unpk2(pacc[p], acc0[p], acc1[p]);
+#endif
 }
 __device__ __forceinline__ void ft_eval1r(const float* tb, int n, float yl, float x0, float (&acc)[4]) {
   const float tx = 2.f * x0 + 1.f;
@@ -2107,6 +2188,24 @@ __global__ void __launch_bounds__(256) fma_probe_kernel(float* out, int iters) {
   if (s == 123.456f) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// which = 7: packed FFMA2 (fma.rn.f32x2), 8 independent pair chains per thread.  Result: scalar
+// FMA lane-operations/s (2 per FFMA2 lane-instruction) -- tells whether the packed form adds
+// FP32 throughput or only saves issue slots.
+__global__ void __launch_bounds__(256) fma2_probe_kernel(float* out, int iters) {
+  f32x2 v[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v[j] = pk2(0.5f + 0.001f * (float)(threadIdx.x + j), 0.25f + 0.001f * (float)(threadIdx.x + j));
+  const f32x2 a = pk2(0.999f, 0.998f), b = pk2(0.0007f, 0.0005f);
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = fma2(v[j], a, b);
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { float lo, hi; unpk2(v[j], lo, hi); s += lo + hi; }
+  if (s == 123.456f) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 // Instruction-mix probes: the inner loop of field_tile_kernel / render_kernel in
 // isolation (no global memory, every lane busy), to measure what fraction of
 // the MUFU peak this MIX can reach on the device.  VAR 2: the full loop (table
@@ -3058,10 +3157,11 @@ int cg_profile_render_read(double* total_ms, int64_t* launches) {
 int cg_pipe_probe(int which, double* ops_per_s, void* stream) {
   NEED_INIT();
   cudaStream_t st = (cudaStream_t)stream;
-  // which: 0 MUFU.EX2, 1 FFMA; 2..5 instruction-mix probes and 6 the row-recurrence loop at
+  // which: 0 MUFU.EX2, 1 FFMA, 7 FFMA2 (packed; counted as 2 FMA per lane); 2..5 instruction-mix probes and 6 the row-recurrence loop at
   // 3 CTAs/SM (24 warps, the tile kernel's residency), 12..16 the same at 8 CTAs/SM (64 warps)
   const int var = which % 10;
-  const int iters = var >= 2 ? 128 : 4096, blocks = g_sm_count * ((which >= 2 && which < 10) ? 3 : 8), threads = 256;
+  const bool raw = var < 2 || which == 7;            // single-pipe probes: long chains, 8 CTAs/SM
+  const int iters = raw ? 4096 : 128, blocks = g_sm_count * ((which >= 2 && which < 10 && !raw) ? 3 : 8), threads = 256;
   float* d_out = nullptr;
   CUDA_TRY(cudaMalloc(&d_out, sizeof(float) * blocks * threads));
   cudaEvent_t e0, e1;
@@ -3072,6 +3172,7 @@ int cg_pipe_probe(int which, double* ops_per_s, void* stream) {
     CUDA_TRY(cudaEventRecord(e0, st));
     if (which == 0) xu_probe_kernel<<<blocks, threads, 0, st>>>(d_out, iters);
     else if (which == 1) fma_probe_kernel<<<blocks, threads, 0, st>>>(d_out, iters);
+    else if (which == 7) fma2_probe_kernel<<<blocks, threads, 0, st>>>(d_out, iters);
     else if (var == 2) mix_probe_kernel<2><<<blocks, threads, 0, st>>>(d_out, iters);
     else if (var == 3) mix_probe_kernel<3><<<blocks, threads, 0, st>>>(d_out, iters);
     else if (var == 4) mix_probe_kernel<4><<<blocks, threads, 0, st>>>(d_out, iters);
@@ -3087,7 +3188,7 @@ int cg_pipe_probe(int which, double* ops_per_s, void* stream) {
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   cudaFree(d_out);
-  if (ops_per_s) *ops_per_s = (double)blocks * threads * 8.0 * iters * (var >= 2 ? 32.0 : 1.0) / (best * 1e-3);
+  if (ops_per_s) *ops_per_s = (double)blocks * threads * 8.0 * iters * (which == 7 ? 2.0 : (raw ? 1.0 : 32.0)) / (best * 1e-3);
   return CG_OK;
 }
 

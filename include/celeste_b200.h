@@ -332,8 +332,9 @@ int cg_profile_render_read(double* h_total_ms, int64_t* h_launches);
  * MUFU.EX2 results/s of the kernels' inner-loop instruction MIX in isolation at 24 /
  * 64 warps per SM (2 full loop with shared-memory table, 3 table in registers,
  * 4 without row terms, 5 one FFMA per exp); 6 / 16 = component x pixel
- * evaluations/s of the row-recurrence loop (3 MUFU.EX2 + 28 FP32 per 8 pixels)
- * in isolation.  Synchronises. */
+ * evaluations/s of the row-recurrence loop (3 MUFU.EX2 + 2 FP32 + 13 packed FP32x2
+ * instructions per 8 pixels) in isolation; 7 = FP32 FMA operations/s issued as packed
+ * FFMA2 (2 per lane-instruction).  Synchronises. */
 int cg_pipe_probe(int which, double* h_ops_per_s, void* stream);
 
 #ifdef __cplusplus
