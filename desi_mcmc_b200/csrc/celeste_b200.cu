@@ -1098,14 +1098,15 @@ __global__ void __launch_bounds__(256) bin_order_kernel(FieldArgs a) {
     int base = 0;
     if ((int)lane == leader) base = atomicAdd(&a.sched[b], __popc(peers));
     base = __shfl_sync(peers, base, leader);
-    // descriptor: image (8 bits) | bin column (12) | bin row (12), list length -- the tile
-    // kernel then needs no division to place the bin
+    // descriptor: image (8 bits) | bin column (12) | bin row (12), then bin index g (26 bits) |
+    // list length clamped to 63 (6 bits; > BIN_CAP = overflow) -- the tile kernel needs no
+    // division to place the bin and can fetch the NEXT bin's list before it gets there
     const int img = g / a.max_tiles, t = g - img * a.max_tiles;
     int bx;
     bins_of(*a.imgs.p[img], &bx);
     const int by = t / bx;
     a.order[(long long)b * a.tiles_total + base + __popc(peers & ((1u << lane) - 1u))] =
-        make_int2((img << 24) | ((t - by * bx) << 12) | by, cnt);
+        make_int2((img << 24) | ((t - by * bx) << 12) | by, (g << 6) | min(cnt, 63));
   }
 }
 
@@ -1376,6 +1377,12 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
   c1 = __shfl_sync(0xffffffffu, c1, 0);
   int2 dcur = make_int2(-1, 0);
   if (c0 < total) dcur = load_unit(c0);
+  // lane's entry of a bin's source list (descriptor word y = g << 6 | length); overflowed lists are scanned instead
+  auto list_entry = [&](int gy) -> int {
+    const int n = gy & 63;
+    return (n <= BIN_CAP && lane < n) ? __ldg(a.tile_list + (long long)(gy >> 6) * BIN_CAP + lane) : 0x7fffffff;
+  };
+  int e_nx = __shfl_sync(0xffffffffu, dcur.x, 0) >= 0 ? list_entry(__shfl_sync(0xffffffffu, dcur.y, 0)) : 0x7fffffff;
 
   while (c0 < total) {
     int c2 = 0;
@@ -1384,15 +1391,22 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
     if (c1 < total) dnext = load_unit(c1);
 
    for (int cj = 0; cj < FT_CHUNK; ++cj) {
-    const int dsc = __shfl_sync(0xffffffffu, dcur.x, cj), cnt = __shfl_sync(0xffffffffu, dcur.y, cj);
+    const int dsc = __shfl_sync(0xffffffffu, dcur.x, cj), gy = __shfl_sync(0xffffffffu, dcur.y, cj);
     if (dsc < 0) break;
+    const int cnt = gy & 63, g = gy >> 6;
     const int img = dsc >> 24;
     const DevImage& im = *a.imgs.p[img];
     const int H = im.H, W = im.W;
-    const int bins_x = (W + BIN_W - 1) / BIN_W;
     FtGeom q;
     q.X0 = ((dsc >> 12) & 0xfff) * BIN_W; q.Y0 = (dsc & 0xfff) * BIN_H;
-    const int g = img * a.max_tiles + (dsc & 0xfff) * bins_x + ((dsc >> 12) & 0xfff);
+    // this bin's list entry was fetched while the previous bin was processed; fetch the next
+    // bin's now if it belongs to this unit (else before the epilogue, from the next unit)
+    const int e_cur = e_nx;
+    bool have_nx = false;
+    if (cj + 1 < FT_CHUNK && __shfl_sync(0xffffffffu, dcur.x, (cj + 1) & 31) >= 0) {
+      e_nx = list_entry(__shfl_sync(0xffffffffu, dcur.y, (cj + 1) & 31));
+      have_nx = true;
+    }
     q.x = q.X0 + (lane & 3) * 4; q.yA = q.Y0 + (lane >> 2); q.yB = q.yA + 8;
 
     // pixel counts: independent of the source list, issue the loads first
@@ -1422,6 +1436,7 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
     double s = 0.0;
 
     if (cnt == 0 && !mdl) {
+      if (!have_nx) e_nx = __shfl_sync(0xffffffffu, dnext.x, 0) >= 0 ? list_entry(__shfl_sync(0xffffffffu, dnext.y, 0)) : 0x7fffffff;
       // no source reaches this bin: lambda = epsilon on every pixel, so its terms
       // are log(eps) * sum(x) - n * eps -- one log per warp instead of one per pixel
       double sd = 0.0;
@@ -1453,7 +1468,7 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
         bool valid = false;
         if (!scan) {
           if (lane < cnt) {
-            e = a.tile_list[(long long)g * BIN_CAP + lane];
+            e = e_cur;
             valid = true;
           }
         } else {
@@ -1489,6 +1504,7 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
         }
       }
 
+      if (!have_nx) e_nx = __shfl_sync(0xffffffffu, dnext.x, 0) >= 0 ? list_entry(__shfl_sync(0xffffffffu, dnext.y, 0)) : 0x7fffffff;
       // Poisson terms.  log(lam) = T[bin] + res (log_accurate): sum x T in float64,
       // sum x res (|res| < 1/60) and the 4-pixel row sums of lam in fp32, then float64
       float sres = 0.f;
@@ -2824,6 +2840,8 @@ int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off, const CgSou
   fa.order = (int2*)(base + L.order); fa.sched = (int*)(base + L.done);
   fa.block_partials = (double*)(base + L.tiles); fa.ll = d_ll;
   fa.max_tiles = max_bins; fa.tiles_total = max_bins * n_img;
+  if ((long long)max_bins * n_img >= (1LL << 25))
+    return fail(CG_EINVAL, "%lld image bins in one call exceed the bin descriptor's 25-bit index", (long long)max_bins * n_img);
   fa.logtab = g_d_logtab; fa.cnt = cnt; fa.cull = g_cull | (g_recur ? 0 : 2);
   if (h_d_model) {
     bool any = false;
