@@ -476,9 +476,9 @@ def main():
                          "kernel_share_of_step": render_ms / serial_ms if serial_ms else None,
                          "serial_ms_per_step": serial_ms / args.steps,
                          # dram__bytes_read.sum + dram__bytes_write.sum of one timed 8-field launch from the
-                         # ncu --set full capture summarised in profiles/r01_prof_tile_v13_*: 664.7 + 4.2 MB
+                         # ncu --set full capture summarised in profiles/r01_prof_tile_v14_*: 663.0 + 4.0 MB
                          # (algorithmic: 4 B of nelec per pixel = 488 MB); scaled to this launch's fields
-                         "traffic": 668.88e6 * FPC / 8.0,
+                         "traffic": 666.97e6 * FPC / 8.0,
                          "traffic_algorithmic": FPC * 5 * H * W * 4,
                          "hbm_peak_gbs": peaks.get("hbm_gbs")},
             "clocks": clocks,
