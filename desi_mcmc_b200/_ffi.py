@@ -19,7 +19,7 @@ LIB_PATH = os.path.join(PKG, "libceleste_b200.so")
 CG_ABI_VERSION = 1
 CG_MAX_PSF = 4
 CG_NUM_BANDS = 5
-CG_MAX_COMP = 48
+CG_MAX_COMP = 56
 CG_MAX_IMAGES = 64
 
 CG_OK, CG_EINVAL, CG_ECUDA, CG_ENOMEM, CG_ESTATE = 0, -1, -2, -3, -4

@@ -33,6 +33,8 @@
 #include <string>
 #include <vector>
 #include <algorithm>
+#include <map>
+#include <mutex>
 
 #include "celeste_b200.h"
 
@@ -177,6 +179,8 @@ struct Counters {
 #define FT_RECUR_DMAX 96.f   // largest |log2 ratio of neighbouring pixels| the row recurrence is used for
 #define FT_RECUR_FLOOR -64.f // log2 of the unit-flux rate below which a value lost to underflow does not count
 #define TAB_STRIDE (CG_MAX_COMP * TAB_W)
+static_assert(14 * CG_MAX_PSF <= CG_MAX_COMP, "a galaxy has (6 exp + 8 dev) x n_psf components");
+static_assert(CG_MAX_COMP < 64, "bin-list entries pack item * 64 + K; cull_components owns components lane and lane + 32");
 
 #define STRIP_THREADS 256
 #define PIX_PER_THREAD 4
@@ -222,7 +226,7 @@ struct PrepArgs {
   long long n_items;
   int default_flags;
   int implicit_mode;        // 0 cross product; 1 per-image fixed boxes + aux=img; 2 indirect list; 3 field batch
-  const CgBox* img_boxes;   // device, n_img (implicit_mode >= 1)
+  CgBox img_boxes[CG_MAX_IMAGES];   // by value (implicit_mode 1, 2): no host->device copy, graph-capturable
   const int* ind_list;      // device (implicit_mode 2)
   const int* ind_count;     // device (implicit_mode 2): points at Counters.guard_count of pass 1
   int aux_per_img;          // implicit_mode >= 1: aux patch index = image index (else -1)
@@ -452,7 +456,7 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
     }
     it.flags = a.default_flags | CG_ITEM_FIXED_BOX;
     it.aux = a.aux_per_img ? it.img : -1;
-    CgBox b = a.img_boxes[it.img];
+    const CgBox b = a.img_boxes[it.img];
     it.box[0] = b.x0; it.box[1] = b.x1; it.box[2] = b.y0; it.box[3] = b.y1;
   }
 
@@ -592,7 +596,9 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
   if (x1 <= x0 || y1 <= y0 || (K == 0 && !(it.flags & CG_ITEM_FIXED_BOX))) { x1 = x0; y1 = y0; }
   long long npx = (long long)(x1 - x0) * (y1 - y0);
   int err = 0;
-  if (npx > a.max_patch_px) { err = 1; x1 = x0; y1 = y0; npx = 0; }
+  // only the entry points that write box-shaped buffers (patches, auxiliary patches) are bounded by
+  // max_patch_px; the fused field path (no work list) clips the footprint to the image and is done
+  if (a.worklist != nullptr && npx > a.max_patch_px) { err = 1; x1 = x0; y1 = y0; npx = 0; }
 
   // flux (celeste.py:38-45,80-81,91-92; planck.py:155-158)
   double flux;
@@ -688,6 +694,7 @@ struct RenderArgs {
   long long max_patch_px;
   const float* aux;           // background / photon patches
   const long long* aux_offsets;
+  long long aux_off_v[CG_MAX_IMAGES];   // used instead of aux_offsets when that is NULL (cg_score_proposals: by value)
   double* partials;           // one per strip
   int cull;                   // 0 disables component culling
   int unit_wt;                // warp tiles per work unit
@@ -944,7 +951,7 @@ __global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
             if (rr == 1 && !two) break;
             const int row = rr ? row1 : row0;
             const long long poff = (long long)row * wbox + cx;
-            const float* auxp = (h.aux >= 0) ? a.aux + a.aux_offsets[h.aux] + poff : nullptr;
+            const float* auxp = (h.aux >= 0) ? a.aux + (a.aux_offsets ? a.aux_offsets[h.aux] : a.aux_off_v[h.aux]) + poff : nullptr;
             const long long ioff = (long long)(h.y0 + row) * im.W + (h.x0 + cx);
 #pragma unroll
             for (int p = 0; p < PIX_PER_THREAD; ++p) {
@@ -1576,7 +1583,9 @@ __global__ void __launch_bounds__(1024) field_tile_final_kernel(FieldArgs a) {
     if (threadIdx.x < o) s_fin[threadIdx.x] += s_fin[threadIdx.x + o];
     __syncthreads();
   }
-  if (threadIdx.x == 0) a.ll[img] = s_fin[0];
+  // an error raised on the device (Counters.err_flag) poisons the result: callers that never
+  // synchronise to read the flag (FieldSet.loglik_device, CUDA-graph replays) still cannot miss it
+  if (threadIdx.x == 0) a.ll[img] = a.cnt->err_flag ? (double)NAN : s_fin[0];
 }
 
 // ---------------------------------------------------------------------------
@@ -2342,11 +2351,10 @@ struct WsLayout {
   long long n_items2;
 };
 
-#define GUARD_CAP 1024
 #define MAX_TILES_PER_IMG_DEFAULT 0
 
 static WsLayout ws_layout(long long n_items, long long max_patch_px, int with_patches,
-                          int n_img_for_guard, long long n_tiles_total) {
+                          int n_img_for_guard, long long n_tiles_total, int guard_cap = 0) {
   WsLayout L;
   memset(&L, 0, sizeof L);
   size_t o = 0;
@@ -2374,8 +2382,9 @@ static WsLayout ws_layout(long long n_items, long long max_patch_px, int with_pa
     L.model_ptrs = take(sizeof(float*) * CG_MAX_IMAGES);
   }
   if (n_img_for_guard > 0) {
-    L.guard_cap = GUARD_CAP;
-    L.n_items2 = (long long)(GUARD_CAP + 1) * n_img_for_guard;
+    // every proposal of the call may fall into the guard band: the float64 re-score list holds them all
+    L.guard_cap = std::max(guard_cap, 1);
+    L.n_items2 = (long long)(L.guard_cap + 1) * n_img_for_guard;
     long long cap2 = L.n_items2 * strips_per_item;
     if (cap2 > 0x7fffffffLL) cap2 = 0x7fffffffLL;
     L.worklist_cap2 = (int)cap2;
@@ -2385,13 +2394,33 @@ static WsLayout ws_layout(long long n_items, long long max_patch_px, int with_pa
     L.worklist2 = take(sizeof(int2) * (size_t)L.worklist_cap2);
     L.partials2 = take(sizeof(double) * (size_t)L.worklist_cap2);
     L.item_ll2 = take(sizeof(double) * L.n_items2);
-    L.guard_list = take(sizeof(int) * GUARD_CAP);
+    L.guard_list = take(sizeof(int) * (size_t)L.guard_cap);
   }
   L.total = o;
   return L;
 }
 
 static Counters* g_last_counters = nullptr;
+
+// Scratch of the small entry points (A2's component table, the Poisson block partials): one
+// block PER STREAM, so that calls enqueued on different streams never share a buffer
+// ("thread-compatible, one stream per thread").  Grown blocks are retired, not
+// freed: work already enqueued may still read them.
+struct StreamScratch { double* p = nullptr; size_t n = 0; };
+static std::mutex g_scratch_mu;
+static std::map<std::pair<int, cudaStream_t>, StreamScratch> g_scratch_map;
+static int stream_scratch(int kind, cudaStream_t st, size_t n_doubles, double** out) {
+  std::lock_guard<std::mutex> lk(g_scratch_mu);
+  StreamScratch& sc = g_scratch_map[std::make_pair(kind, st)];
+  if (sc.n < n_doubles) {
+    double* p = nullptr;
+    const size_t n = std::max<size_t>(n_doubles, 1024);
+    CUDA_TRY(cudaMalloc(&p, sizeof(double) * n));
+    sc.p = p; sc.n = n;          // the previous (smaller) block stays allocated for in-flight work
+  }
+  *out = sc.p;
+  return CG_OK;
+}
 
 extern "C" {
 
@@ -2612,8 +2641,6 @@ int cg_galaxy_psf_mixture_params(const double* thetas, const double* W, const do
 }
 
 // ---- A2 ------------------------------------------------------------------------
-static double* g_gmm_tab = nullptr;  // K_max*6 doubles, lazily allocated
-static int g_gmm_tab_cap = 0;
 
 int cg_gmm_like_2d(double* d_probs, const double* d_x, const double* d_ws, const double* d_mus,
                    const double* d_sigs, int64_t N, int32_t K, void* stream) {
@@ -2623,11 +2650,8 @@ int cg_gmm_like_2d(double* d_probs, const double* d_x, const double* d_ws, const
   cudaStream_t st = (cudaStream_t)stream;
   if (N == 0) return CG_OK;
   if (K == 0) { CUDA_TRY(cudaMemsetAsync(d_probs, 0, sizeof(double) * N, st)); return CG_OK; }
-  if (K > g_gmm_tab_cap) {
-    if (g_gmm_tab) cudaFree(g_gmm_tab);
-    g_gmm_tab_cap = std::max(K, 64);
-    CUDA_TRY(cudaMalloc(&g_gmm_tab, sizeof(double) * 6 * g_gmm_tab_cap));
-  }
+  double* g_gmm_tab = nullptr;
+  { int rc = stream_scratch(0, st, (size_t)6 * K, &g_gmm_tab); if (rc) return rc; }
   gmm_prep_kernel<<<(K + 63) / 64, 64, 0, st>>>(d_ws, d_mus, d_sigs, K, g_gmm_tab);
   LAUNCH_CHECK();
   int blocks = (int)std::min<long long>((N + 255) / 256, (long long)g_sm_count * 8);
@@ -2660,7 +2684,7 @@ size_t cg_workspace_bytes(int32_t kind, int64_t n_items, int32_t n_img, int64_t 
     case CG_WS_RENDER: L = ws_layout(n_items, max_patch_px, 0, 0, 0); break;
     case CG_WS_FIELD: L = ws_layout(std::max<long long>(n_items, 1), max_patch_px, 1, 0, n_tiles); break;
     case CG_WS_ITEMS: L = ws_layout(n_items * 2, max_patch_px, 0, 0, 0); break;
-    case CG_WS_SCORE: L = ws_layout(n_items, max_patch_px, 0, n_img, 0); break;
+    case CG_WS_SCORE: L = ws_layout(n_items, max_patch_px, 0, n_img, 0, n_img > 0 ? (int)(n_items / n_img) - 1 : 0); break;
     default: return 0;
   }
   return L.total + 256;
@@ -2955,20 +2979,17 @@ int cg_score_proposals(CgImage* const* imgs, int32_t n_img, const CgSource* d_sr
     if (!imgs[i]->h.nelec) return fail(CG_EINVAL, "image %d has no nelec buffer", i);
   }
   const long long n_items = (long long)(P + 1) * n_img;
-  WsLayout L = ws_layout(n_items, max_px, 0, guard > 0 ? n_img : 0, 0);
+  WsLayout L = ws_layout(n_items, max_px, 0, guard > 0 ? n_img : 0, 0, P);
   if (L.total > ws_bytes) return fail(CG_ENOMEM, "workspace too small: need %zu bytes, have %zu", L.total, ws_bytes);
   char* base = (char*)d_ws;
   Counters* cnt = (Counters*)(base + L.counters);
   CUDA_TRY(cudaMemsetAsync(cnt, 0, sizeof(Counters), st));
-  CgBox* d_boxes = (CgBox*)(base + L.img_boxes);
-  long long* d_off = (long long*)(base + L.aux_offsets);
-  CUDA_TRY(cudaMemcpyAsync(d_boxes, h_boxes, sizeof(CgBox) * n_img, cudaMemcpyHostToDevice, st));
-  if (d_bg) {
-    if (!h_bg_offsets) return fail(CG_EINVAL, "background offsets are required with d_bg");
-    CUDA_TRY(cudaMemcpyAsync(d_off, h_bg_offsets, sizeof(long long) * n_img, cudaMemcpyHostToDevice, st));
-  }
+  if (d_bg && !h_bg_offsets) return fail(CG_EINVAL, "background offsets are required with d_bg");
+  // the boxes and offsets (n_img <= 64 small records) travel inside the kernel arguments: no
+  // host->device copy from pageable memory, and the call can be captured into a CUDA graph
+  for (int i = 0; i < n_img; ++i) pa.img_boxes[i] = h_boxes[i];
   pa.n_img = n_img; pa.srcs = d_srcs; pa.n_src = P + 1; pa.items = nullptr; pa.n_items = n_items;
-  pa.default_flags = CG_ITEM_FLUX_BAND; pa.implicit_mode = 1; pa.img_boxes = d_boxes;
+  pa.default_flags = CG_ITEM_FLUX_BAND; pa.implicit_mode = 1;
   pa.aux_per_img = d_bg ? 1 : 0;
   pa.bound_cap = 0; pa.max_patch_px = max_px; pa.hdr = (ItemHdr*)(base + L.hdr);
   pa.tab = base + L.tab; pa.worklist = (int2*)(base + L.worklist); pa.worklist_cap = L.worklist_cap;
@@ -2978,7 +2999,8 @@ int cg_score_proposals(CgImage* const* imgs, int32_t n_img, const CgSource* d_sr
   RenderArgs ra;
   memset(&ra, 0, sizeof ra);
   ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.worklist_cap = pa.worklist_cap; ra.cull = g_cull | (g_recur ? 0 : 2); ra.logtab = g_d_logtab; ra.cnt = cnt;
-  ra.aux = d_bg; ra.aux_offsets = d_off; ra.partials = (double*)(base + L.partials);
+  ra.aux = d_bg; ra.aux_offsets = nullptr; ra.partials = (double*)(base + L.partials);
+  if (d_bg) for (int i = 0; i < n_img; ++i) ra.aux_off_v[i] = h_bg_offsets[i];
   rc = run_render<float, MODE_POISSON>(ra, n_items, st);
   if (rc) return rc;
   double* item_ll = (double*)(base + L.item_ll);
@@ -3021,13 +3043,13 @@ int cg_score_proposals(CgImage* const* imgs, int32_t n_img, const CgSource* d_sr
 }
 
 // ---- sources.py:6-12 ---------------------------------------------------------------
-static double* g_scratch = nullptr;   // 1024 doubles of block partials
 int cg_poisson_loglike(const double* d_data, const double* d_model, const double* d_mask, int64_t n,
                        double* d_out, void* stream) {
   NEED_INIT();
   if (n < 0) return fail(CG_EINVAL, "negative size");
   cudaStream_t st = (cudaStream_t)stream;
-  if (!g_scratch) CUDA_TRY(cudaMalloc(&g_scratch, sizeof(double) * 1024));
+  double* g_scratch = nullptr;        // 1024 doubles of block partials, owned by this stream
+  { int rc = stream_scratch(1, st, 1024, &g_scratch); if (rc) return rc; }
   int blocks = (int)std::min<long long>(1024, std::max<long long>(1, (n + 255) / 256));
   poisson_partial_kernel<<<blocks, 256, 0, st>>>(d_data, d_model, d_mask, n, g_scratch);
   LAUNCH_CHECK();

@@ -36,7 +36,7 @@ extern "C" {
 
 #define CG_MAX_PSF 4      /* PSF mixture components per image (reference: 3, fits_image.py:130-133) */
 #define CG_NUM_BANDS 5    /* u g r i z */
-#define CG_MAX_COMP 48    /* components per (source, image): (6 exp + 8 dev) x 3 PSF = 42 */
+#define CG_MAX_COMP 56    /* components per (source, image): (6 exp + 8 dev) x n_psf; 42 with the reference's 3-component PSF */
 #define CG_MAX_IMAGES 64  /* images per call */
 
 enum {
