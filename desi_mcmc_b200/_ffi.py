@@ -16,7 +16,7 @@ import numpy as np
 PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(PKG, "libceleste_b200.so")
 
-CG_ABI_VERSION = 1
+CG_ABI_VERSION = 2
 CG_MAX_PSF = 4
 CG_NUM_BANDS = 5
 CG_MAX_COMP = 56
@@ -25,6 +25,7 @@ CG_MAX_IMAGES = 64
 CG_OK, CG_EINVAL, CG_ECUDA, CG_ENOMEM, CG_ESTATE = 0, -1, -2, -3, -4
 
 CG_SRC_PLANCK = 1
+CG_SRC_EIGEN = 2
 
 CG_ITEM_FLUX_BAND = 0x00
 CG_ITEM_FLUX_UNIT = 0x01
@@ -36,6 +37,7 @@ CG_ITEM_HEADER_CD = 0x40
 CG_ITEM_NO_MASK = 0x80
 
 CG_WS_RENDER, CG_WS_FIELD, CG_WS_ITEMS, CG_WS_SCORE = 0, 1, 2, 3
+CG_WS_SWEEP_ALLOC, CG_WS_SWEEP_SCORE, CG_WS_SWEEP_BACKGROUND = 4, 5, 6
 
 CG_LL_POISSON_BG = 0
 CG_LL_CONDITIONAL = 1
@@ -66,11 +68,11 @@ CG_MAX_FIELDS = 16
 # numpy mirrors of the POD arrays that cross the boundary in bulk
 SRC_DTYPE = np.dtype([("type", "<i4"), ("flags", "<i4"), ("u", "<f8", (2,)),
                       ("flux", "<f8", (CG_NUM_BANDS,)), ("theta", "<f8"), ("sigma", "<f8"),
-                      ("phi", "<f8"), ("rho", "<f8"), ("t", "<f8"), ("b", "<f8")])
+                      ("phi", "<f8"), ("rho", "<f8"), ("t", "<f8"), ("b", "<f8"), ("flux_row", "<i8")])
 ITEM_DTYPE = np.dtype([("src", "<i4"), ("img", "<i4"), ("flags", "<i4"),
                        ("box", "<i4", (4,)), ("aux", "<i4")])
 BOX_DTYPE = np.dtype([("x0", "<i4"), ("x1", "<i4"), ("y0", "<i4"), ("y1", "<i4")])
-assert SRC_DTYPE.itemsize == 112 and ITEM_DTYPE.itemsize == 32 and BOX_DTYPE.itemsize == 16
+assert SRC_DTYPE.itemsize == 120 and ITEM_DTYPE.itemsize == 32 and BOX_DTYPE.itemsize == 16
 
 _vp, _i32, _i64, _dbl, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_double, C.c_size_t
 _dp = C.POINTER(C.c_double)
@@ -87,6 +89,7 @@ PROTOTYPES = {
     "cg_image_set_epsilon": (C.c_int, [_vp, _dbl]),
     "cg_image_radius": (_dbl, [_vp]),
     "cg_set_filter_curves": (C.c_int, [_vp, _vp, _vp, _vp]),
+    "cg_set_flux_table": (C.c_int, [_vp, _i64]),
     "cg_gmm_like_2d": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i32, _vp]),
     "cg_mvn2d_logpdf": (C.c_int, [_vp, _vp, _vp, _vp, _dbl, _i64, _vp]),
     "cg_galaxy_prof_psf_mixture_params": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32,
@@ -109,6 +112,18 @@ PROTOTYPES = {
     "cg_alloc_workspace_bytes": (_sz, [_i32, _i64]),
     "cg_sample_source_counts": (C.c_int, [_vp, _i32, _i32, _vp, _vp, _i64, C.c_uint64, _vp, _vp, _vp, _sz, _vp]),
     "cg_binomial_draws": (C.c_int, [_i64, _dbl, C.c_uint64, _i64, _vp, _vp]),
+    "cg_sweep_workspace_bytes": (_sz, [_i32, _i32, _i32, _i32, _i64, _i64]),
+    "cg_field_sample_photons": (C.c_int, [_vp, _i32, _vp, _i32, _dbl, _i64, C.c_uint64, _vp, _vp, _vp, _vp, _vp,
+                                          _vp, _sz, _vp]),
+    "cg_resample_fluxes": (C.c_int, [_vp, _i32, _vp, _i32, _vp, _vp, _dbl, _dbl, C.c_uint64, _vp]),
+    "cg_resample_epsilon": (C.c_int, [_vp, _i32, _vp, _dbl, _dbl, C.c_uint64, _vp, _vp]),
+    "cg_image_sync_epsilon": (C.c_int, [_vp, _vp, _dp]),
+    "cg_make_proposals": (C.c_int, [_vp, _i32, _i32, _vp, C.c_uint64, _vp, _vp]),
+    "cg_sweep_guard_cap": (_i32, [_i32, _i32]),
+    "cg_score_proposals_multi": (C.c_int, [_vp, _i32, _vp, _i32, _i32, _vp, _i32, _vp, _i64, _vp, _vp, _dbl,
+                                           _vp, _vp, _vp, _vp, _sz, _vp]),
+    "cg_select_proposals": (C.c_int, [_vp, _i32, _i32, _vp, _vp, _vp, _vp]),
+    "cg_background_patches": (C.c_int, [_vp, _i32, _vp, _i32, _vp, _vp, _vp, _i64, _i32, _vp, _vp, _sz, _vp]),
     "cg_planck_fluxes": (C.c_int, [_vp, _vp, _i64, _vp, _vp]),
     "cg_eigen_fluxes": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp]),
     "cg_mog_logpdf": (C.c_int, [_vp, _i64, _i32, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp]),

@@ -37,7 +37,9 @@ def needs_build() -> bool:
     if not os.path.exists(LIB):
         return True
     t = os.path.getmtime(LIB)
-    return any(os.path.getmtime(p) > t for p in (SRC, HDR))
+    csrc = os.path.dirname(SRC)
+    deps = [HDR] + [os.path.join(csrc, f) for f in os.listdir(csrc)]
+    return any(os.path.getmtime(p) > t for p in deps)
 
 
 def build(force: bool = False, verbose: bool = False, ptxas_info: bool = False) -> str:

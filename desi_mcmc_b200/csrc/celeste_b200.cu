@@ -114,6 +114,8 @@ static FilterTables* g_d_filters = nullptr;  // device
 struct LogTable;
 static LogTable* g_d_logtab = nullptr;       // device, filled at cg_init
 static int g_filters_loaded = 0;
+static const double* g_flux_table = nullptr;  // device [g_flux_rows][5] nanomaggies (cg_set_flux_table)
+static long long g_flux_rows = 0;
 
 // ---------------------------------------------------------------------------
 // device-side structures
@@ -157,7 +159,7 @@ struct Counters {
   int total_strips;    // partial-sum slots handed out
   int work_counter;
   int guard_count;
-  int err_flag;        // 1: footprint larger than max_patch_px, 2: guard list overflow, 3: work list overflow
+  int err_flag;        // 1: footprint larger than max_patch_px, 2: guard list overflow, 3: work list overflow, 4: CG_SRC_EIGEN row outside the flux table
   unsigned long long evals;    // algorithmic: footprint pixels x components
   unsigned long long issued;   // lane-evaluations actually issued after culling (warp granular)
   int heavy_strips;    // work units of galaxies, listed from the front of the work list
@@ -238,7 +240,10 @@ struct PrepArgs {
   int worklist_cap;
   Counters* cnt;
   CgBox* out_boxes;         // optional
+  int cap_boxes;            // footprints above max_patch_px are an error (set when box-shaped buffers are written)
   const FilterTables* filters;
+  const double* flux_table;  // CG_SRC_EIGEN: [flux_rows][5] nanomaggies resident in HBM
+  long long flux_rows;
   // full-field path: per (image, 64x16 tile) list of the items that overlap it
   int unit_wt;              // warp tiles per work unit (same value in RenderArgs)
   int* tile_count;          // [n_img][max_tiles] (NULL: no binning)
@@ -598,12 +603,21 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
   int err = 0;
   // only the entry points that write box-shaped buffers (patches, auxiliary patches) are bounded by
   // max_patch_px; the fused field path (no work list) clips the footprint to the image and is done
-  if (a.worklist != nullptr && npx > a.max_patch_px) { err = 1; x1 = x0; y1 = y0; npx = 0; }
+  if ((a.worklist != nullptr || a.cap_boxes) && npx > a.max_patch_px) { err = 1; x1 = x0; y1 = y0; npx = 0; }
 
   // flux (celeste.py:38-45,80-81,91-92; planck.py:155-158)
   double flux;
   if (it.flags & CG_ITEM_FLUX_UNIT) {
     flux = 1.0;
+  } else if (s.flags & CG_SRC_EIGEN) {
+    // eigen-spectrum route: the band flux was projected on the device (eigen_flux_kernel) and is read
+    // from HBM here -- redshift_utils.py:304-323 feeding celeste.py:80-81,91-92
+    if (a.flux_table && s.flux_row >= 0 && s.flux_row < a.flux_rows) {
+      flux = (a.flux_table[s.flux_row * CG_NUM_BANDS + im.band] / im.calib) * im.kappa;
+    } else {
+      flux = (double)NAN;
+      err = 4;
+    }
   } else if (star && (s.flags & CG_SRC_PLANCK) && s.t != 0.0) {
     double ppj = planck_photons_per_joule_warp(a.filters, s.t, im.band, lane);
     ppj = __shfl_sync(0xffffffffu, ppj, 0);
@@ -631,7 +645,7 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
       wpos = atomicAdd(heavy ? &a.cnt->heavy_strips : &a.cnt->light_strips, n_units);
     }
     if (npx) atomicAdd(&a.cnt->evals, (unsigned long long)npx * (unsigned long long)K);
-    if (err) atomicExch(&a.cnt->err_flag, 1);
+    if (err) atomicExch(&a.cnt->err_flag, err);
     if (listed && start + n_strips > a.worklist_cap) { atomicExch(&a.cnt->err_flag, 3); }
   }
   start = __shfl_sync(0xffffffffu, start, 0);
@@ -695,6 +709,7 @@ struct RenderArgs {
   const float* aux;           // background / photon patches
   const long long* aux_offsets;
   long long aux_off_v[CG_MAX_IMAGES];   // used instead of aux_offsets when that is NULL (cg_score_proposals: by value)
+  long long aux_stride;       // > 0 (with aux_offsets NULL): auxiliary patch k lies at aux + k * aux_stride
   double* partials;           // one per strip
   int cull;                   // 0 disables component culling
   int unit_wt;                // warp tiles per work unit
@@ -951,7 +966,7 @@ __global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
             if (rr == 1 && !two) break;
             const int row = rr ? row1 : row0;
             const long long poff = (long long)row * wbox + cx;
-            const float* auxp = (h.aux >= 0) ? a.aux + (a.aux_offsets ? a.aux_offsets[h.aux] : a.aux_off_v[h.aux]) + poff : nullptr;
+            const float* auxp = (h.aux >= 0) ? a.aux + (a.aux_offsets ? a.aux_offsets[h.aux] : (a.aux_stride ? (long long)h.aux * a.aux_stride : a.aux_off_v[h.aux])) + poff : nullptr;
             const long long ioff = (long long)(h.y0 + row) * im.W + (h.x0 + cx);
 #pragma unroll
             for (int p = 0; p < PIX_PER_THREAD; ++p) {
@@ -1250,13 +1265,16 @@ FT_PRAGMA(unroll FT_UNROLL)
 
 struct FtGeom { int X0, Y0, x, yA, yB; };
 
-// one source on the warp's bin: cull, evaluate, add the rates inside the footprint
-__device__ __forceinline__ void ft_source(const FieldArgs& a, int item, int K, int4 bx, int2 o, float fl,
-                                          const FtGeom& q, int lane, float* wtab,
-                                          float (&lam)[2][4], unsigned long long& issued) {
+// one source on the warp's bin: cull the components against the part of the rectangle bx that lies
+// in the bin and evaluate the survivors at the lane's pixels -> UNIT-flux values acc0 (row yA) and
+// acc1 (row yB), unmasked (lanes outside bx hold values the caller must not use).  Returns false
+// (warp-uniform) when bx misses the bin.
+__device__ __forceinline__ bool ft_source_rates(const FieldArgs& a, int item, int K, int4 bx, int2 o,
+                                                const FtGeom& q, int lane, float* wtab,
+                                                float (&acc0)[4], float (&acc1)[4], unsigned long long& issued) {
   const int ix0 = max(q.X0, bx.x), ix1 = min(q.X0 + BIN_W, bx.y);
   const int iy0 = max(q.Y0, bx.z), iy1 = min(q.Y0 + BIN_H, bx.w);
-  if (ix0 >= ix1 || iy0 >= iy1 || K <= 0) return;                // warp-uniform
+  if (ix0 >= ix1 || iy0 >= iy1 || K <= 0) return false;          // warp-uniform
   const float* gtab = a.tab + (long long)item * TAB_STRIDE;
   int n = K;
   bool recur = false;
@@ -1296,7 +1314,8 @@ __device__ __forceinline__ void ft_source(const FieldArgs& a, int item, int K, i
 #pragma unroll
   for (int p = 0; p < 4; ++p) xl[p] = (float)(q.x + p - o.x);
   const bool doA = iy0 < q.Y0 + 8, doB = iy1 > q.Y0 + 8;         // which row halves the footprint reaches
-  float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int p = 0; p < 4; ++p) { acc0[p] = 0.f; acc1[p] = 0.f; }
   if (doA && doB) {
     if (recur) ft_eval2r(tb, n, (float)(q.yA - o.y), (float)(q.yB - o.y), xl[0], acc0, acc1);
     else ft_eval2(tb, n, (float)(q.yA - o.y), (float)(q.yB - o.y), xl, acc0, acc1);
@@ -1310,7 +1329,17 @@ __device__ __forceinline__ void ft_source(const FieldArgs& a, int item, int K, i
     else ft_eval1(tb, n, (float)(q.yB - o.y), xl, acc1);
     if (lane == 0) issued += (unsigned long long)n * 128;
   }
-  if (ix1 - ix0 == BIN_W && iy1 - iy0 == BIN_H) {                 // the footprint covers the bin: no masks
+  return true;
+}
+
+// ... and add the rates inside the footprint to lambda (the field kernel's use)
+__device__ __forceinline__ void ft_source(const FieldArgs& a, int item, int K, int4 bx, int2 o, float fl,
+                                          const FtGeom& q, int lane, float* wtab,
+                                          float (&lam)[2][4], unsigned long long& issued) {
+  float acc0[4], acc1[4];
+  if (!ft_source_rates(a, item, K, bx, o, q, lane, wtab, acc0, acc1, issued)) return;
+  if (min(q.X0 + BIN_W, bx.y) - max(q.X0, bx.x) == BIN_W &&
+      min(q.Y0 + BIN_H, bx.w) - max(q.Y0, bx.z) == BIN_H) {       // the footprint covers the bin: no masks
 #pragma unroll
     for (int p = 0; p < 4; ++p) {
       lam[0][p] += acc0[p] * fl;
@@ -2499,7 +2528,9 @@ int64_t cg_last_eval_count(void* stream) {
   if (cudaMemcpy(&c, g_last_counters, sizeof c, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
   if (c.err_flag) {
     fail(CG_ENOMEM, c.err_flag == 1 ? "a footprint exceeded max_patch_px"
-                                    : (c.err_flag == 2 ? "guard list overflow" : "work list overflow"));
+                                    : (c.err_flag == 2 ? "guard list overflow"
+                                    : (c.err_flag == 3 ? "work list overflow"
+                                                       : "a CG_SRC_EIGEN source points outside the bound flux table")));
     return -(int64_t)c.err_flag;
   }
   return (int64_t)c.evals;
@@ -2577,6 +2608,14 @@ int cg_image_set_epsilon(CgImage* img, double epsilon) {
 }
 
 double cg_image_radius(const CgImage* img) { return img ? img->h.R : NAN; }
+
+int cg_set_flux_table(const double* d_flux, int64_t n_rows) {
+  NEED_INIT();
+  if (d_flux && n_rows <= 0) return fail(CG_EINVAL, "flux table needs at least one row");
+  g_flux_table = d_flux;
+  g_flux_rows = d_flux ? n_rows : 0;
+  return CG_OK;
+}
 
 int cg_set_filter_curves(const double* wl, const double* hv, const double* sens, const int32_t* counts) {
   NEED_INIT();
@@ -2788,7 +2827,7 @@ int cg_render_patches(CgImage* const* imgs, int32_t n_img, const CgSource* d_src
   pa.default_flags = default_flags; pa.implicit_mode = 0; pa.bound_cap = bound_cap;
   pa.max_patch_px = max_patch_px; pa.hdr = (ItemHdr*)(base + L.hdr); pa.tab = base + L.tab;
   pa.worklist = (int2*)(base + L.worklist); pa.worklist_cap = L.worklist_cap; pa.cnt = cnt;
-  pa.out_boxes = d_boxes; pa.filters = g_d_filters;
+  pa.out_boxes = d_boxes; pa.filters = g_d_filters; pa.flux_table = g_flux_table; pa.flux_rows = g_flux_rows;
   rc = run_prepare<float>(pa, st);
   if (rc) return rc;
   RenderArgs ra;
@@ -2800,20 +2839,20 @@ int cg_render_patches(CgImage* const* imgs, int32_t n_img, const CgSource* d_src
   return rc;
 }
 
-int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off, const CgSource* d_srcs,
-                     const int32_t* h_src_off, int32_t n_fields, double bound_cap,
-                     int64_t max_patch_px, double* d_ll, float* const* h_d_model, void* d_ws,
-                     size_t ws_bytes, void* stream) {
-  NEED_INIT();
-  cudaStream_t st = (cudaStream_t)stream;
+}  // extern "C"
+
+// Set-up shared by the entry points that walk the 16 x 16 image bins (full-field likelihood, photon
+// allocation): prepare_kernel with binning, then bin_order_kernel.  Fills pa / fa / L.
+static int field_setup(CgImage* const* imgs, const int32_t* h_img_off, const CgSource* d_srcs,
+                       const int32_t* h_src_off, int32_t n_fields, double bound_cap, int64_t max_patch_px,
+                       void* d_ws, size_t ws_bytes, size_t extra_bytes, cudaStream_t st, int default_flags,
+                       CgBox* d_out_boxes, PrepArgs& pa, FieldArgs& fa, WsLayout& L) {
   if (n_fields < 1 || n_fields > CG_MAX_FIELDS) return fail(CG_EINVAL, "n_fields must be in [1,%d]", CG_MAX_FIELDS);
   if (!h_img_off || !h_src_off) return fail(CG_EINVAL, "null offsets");
   const int n_img = h_img_off[n_fields];
-  PrepArgs pa;
   memset(&pa, 0, sizeof pa);
   int rc = fill_imgs(imgs, n_img, &pa.imgs);
   if (rc) return rc;
-  FieldArgs fa;
   memset(&fa, 0, sizeof fa);
   long long n_items = 0;
   pa.fb.n_fields = n_fields;
@@ -2834,7 +2873,7 @@ int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off, const CgSou
   pa.fb.item_off[n_fields] = (int)n_items;
   pa.fb.src_off[n_fields] = h_src_off[n_fields];
   pa.fb.img_off[n_fields] = n_img;
-  if (n_items > 0x7fffffffLL) return fail(CG_EINVAL, "too many (source, image) items");
+  if (n_items > 0x7fffffffLL / 64) return fail(CG_EINVAL, "too many (source, image) items");
   int max_tiles = 0;
   for (int i = 0; i < n_img; ++i) {
     max_tiles = std::max(max_tiles, (int)cg_field_tiles(imgs[i]->h.H, imgs[i]->h.W));
@@ -2842,17 +2881,19 @@ int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off, const CgSou
     if (imgs[i]->h.H > 4096 * BIN_H || imgs[i]->h.W > 4096 * BIN_W)       // 12-bit bin coordinates (bin_order_kernel)
       return fail(CG_EINVAL, "image %d is larger than %d x %d pixels", i, 4096 * BIN_W, 4096 * BIN_H);
   }
-  WsLayout L = ws_layout(std::max<long long>(n_items, 1), max_patch_px, 1, 0, (long long)max_tiles * n_img);
-  if (L.total > ws_bytes) return fail(CG_ENOMEM, "workspace too small: need %zu bytes, have %zu", L.total, ws_bytes);
+  L = ws_layout(std::max<long long>(n_items, 1), max_patch_px, 1, 0, (long long)max_tiles * n_img);
+  if (L.total + extra_bytes > ws_bytes)
+    return fail(CG_ENOMEM, "workspace too small: need %zu bytes, have %zu", L.total + extra_bytes, ws_bytes);
   char* base = (char*)d_ws;
   Counters* cnt = (Counters*)(base + L.counters);
   CUDA_TRY(cudaMemsetAsync(cnt, 0, sizeof(Counters), st));
   CUDA_TRY(cudaMemsetAsync(base + L.tile_count, 0, L.tile_zero_bytes, st));
   pa.n_img = n_img; pa.srcs = d_srcs; pa.n_src = h_src_off[n_fields]; pa.items = nullptr; pa.n_items = n_items;
-  pa.default_flags = CG_ITEM_FLUX_BAND; pa.implicit_mode = 3; pa.bound_cap = bound_cap;
+  pa.default_flags = default_flags; pa.implicit_mode = 3; pa.bound_cap = bound_cap;
   pa.max_patch_px = max_patch_px; pa.hdr = (ItemHdr*)(base + L.hdr); pa.tab = base + L.tab;
   pa.worklist = nullptr; pa.worklist_cap = 0; pa.cnt = cnt;     // rendered by image bin, not by work list
-  pa.filters = g_d_filters;
+  pa.filters = g_d_filters; pa.flux_table = g_flux_table; pa.flux_rows = g_flux_rows;
+  pa.out_boxes = d_out_boxes; pa.cap_boxes = d_out_boxes != nullptr;
   pa.tile_count = (int*)(base + L.tile_count); pa.tile_list = (int*)(base + L.tile_list);
   const int max_bins = max_tiles * BINS_PER_TILE;
   pa.max_tiles = max_bins;
@@ -2862,11 +2903,33 @@ int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off, const CgSou
   fa.imgs = pa.imgs; fa.n_img = n_img; fa.hdr = pa.hdr; fa.tab = (const float*)pa.tab;
   fa.tile_count = pa.tile_count; fa.tile_list = pa.tile_list;
   fa.order = (int2*)(base + L.order); fa.sched = (int*)(base + L.done);
-  fa.block_partials = (double*)(base + L.tiles); fa.ll = d_ll;
+  fa.block_partials = (double*)(base + L.tiles);
   fa.max_tiles = max_bins; fa.tiles_total = max_bins * n_img;
   if ((long long)max_bins * n_img >= (1LL << 25))
     return fail(CG_EINVAL, "%lld image bins in one call exceed the bin descriptor's 25-bit index", (long long)max_bins * n_img);
   fa.logtab = g_d_logtab; fa.cnt = cnt; fa.cull = g_cull | (g_recur ? 0 : 2);
+  bin_order_kernel<<<(fa.tiles_total + 255) / 256, 256, 0, st>>>(fa);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
+extern "C" {
+
+int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off, const CgSource* d_srcs,
+                     const int32_t* h_src_off, int32_t n_fields, double bound_cap,
+                     int64_t max_patch_px, double* d_ll, float* const* h_d_model, void* d_ws,
+                     size_t ws_bytes, void* stream) {
+  NEED_INIT();
+  cudaStream_t st = (cudaStream_t)stream;
+  PrepArgs pa;
+  FieldArgs fa;
+  WsLayout L;
+  int rc = field_setup(imgs, h_img_off, d_srcs, h_src_off, n_fields, bound_cap, max_patch_px, d_ws, ws_bytes, 0,
+                       st, CG_ITEM_FLUX_BAND, nullptr, pa, fa, L);
+  if (rc) return rc;
+  char* base = (char*)d_ws;
+  const int n_img = pa.n_img;
+  fa.ll = d_ll;
   if (h_d_model) {
     bool any = false;
     for (int i = 0; i < n_img; ++i) any = any || h_d_model[i];
@@ -2875,15 +2938,13 @@ int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off, const CgSou
       fa.model = (float* const*)(base + L.model_ptrs);
     }
   }
-  bin_order_kernel<<<(fa.tiles_total + 255) / 256, 256, 0, st>>>(fa);
-  LAUNCH_CHECK();
   const bool prof = prof_begin(st);
   field_tile_kernel<<<g_sm_count * FT_MINB, FT_THREADS, 0, st>>>(fa);      // persistent: FT_MINB CTAs per SM (launch bounds)
   prof_end(prof, st);
   LAUNCH_CHECK();
   field_tile_final_kernel<<<n_img, 1024, 0, st>>>(fa);
   LAUNCH_CHECK();
-  g_last_counters = cnt;
+  g_last_counters = pa.cnt;
   return CG_OK;
 }
 
@@ -2932,7 +2993,7 @@ int cg_items_loglik(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs,
   pa.n_img = n_img; pa.srcs = d_srcs; pa.n_src = n_src; pa.items = d_items; pa.n_items = n_items;
   pa.bound_cap = bound_cap; pa.max_patch_px = max_px; pa.hdr = (ItemHdr*)(base + L.hdr);
   pa.tab = base + L.tab; pa.worklist = (int2*)(base + L.worklist); pa.worklist_cap = L.worklist_cap;
-  pa.cnt = cnt; pa.out_boxes = d_boxes; pa.filters = g_d_filters;
+  pa.cnt = cnt; pa.out_boxes = d_boxes; pa.filters = g_d_filters; pa.flux_table = g_flux_table; pa.flux_rows = g_flux_rows;
   RenderArgs ra;
   memset(&ra, 0, sizeof ra);
   ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.worklist_cap = pa.worklist_cap; ra.cull = g_cull | (g_recur ? 0 : 2); ra.logtab = g_d_logtab; ra.cnt = cnt;
@@ -2993,7 +3054,7 @@ int cg_score_proposals(CgImage* const* imgs, int32_t n_img, const CgSource* d_sr
   pa.aux_per_img = d_bg ? 1 : 0;
   pa.bound_cap = 0; pa.max_patch_px = max_px; pa.hdr = (ItemHdr*)(base + L.hdr);
   pa.tab = base + L.tab; pa.worklist = (int2*)(base + L.worklist); pa.worklist_cap = L.worklist_cap;
-  pa.cnt = cnt; pa.filters = g_d_filters;
+  pa.cnt = cnt; pa.filters = g_d_filters; pa.flux_table = g_flux_table; pa.flux_rows = g_flux_rows;
   rc = run_prepare<float>(pa, st);
   if (rc) return rc;
   RenderArgs ra;
@@ -3233,3 +3294,5 @@ int cg_pipe_probe(int which, double* ops_per_s, void* stream) {
 }
 
 }  // extern "C"
+
+#include "celeste_sweep.cuh"

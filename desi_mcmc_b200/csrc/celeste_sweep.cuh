@@ -1,0 +1,736 @@
+// celeste_sweep.cuh -- device-resident Gibbs sweep over a crowded field (BASELINE config 4).
+// Included at the end of celeste_b200.cu (one translation unit: it reuses the field path's bin
+// lists, ft_source_rates, the render kernels and the Philox / binomial samplers).
+//
+//   models.py:123-160 + celeste_mcmc.py:98-150 + celeste_sample_sources.pyx:61-156
+//       cg_field_sample_photons   render + multinomial photon allocation per 16 x 16 image bin:
+//                                 no rate-patch buffer, the rates live in registers
+//   sources.py:327-350, models.py:156-160
+//       cg_resample_fluxes / cg_resample_epsilon   gamma conditionals drawn on the device
+//   sources.py:476-483
+//       cg_background_patches     epsilon + the active neighbours rendered on every source's box
+//   sources.py:134-183 / :275-306 for EVERY source at once
+//       cg_make_proposals, cg_score_proposals_multi, cg_select_proposals
+
+// ---------------------------------------------------------------------------
+// random variates from the counter-based generator (distributional parity, as N1)
+// ---------------------------------------------------------------------------
+__device__ inline double philox_normal(Philox& g, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  const double u1 = g.uniform(a, b, c, d), u2 = g.uniform(a, b, c, d ^ 0x80000000u);
+  return sqrt(-2. * log(u1)) * cospi(2. * u2);
+}
+
+// Marsaglia & Tsang (2000) for shape >= 1; shape < 1 through gamma(shape + 1) U^(1 / shape).
+// numpy.random.gamma (the reference's draw, sources.py:349, models.py:159) samples the same law
+// with the same method from MT19937; the stream cannot be followed in parallel.
+__device__ inline double gamma_draw(Philox& g, double shape, uint32_t id0, uint32_t id1, uint32_t tag) {
+  if (!(shape > 0.)) return 0.;
+  double boost = 1.;
+  if (shape < 1.) {
+    boost = pow(g.uniform(id0, id1, 0xffffu, tag), 1. / shape);
+    shape += 1.;
+  }
+  const double d = shape - 1. / 3., c = 1. / sqrt(9. * d);
+  for (uint32_t it = 0; it < 256; ++it) {
+    const double x = philox_normal(g, id0, id1, 2 * it, tag);
+    double v = 1. + c * x;
+    if (v <= 0.) continue;
+    v = v * v * v;
+    const double u = g.uniform(id0, id1, 2 * it + 1, tag);
+    if (log(u) < .5 * x * x + d - d * v + d * log(v)) return d * v * boost;
+  }
+  return d * boost;
+}
+
+// ---------------------------------------------------------------------------
+// photon allocation on the field path's bin lists
+// ---------------------------------------------------------------------------
+#define UNIT_FX 17592186044416.0        /* 2^44: fixed-point scale of the unit-flux patch sums */
+struct AllocTileArgs {
+  FieldArgs f;                 // tables, headers, bin lists in source order, class lists (bin_order_kernel)
+  float* samp;                 // [n_items][max_patch_px] photons given to each source, box-shaped row-major
+  long long max_patch_px;
+  double* item_counts;         // [n_items] sum of samp (integers: exact in float64 whatever the order)
+  unsigned long long* item_unit_fx;  // [n_items] sum of the unit-flux patch over the box, fixed point 2^-44
+  unsigned long long seed;
+};
+
+// One WARP per 16 x 16 image bin, lane = 4 pixels of rows r and r + 8 (field_tile_kernel's layout).
+// Pass 1 renders every source of the bin's list and sums, per pixel and in source order, the rates
+// of the sources whose box STRICTLY contains the pixel (celeste_sample_sources.pyx:53-54) --
+// sum_probs of sample_multinomial (:140-142).  Pass 2 renders them again (same instructions, same
+// values) and draws the conditional binomials in source order (:144-151); what is left is sky
+// (:152).  Pixels no box contains are all sky (:94-96).  The draws are keyed by (seed, image,
+// pixel, draw index) exactly as sample_counts_kernel keys them.
+__global__ void __launch_bounds__(256, 2) alloc_tile_kernel(AllocTileArgs A) {
+  const FieldArgs& a = A.f;
+  __shared__ __align__(16) float s_wtab[8][(CG_MAX_COMP + 1) * 8];
+  __shared__ int s_csize[FT_BUCKETS];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* const wtab = s_wtab[warp];
+  if (threadIdx.x < FT_BUCKETS) s_csize[threadIdx.x] = a.sched[threadIdx.x];
+  __syncthreads();
+  int total = 0;
+#pragma unroll
+  for (int b = 0; b < FT_BUCKETS; ++b) total += s_csize[b];
+  unsigned long long issued = 0;
+  Philox g;
+  g.key[0] = (uint32_t)A.seed; g.key[1] = (uint32_t)(A.seed >> 32);
+
+  for (;;) {
+    int u = 0;
+    if (lane == 0) u = atomicAdd(&a.sched[FT_BUCKETS + 1], 1);
+    u = __shfl_sync(0xffffffffu, u, 0);
+    if (u >= total) break;
+    int cls = FT_BUCKETS - 1, v = u;                   // heaviest class first
+    while (v >= s_csize[cls]) { v -= s_csize[cls]; --cls; }
+    const int2 dd = a.order[(long long)cls * a.tiles_total + v];
+    const int dsc = dd.x, gy = dd.y;
+    const int cnt = gy & 63, gbin = gy >> 6;
+    const int img = dsc >> 24;
+    const DevImage& im = *a.imgs.p[img];
+    const int H = im.H, W = im.W;
+    FtGeom q;
+    q.X0 = ((dsc >> 12) & 0xfff) * BIN_W; q.Y0 = (dsc & 0xfff) * BIN_H;
+    q.x = q.X0 + (lane & 3) * 4; q.yA = q.Y0 + (lane >> 2); q.yB = q.yA + 8;
+
+    float d[2][4];
+    bool inimg[2][4];
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      const int y = r ? q.yB : q.yA;
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        inimg[r][p] = (y < H) && (q.x + p < W);
+        d[r][p] = inimg[r][p] ? __ldg(im.nelec + (long long)y * W + q.x + p) : 0.f;
+      }
+    }
+    double noise = 0.0;
+    if (cnt == 0) {
+#pragma unroll
+      for (int r = 0; r < 2; ++r)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) noise += (double)d[r][p];
+    } else {
+      // candidates: the bin's list in source order, or (overflowed list) every source of the image
+      const bool scan = cnt > BIN_CAP;
+      const int ns = scan ? a.n_src[img] : 0;
+      const int rounds = scan ? (ns + 31) / 32 : 1;
+      double tot[2][4];
+      unsigned any = 0u;                       // bit r * 4 + p: some box strictly contains the pixel
+      int left[2][4];                          // photons not yet given away (nelec < 2^24: exact in fp32)
+      unsigned long long draw = 0ull;          // 8 bits per pixel: owners seen so far = index of the next draw
+#pragma unroll
+      for (int r = 0; r < 2; ++r)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) { tot[r][p] = 0.0; left[r][p] = (int)d[r][p]; }
+
+#pragma unroll 1
+      for (int pass = 0; pass < 2; ++pass) {
+        if (pass == 1) {
+          const double eps = im.epsilon;
+#pragma unroll
+          for (int r = 0; r < 2; ++r)
+#pragma unroll
+            for (int p = 0; p < 4; ++p) {
+              tot[r][p] += eps;                                        // model_fluxes[S-1] = epsilon (:104)
+              if (!((any >> (r * 4 + p)) & 1u)) { noise += (double)d[r][p]; left[r][p] = 0; }   // (:94-96)
+            }
+        }
+#pragma unroll 1
+        for (int rd = 0; rd < rounds; ++rd) {
+          int e = 0x7fffffff;
+          bool valid = false;
+          if (!scan) {
+            if (lane < cnt) { e = __ldg(a.tile_list + (long long)gbin * BIN_CAP + lane); valid = true; }
+          } else {
+            const int sidx = rd * 32 + lane;
+            if (sidx < ns) {
+              const int it = a.item_base[img] + sidx * a.item_stride[img];
+              const ItemHdr* hp = a.hdr + it;
+              const int K = hp->K;
+              e = it * 64 + K;
+              valid = (K > 0) && hp->x0 < q.X0 + BIN_W && hp->x1 > q.X0 && hp->y0 < q.Y0 + BIN_H && hp->y1 > q.Y0;
+            }
+          }
+          const unsigned vm = __ballot_sync(0xffffffffu, valid);
+          const int nv = __popc(vm);
+          const int rk = __popc(vm & ((1u << lane) - 1u));
+#pragma unroll 1
+          for (int r0 = 0; r0 < nv; ++r0) {
+            const unsigned m = __ballot_sync(0xffffffffu, valid && rk == r0);
+            const int ee = __shfl_sync(0xffffffffu, e, __ffs(m) - 1);
+            const int item = ee >> 6;
+            const ItemHdr* hp = a.hdr + item;                           // warp-uniform address: one broadcast load
+            const int4 bx = *reinterpret_cast<const int4*>(hp);
+            const int2 o = *reinterpret_cast<const int2*>(&hp->ox);
+            const float fl = (float)hp->flux;
+            float acc[2][4];
+            if (!ft_source_rates(a, item, ee & 63, bx, o, q, lane, wtab, acc[0], acc[1], issued)) continue;
+            const int wbox = bx.y - bx.x;
+            double got_sum = 0.0;
+            float unit_sum = 0.f;
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+              const int y = r ? q.yB : q.yA;
+              const bool iny = y >= bx.z && y < bx.w;
+#pragma unroll
+              for (int p = 0; p < 4; ++p) {
+                const int x = q.x + p;
+                const bool inbox = iny && x >= bx.x && x < bx.y;
+                if (!inbox) continue;
+                const bool own = x > bx.x && y > bx.z;                  // strict on the low sides (:53-54)
+                const float rate = acc[r][p] * fl;
+                if (pass == 0) {
+                  if (own) { tot[r][p] += (double)rate; any |= 1u << (r * 4 + p); }
+                } else {
+                  double got = 0.0;
+                  if (own && left[r][p] > 0) {
+                    const uint32_t pix = (uint32_t)((long long)y * W + x);
+                    const double U = g.uniform(pix, (uint32_t)img, (uint32_t)((draw >> (8 * (r * 4 + p))) & 255ull), 0xa110cu);
+                    got = binomial_from_uniform((long long)left[r][p], (double)rate / tot[r][p], U);
+                    left[r][p] -= (int)got;
+                  }
+                  if (own) { draw += 1ull << (8 * (r * 4 + p)); tot[r][p] -= (double)rate; }
+                  A.samp[(long long)item * A.max_patch_px + (long long)(y - bx.z) * wbox + (x - bx.x)] = (float)got;
+                  got_sum += got;
+                  unit_sum += acc[r][p];
+                }
+              }
+            }
+            if (pass == 1) {
+              got_sum = warp_sum(got_sum);
+#pragma unroll
+              for (int o2 = 16; o2 > 0; o2 >>= 1) unit_sum += __shfl_down_sync(0xffffffffu, unit_sum, o2);
+              if (lane == 0) {
+                if (got_sum != 0.0) atomicAdd(&A.item_counts[item], got_sum);
+                // fixed point: integer adds commute, so the sum is bitwise reproducible
+                atomicAdd(&A.item_unit_fx[item], (unsigned long long)llrint((double)unit_sum * UNIT_FX));
+              }
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < 2; ++r)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) noise += (double)left[r][p];      // samples[S-1] += unsampled (:152)
+    }
+    noise = warp_sum(noise);
+    if (lane == 0) a.block_partials[gbin] = noise;
+  }
+  if (lane == 0 && issued) atomicAdd(&a.cnt->issued, issued);
+}
+
+__global__ void unit_sums_kernel(const unsigned long long* fx, long long n, double* out) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (double)fx[i] * (1.0 / UNIT_FX);
+}
+
+// ---------------------------------------------------------------------------
+// gamma conditionals (sources.py:327-350, models.py:156-160)
+// ---------------------------------------------------------------------------
+__global__ void resample_fluxes_kernel(CgSource* srcs, int n_src, int n_img, ImgPtrs imgs,
+                                       const double* item_counts, const double* item_unit, double a0,
+                                       double b0, unsigned long long seed) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_src * CG_NUM_BANDS) return;
+  const int s = t / CG_NUM_BANDS, band = t - s * CG_NUM_BANDS;
+  CgSource& src = srcs[s];
+  // fluxes that are functions of other parameters (temperature, eigen-spectrum weights) are not free
+  if ((src.flags & CG_SRC_EIGEN) || (src.type == 0 && (src.flags & CG_SRC_PLANCK) && src.t != 0.0)) return;
+  double counts = 0.0, psf = 0.0;
+  for (int b = 0; b < n_img; ++b) {
+    const DevImage& im = *imgs.p[b];
+    if (im.band != band) continue;
+    const long long it = (long long)s * n_img + b;
+    counts += item_counts[it];                                         // :340
+    psf += item_unit[it] * im.kappa / im.calib;                        // :342
+  }
+  Philox g;
+  g.key[0] = (uint32_t)seed; g.key[1] = (uint32_t)(seed >> 32);
+  src.flux[band] = gamma_draw(g, a0 + counts, (uint32_t)s, (uint32_t)band, 0xf1u) / (b0 + psf);   // :346-349
+}
+
+__global__ void resample_epsilon_kernel(ImgPtrs imgs, int n_img, const double* noise_sum, double a0, double b0,
+                                        unsigned long long seed, double* eps_out) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= n_img) return;
+  DevImage* im = const_cast<DevImage*>(imgs.p[b]);
+  Philox g;
+  g.key[0] = (uint32_t)seed; g.key[1] = (uint32_t)(seed >> 32);
+  const double a_n = a0 + noise_sum[b], b_n = b0 + (double)im->H * (double)im->W;     // models.py:157-158
+  const double e = gamma_draw(g, a_n, (uint32_t)b, 0u, 0xe9u) / b_n;
+  im->epsilon = e;
+  if (eps_out) eps_out[b] = e;
+}
+
+// ---------------------------------------------------------------------------
+// proposals for every source
+// ---------------------------------------------------------------------------
+struct ProposalScales { double u_deg, flux_rel, theta, rho, phi_deg, sigma_rel; };
+
+// states[s][0] = current state, states[s][1..P] = Gaussian perturbations of it
+__global__ void make_proposals_kernel(const CgSource* cur, int n_src, int P, ProposalScales sc,
+                                      unsigned long long seed, CgSource* states) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long long)n_src * (P + 1)) return;
+  const int s = (int)(t / (P + 1)), p = (int)(t - (long long)s * (P + 1));
+  CgSource x = cur[s];
+  if (p > 0) {
+    Philox g;
+    g.key[0] = (uint32_t)seed; g.key[1] = (uint32_t)(seed >> 32);
+    uint32_t k = 0;
+    auto nrm = [&]() { return philox_normal(g, (uint32_t)s, (uint32_t)p, k++, 0x9e0u); };
+    x.u[0] += sc.u_deg * nrm();
+    x.u[1] += sc.u_deg * nrm();
+    const bool free_flux = !((x.flags & CG_SRC_EIGEN) || (x.type == 0 && (x.flags & CG_SRC_PLANCK) && x.t != 0.0));
+    for (int b = 0; b < CG_NUM_BANDS; ++b) {
+      const double z = nrm();
+      if (free_flux) x.flux[b] *= (1. + sc.flux_rel * z);
+    }
+    if (x.type == 1) {
+      x.theta = fmin(fmax(x.theta + sc.theta * nrm(), .01), .99);
+      x.rho = fmin(fmax(x.rho + sc.rho * nrm(), .05), 1.);
+      x.phi += sc.phi_deg * nrm();
+      x.sigma *= (1. + sc.sigma_rel * nrm());
+    }
+  }
+  states[t] = x;
+}
+
+// item (s, p, b) -> index (s (P+1) + p) n_img + b : fixed box of (s, b), auxiliary patch of (s, b)
+__global__ void score_items_kernel(const CgBox* boxes, int n_src, int P, int n_img, int flags, int use_aux,
+                                   CgItem* items) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long n = (long long)n_src * (P + 1) * n_img;
+  if (i >= n) return;
+  const int b = (int)(i % n_img);
+  const long long sp = i / n_img;
+  const int s = (int)(sp / (P + 1));
+  const CgBox bx = boxes[(long long)s * n_img + b];
+  CgItem it;
+  it.src = (int)sp; it.img = b; it.flags = flags | CG_ITEM_FIXED_BOX;
+  it.box[0] = bx.x0; it.box[1] = bx.x1; it.box[2] = bx.y0; it.box[3] = bx.y1;
+  it.aux = use_aux ? s * n_img + b : -1;
+  items[i] = it;
+}
+
+__global__ void score_multi_finalize_kernel(const double* item_ll, int n_src, int P, int n_img,
+                                            const double* log_terms, const double* log_u, double guard,
+                                            double* delta, uint8_t* accept, Counters* cnt, int* guard_list,
+                                            int guard_cap) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // (s, p - 1)
+  if (t >= (long long)n_src * P) return;
+  const int s = (int)(t / P), p = (int)(t - (long long)s * P) + 1;
+  const double* c = item_ll + (long long)s * (P + 1) * n_img;
+  double cur = 0, prop = 0;
+  for (int b = 0; b < n_img; ++b) { cur += c[b]; prop += c[(long long)p * n_img + b]; }
+  const double d = (prop - cur) + (log_terms ? log_terms[t] : 0.0);
+  const double lu = log_u[t];
+  delta[t] = d;
+  accept[t] = (lu < d) ? 1 : 0;
+  if (guard > 0 && fabs(lu - d) < guard) {
+    const int pos = atomicAdd(&cnt->guard_count, 1);
+    if (pos < guard_cap) guard_list[pos] = (int)t;
+    else atomicExch(&cnt->err_flag, 2);
+  }
+}
+
+// float64 re-score of the guard band: entry g of the list -> items [g][cur | prop][b]
+__global__ void rescore_items_kernel(const CgBox* boxes, const Counters* cnt1, const int* guard_list, int guard_cap,
+                                     int P, int n_img, int flags, int use_aux, CgItem* items) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)guard_cap * 2 * n_img) return;
+  const int b = (int)(i % n_img);
+  const int which = (int)((i / n_img) & 1);
+  const int gi = (int)(i / (2 * n_img));
+  CgItem it;
+  it.src = 0; it.img = b; it.flags = flags | CG_ITEM_FIXED_BOX; it.aux = -1;
+  it.box[0] = it.box[1] = it.box[2] = it.box[3] = 0;                   // empty: renders nothing
+  if (gi < min(cnt1->guard_count, guard_cap)) {
+    const int t = guard_list[gi];
+    const int s = t / P, p = t - s * P + 1;
+    const CgBox bx = boxes[(long long)s * n_img + b];
+    it.src = s * (P + 1) + (which ? p : 0);
+    it.box[0] = bx.x0; it.box[1] = bx.x1; it.box[2] = bx.y0; it.box[3] = bx.y1;
+    it.aux = use_aux ? s * n_img + b : -1;
+  }
+  items[i] = it;
+}
+
+__global__ void score_multi_rescore_kernel(const double* item_ll2, int n_img, const Counters* cnt1,
+                                           const int* guard_list, int guard_cap, const double* log_terms,
+                                           const double* log_u, double* delta, uint8_t* accept) {
+  const int gi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (gi >= min(cnt1->guard_count, guard_cap)) return;
+  const int t = guard_list[gi];
+  const double* c = item_ll2 + (long long)gi * 2 * n_img;
+  double cur = 0, prop = 0;
+  for (int b = 0; b < n_img; ++b) { cur += c[b]; prop += c[n_img + b]; }
+  const double d = (prop - cur) + (log_terms ? log_terms[t] : 0.0);
+  delta[t] = d;
+  accept[t] = (log_u[t] < d) ? 1 : 0;
+}
+
+// a device error (Counters.err_flag) poisons the scores: no caller can miss it
+__global__ void score_poison_kernel(const Counters* c1, const Counters* c2, long long n, double* delta) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n && (c1->err_flag || (c2 && c2->err_flag))) delta[t] = (double)NAN;
+}
+
+// Speculative MH: the P proposals of a source were all drawn around its current state, so taking
+// them in order until the first acceptance is exactly p* sequential MH steps (the proposals after
+// p* would have to be re-drawn around the new state and are discarded).
+__global__ void select_proposals_kernel(const CgSource* states, int n_src, int P, const uint8_t* accept,
+                                        CgSource* cur, int* n_accepted) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n_src) return;
+  for (int p = 0; p < P; ++p)
+    if (accept[(long long)s * P + p]) {
+      cur[s] = states[(long long)s * (P + 1) + p + 1];
+      if (n_accepted) atomicAdd(n_accepted, 1);
+      return;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// background patches (sources.py:476-483)
+// ---------------------------------------------------------------------------
+struct BgArgs {
+  FieldArgs f;               // hdr / tab of the (source, image) items, item = src * n_img + img
+  const CgBox* boxes;        // [n_src * n_img] the cached bounding boxes (sources.py:434-455)
+  const int* nbr_off;        // [n_src * n_img + 1] CSR of each (source, image)'s active neighbours (sources.py:457-472)
+  const int* nbr_idx;
+  float* bg;                 // [n_src * n_img][max_patch_px]
+  long long max_patch_px;
+  int n_src, n_img, tiles_side;   // tiles_side^2 16 x 16 tiles cover the largest box
+};
+
+// One warp per 16 x 16 tile of a target box: the active neighbours are rendered ON THE TARGET'S BOX
+// (not on their own footprints: compute_model_patch(image, xlim, ylim) of sources.py:481) and summed
+// in list order on top of epsilon.
+__global__ void __launch_bounds__(256, 2) bg_tile_kernel(BgArgs A) {
+  const FieldArgs& a = A.f;
+  __shared__ __align__(16) float s_wtab[8][(CG_MAX_COMP + 1) * 8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* const wtab = s_wtab[warp];
+  unsigned long long issued = 0;
+  const int tiles_per = A.tiles_side * A.tiles_side;
+  const long long n_units = (long long)A.n_src * A.n_img * tiles_per;
+  const long long n_warps = (long long)gridDim.x * (blockDim.x >> 5);
+  for (long long u = (long long)blockIdx.x * (blockDim.x >> 5) + warp; u < n_units; u += n_warps) {
+    const long long target = u / tiles_per;
+    const int tile = (int)(u - target * tiles_per);
+    const int s = (int)(target / A.n_img), b = (int)(target - (long long)s * A.n_img);
+    const CgBox box = A.boxes[target];
+    FtGeom q;
+    q.X0 = box.x0 + (tile % A.tiles_side) * BIN_W; q.Y0 = box.y0 + (tile / A.tiles_side) * BIN_H;
+    if (q.X0 >= box.x1 || q.Y0 >= box.y1) continue;
+    q.x = q.X0 + (lane & 3) * 4; q.yA = q.Y0 + (lane >> 2); q.yB = q.yA + 8;
+    const float eps = (float)a.imgs.p[b]->epsilon;
+    float lam[2][4];
+#pragma unroll
+    for (int r = 0; r < 2; ++r)
+#pragma unroll
+      for (int p = 0; p < 4; ++p) lam[r][p] = eps;
+    const int4 bx = make_int4(box.x0, box.x1, box.y0, box.y1);
+    for (int j = A.nbr_off[target]; j < A.nbr_off[target + 1]; ++j) {
+      const int item = A.nbr_idx[j] * A.n_img + b;
+      const ItemHdr* hp = a.hdr + item;
+      const int2 o = *reinterpret_cast<const int2*>(&hp->ox);
+      ft_source(a, item, hp->K, bx, o, (float)hp->flux, q, lane, wtab, lam, issued);
+    }
+    const int wbox = box.x1 - box.x0;
+    float* out = A.bg + target * A.max_patch_px;
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      const int y = r ? q.yB : q.yA;
+      if (y >= box.y1) continue;
+#pragma unroll
+      for (int p = 0; p < 4; ++p)
+        if (q.x + p < box.x1) out[(long long)(y - box.y0) * wbox + (q.x + p - box.x0)] = lam[r][p];
+    }
+  }
+  if (lane == 0 && issued) atomicAdd(&a.cnt->issued, issued);
+}
+
+// ===========================================================================
+// host side
+// ===========================================================================
+struct SweepLayout {
+  size_t items, items2, unit_fx, total;
+};
+
+extern "C" {
+
+size_t cg_sweep_workspace_bytes(int32_t kind, int32_t n_src, int32_t n_img, int32_t P, int64_t max_patch_px,
+                                int64_t n_tiles) {
+  const long long n_items = (long long)n_src * n_img;
+  switch (kind) {
+    case CG_WS_SWEEP_ALLOC: {
+      WsLayout L = ws_layout(std::max<long long>(n_items, 1), max_patch_px, 1, 0, n_tiles);
+      return L.total + align_up(sizeof(unsigned long long) * std::max<long long>(n_items, 1), 256) + 512;
+    }
+    case CG_WS_SWEEP_SCORE: {
+      const long long n1 = n_items * (P + 1);
+      const int cap = cg_sweep_guard_cap(n_src, P);
+      WsLayout L = ws_layout(std::max<long long>(n1, 1), max_patch_px, 0, 0, 0);
+      WsLayout L2 = ws_layout((long long)cap * 2 * n_img * 2, max_patch_px, 0, 0, 0);   // x2: float64 tables
+      return L.total + L2.total + align_up(sizeof(CgItem) * n1, 256) +
+             align_up(sizeof(CgItem) * (size_t)cap * 2 * n_img, 256) + align_up(sizeof(int) * (size_t)cap, 256) + 1024;
+    }
+    case CG_WS_SWEEP_BACKGROUND: {
+      WsLayout L = ws_layout(std::max<long long>(n_items, 1), max_patch_px, 0, 0, 0);
+      return L.total + 512;
+    }
+    default: return 0;
+  }
+}
+
+int32_t cg_sweep_guard_cap(int32_t n_src, int32_t P) {
+  const long long n = (long long)n_src * P;
+  return (int32_t)std::min<long long>(n, std::max<long long>(4096, n / 8));
+}
+
+int cg_field_sample_photons(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs, int32_t n_src,
+                            double bound_cap, int64_t max_patch_px, uint64_t seed, float* d_samp,
+                            CgBox* d_boxes, double* d_noise_sum, double* d_counts, double* d_unit_sums,
+                            void* d_ws, size_t ws_bytes, void* stream) {
+  NEED_INIT();
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n_src < 0) return fail(CG_EINVAL, "negative n_src");
+  if (!d_samp || !d_boxes || !d_noise_sum) return fail(CG_EINVAL, "null output");
+  const long long n_items = (long long)n_src * n_img;
+  const int32_t img_off[2] = {0, n_img}, src_off[2] = {0, n_src};
+  PrepArgs pa;
+  AllocTileArgs A;
+  memset(&A, 0, sizeof A);
+  WsLayout L;
+  const size_t extra = align_up(sizeof(unsigned long long) * std::max<long long>(n_items, 1), 256);
+  int rc = field_setup(imgs, img_off, d_srcs, src_off, 1, bound_cap, max_patch_px, d_ws, ws_bytes, extra, st,
+                       CG_ITEM_FLUX_BAND, d_boxes, pa, A.f, L);
+  if (rc) return rc;
+  char* base = (char*)d_ws;
+  A.samp = d_samp; A.max_patch_px = max_patch_px; A.seed = seed;
+  A.item_unit_fx = (unsigned long long*)(base + align_up(L.total, 256));
+  // the counts are accumulated here whether or not the caller wants them
+  double* counts = d_counts ? d_counts : (double*)(base + L.item_ll);
+  A.item_counts = counts;
+  if (n_items > 0) {
+    CUDA_TRY(cudaMemsetAsync(counts, 0, sizeof(double) * n_items, st));
+    CUDA_TRY(cudaMemsetAsync(A.item_unit_fx, 0, sizeof(unsigned long long) * n_items, st));
+  }
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, alloc_tile_kernel, 256, 0) != cudaSuccess || per_sm < 1)
+    per_sm = 2;
+  alloc_tile_kernel<<<g_sm_count * per_sm, 256, 0, st>>>(A);
+  LAUNCH_CHECK();
+  A.f.ll = d_noise_sum;                       // per-image sum of the per-bin noise photons, fixed order
+  field_tile_final_kernel<<<n_img, 1024, 0, st>>>(A.f);
+  LAUNCH_CHECK();
+  if (d_unit_sums && n_items > 0) {
+    unit_sums_kernel<<<(unsigned)((n_items + 255) / 256), 256, 0, st>>>(A.item_unit_fx, n_items, d_unit_sums);
+    LAUNCH_CHECK();
+  }
+  g_last_counters = pa.cnt;
+  return CG_OK;
+}
+
+int cg_resample_fluxes(CgImage* const* imgs, int32_t n_img, CgSource* d_srcs, int32_t n_src,
+                       const double* d_counts, const double* d_unit_sums, double a0, double b0, uint64_t seed,
+                       void* stream) {
+  NEED_INIT();
+  ImgPtrs ip;
+  int rc = fill_imgs(imgs, n_img, &ip);
+  if (rc) return rc;
+  if (n_src <= 0) return CG_OK;
+  if (!d_counts || !d_unit_sums) return fail(CG_EINVAL, "photon counts and unit-patch sums are required");
+  resample_fluxes_kernel<<<(n_src * CG_NUM_BANDS + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+      d_srcs, n_src, n_img, ip, d_counts, d_unit_sums, a0, b0, seed);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
+int cg_resample_epsilon(CgImage* const* imgs, int32_t n_img, const double* d_noise_sum, double a0, double b0,
+                        uint64_t seed, double* d_eps_out, void* stream) {
+  NEED_INIT();
+  ImgPtrs ip;
+  int rc = fill_imgs(imgs, n_img, &ip);
+  if (rc) return rc;
+  resample_epsilon_kernel<<<1, 64, 0, (cudaStream_t)stream>>>(ip, n_img, d_noise_sum, a0, b0, seed, d_eps_out);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
+int cg_image_sync_epsilon(CgImage* img, void* stream, double* h_epsilon) {
+  NEED_INIT();
+  if (!img) return fail(CG_EINVAL, "null image");
+  CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+  CUDA_TRY(cudaMemcpy(&img->h.epsilon, &img->d->epsilon, sizeof(double), cudaMemcpyDeviceToHost));
+  if (h_epsilon) *h_epsilon = img->h.epsilon;
+  return CG_OK;
+}
+
+int cg_make_proposals(const CgSource* d_cur, int32_t n_src, int32_t P, const double* h_scales, uint64_t seed,
+                      CgSource* d_states, void* stream) {
+  NEED_INIT();
+  if (n_src <= 0) return CG_OK;
+  if (P < 0 || !h_scales) return fail(CG_EINVAL, "bad proposal arguments");
+  ProposalScales sc = {h_scales[0], h_scales[1], h_scales[2], h_scales[3], h_scales[4], h_scales[5]};
+  const long long n = (long long)n_src * (P + 1);
+  make_proposals_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(d_cur, n_src, P, sc, seed,
+                                                                                     d_states);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
+int cg_select_proposals(const CgSource* d_states, int32_t n_src, int32_t P, const uint8_t* d_accept,
+                        CgSource* d_cur, int32_t* d_n_accepted, void* stream) {
+  NEED_INIT();
+  if (n_src <= 0) return CG_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (d_n_accepted) CUDA_TRY(cudaMemsetAsync(d_n_accepted, 0, sizeof(int), st));
+  select_proposals_kernel<<<(n_src + 255) / 256, 256, 0, st>>>(d_states, n_src, P, d_accept, d_cur, d_n_accepted);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
+int cg_score_proposals_multi(CgImage* const* imgs, int32_t n_img, const CgSource* d_states, int32_t n_src,
+                             int32_t P, const CgBox* d_boxes, int32_t mode, const float* d_aux,
+                             int64_t max_patch_px, const double* d_log_terms, const double* d_log_u,
+                             double guard, double* d_delta, uint8_t* d_accept, int32_t* d_n_guard, void* d_ws,
+                             size_t ws_bytes, void* stream) {
+  NEED_INIT();
+  cudaStream_t st = (cudaStream_t)stream;
+  if (mode != CG_LL_POISSON_BG && mode != CG_LL_CONDITIONAL) return fail(CG_EINVAL, "unknown mode %d", mode);
+  if (mode == CG_LL_CONDITIONAL && !d_aux) return fail(CG_EINVAL, "conditional mode needs the photon patches");
+  if (n_src <= 0 || P <= 0) return CG_OK;
+  if (!d_boxes || !d_log_u || !d_delta || !d_accept) return fail(CG_EINVAL, "null argument");
+  PrepArgs pa;
+  memset(&pa, 0, sizeof pa);
+  int rc = fill_imgs(imgs, n_img, &pa.imgs);
+  if (rc) return rc;
+  for (int i = 0; i < n_img; ++i)
+    if (!imgs[i]->h.nelec) return fail(CG_EINVAL, "image %d has no nelec buffer", i);
+  const long long n1 = (long long)n_src * (P + 1) * n_img;
+  if (n1 > 0x7fffffffLL) return fail(CG_EINVAL, "too many items");
+  const int cap = guard > 0 ? cg_sweep_guard_cap(n_src, P) : 0;
+  const long long n2 = (long long)cap * 2 * n_img;
+  WsLayout L = ws_layout(n1, max_patch_px, 0, 0, 0);
+  WsLayout L2 = ws_layout(std::max<long long>(n2, 1) * 2, max_patch_px, 0, 0, 0);
+  size_t o = align_up(L.total, 256);
+  const size_t o_l2 = o; o += align_up(L2.total, 256);
+  const size_t o_items = o; o += align_up(sizeof(CgItem) * n1, 256);
+  const size_t o_items2 = o; o += align_up(sizeof(CgItem) * (size_t)std::max<long long>(n2, 1), 256);
+  const size_t o_glist = o; o += align_up(sizeof(int) * (size_t)std::max(cap, 1), 256);
+  if (o > ws_bytes) return fail(CG_ENOMEM, "workspace too small: need %zu bytes, have %zu", o, ws_bytes);
+  char* base = (char*)d_ws;
+  Counters* cnt = (Counters*)(base + L.counters);
+  CUDA_TRY(cudaMemsetAsync(cnt, 0, sizeof(Counters), st));
+  CgItem* items = (CgItem*)(base + o_items);
+  const int use_aux = d_aux != nullptr;
+  score_items_kernel<<<(unsigned)((n1 + 255) / 256), 256, 0, st>>>(d_boxes, n_src, P, n_img, CG_ITEM_FLUX_BAND,
+                                                                   use_aux, items);
+  LAUNCH_CHECK();
+  pa.n_img = n_img; pa.srcs = d_states; pa.n_src = n_src * (P + 1); pa.items = items; pa.n_items = n1;
+  pa.bound_cap = 0; pa.max_patch_px = max_patch_px; pa.hdr = (ItemHdr*)(base + L.hdr); pa.tab = base + L.tab;
+  pa.worklist = (int2*)(base + L.worklist); pa.worklist_cap = L.worklist_cap; pa.cnt = cnt;
+  pa.filters = g_d_filters; pa.flux_table = g_flux_table; pa.flux_rows = g_flux_rows;
+  rc = run_prepare<float>(pa, st);
+  if (rc) return rc;
+  RenderArgs ra;
+  memset(&ra, 0, sizeof ra);
+  ra.imgs = pa.imgs; ra.hdr = pa.hdr; ra.tab = pa.tab; ra.worklist = pa.worklist; ra.worklist_cap = pa.worklist_cap;
+  ra.cull = g_cull | (g_recur ? 0 : 2); ra.logtab = g_d_logtab; ra.cnt = cnt;
+  ra.aux = d_aux; ra.aux_offsets = nullptr; ra.aux_stride = max_patch_px; ra.partials = (double*)(base + L.partials);
+  rc = (mode == CG_LL_POISSON_BG) ? run_render<float, MODE_POISSON>(ra, n1, st) : run_render<float, MODE_COND>(ra, n1, st);
+  if (rc) return rc;
+  double* item_ll = (double*)(base + L.item_ll);
+  items_finalize_kernel<<<(unsigned)((n1 + 255) / 256), 256, 0, st>>>(pa.hdr, ra.partials, n1, mode, item_ll, nullptr, 1);
+  LAUNCH_CHECK();
+  int* guard_list = (int*)(base + o_glist);
+  const long long n_sp = (long long)n_src * P;
+  score_multi_finalize_kernel<<<(unsigned)((n_sp + 255) / 256), 256, 0, st>>>(
+      item_ll, n_src, P, n_img, d_log_terms, d_log_u, guard, d_delta, d_accept, cnt, guard_list, cap);
+  LAUNCH_CHECK();
+  Counters* cnt2 = nullptr;
+  if (cap > 0) {
+    char* b2 = base + o_l2;
+    cnt2 = (Counters*)(b2 + L2.counters);
+    CUDA_TRY(cudaMemsetAsync(cnt2, 0, sizeof(Counters), st));
+    CgItem* items2 = (CgItem*)(base + o_items2);
+    rescore_items_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, st>>>(d_boxes, cnt, guard_list, cap, P, n_img,
+                                                                       CG_ITEM_FLUX_BAND, use_aux, items2);
+    LAUNCH_CHECK();
+    PrepArgs p2 = pa;
+    p2.items = items2; p2.n_items = n2; p2.hdr = (ItemHdr*)(b2 + L2.hdr); p2.tab = b2 + L2.tab;
+    p2.worklist = (int2*)(b2 + L2.worklist); p2.worklist_cap = L2.worklist_cap; p2.cnt = cnt2;
+    rc = run_prepare<double>(p2, st);
+    if (rc) return rc;
+    RenderArgs r2 = ra;
+    r2.hdr = p2.hdr; r2.tab = p2.tab; r2.worklist = p2.worklist; r2.worklist_cap = p2.worklist_cap; r2.cnt = cnt2;
+    r2.partials = (double*)(b2 + L2.partials);
+    rc = (mode == CG_LL_POISSON_BG) ? run_render<double, MODE_POISSON>(r2, n2, st)
+                                    : run_render<double, MODE_COND>(r2, n2, st);
+    if (rc) return rc;
+    double* item_ll2 = (double*)(b2 + L2.item_ll);
+    items_finalize_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, st>>>(p2.hdr, r2.partials, n2, mode, item_ll2,
+                                                                        nullptr, 1);
+    LAUNCH_CHECK();
+    score_multi_rescore_kernel<<<(cap + 255) / 256, 256, 0, st>>>(item_ll2, n_img, cnt, guard_list, cap, d_log_terms,
+                                                                  d_log_u, d_delta, d_accept);
+    LAUNCH_CHECK();
+  }
+  score_poison_kernel<<<(unsigned)((n_sp + 255) / 256), 256, 0, st>>>(cnt, cnt2, n_sp, d_delta);
+  LAUNCH_CHECK();
+  if (d_n_guard)
+    CUDA_TRY(cudaMemcpyAsync(d_n_guard, &cnt->guard_count, sizeof(int), cudaMemcpyDeviceToDevice, st));
+  g_last_counters = cnt;
+  return CG_OK;
+}
+
+int cg_background_patches(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs, int32_t n_src,
+                          const CgBox* d_boxes, const int32_t* d_nbr_off, const int32_t* d_nbr_idx,
+                          int64_t max_patch_px, int32_t max_box_side, float* d_bg, void* d_ws, size_t ws_bytes,
+                          void* stream) {
+  NEED_INIT();
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n_src <= 0) return CG_OK;
+  if (!d_boxes || !d_nbr_off || !d_bg) return fail(CG_EINVAL, "null argument");
+  if (max_box_side < 1 || (long long)max_box_side * max_box_side > max_patch_px)
+    return fail(CG_EINVAL, "max_box_side^2 must not exceed max_patch_px");
+  PrepArgs pa;
+  memset(&pa, 0, sizeof pa);
+  int rc = fill_imgs(imgs, n_img, &pa.imgs);
+  if (rc) return rc;
+  const long long n_items = (long long)n_src * n_img;
+  WsLayout L = ws_layout(n_items, max_patch_px, 0, 0, 0);
+  if (L.total > ws_bytes) return fail(CG_ENOMEM, "workspace too small: need %zu bytes, have %zu", L.total, ws_bytes);
+  char* base = (char*)d_ws;
+  Counters* cnt = (Counters*)(base + L.counters);
+  CUDA_TRY(cudaMemsetAsync(cnt, 0, sizeof(Counters), st));
+  // tables of every (source, image) item; the footprints are not used (the neighbours are rendered on
+  // the TARGET's box), so nothing is listed, binned or capped
+  pa.n_img = n_img; pa.srcs = d_srcs; pa.n_src = n_src; pa.items = nullptr; pa.n_items = n_items;
+  pa.default_flags = CG_ITEM_FLUX_BAND; pa.implicit_mode = 0; pa.bound_cap = 0; pa.max_patch_px = max_patch_px;
+  pa.hdr = (ItemHdr*)(base + L.hdr); pa.tab = base + L.tab; pa.worklist = nullptr; pa.cnt = cnt;
+  pa.filters = g_d_filters; pa.flux_table = g_flux_table; pa.flux_rows = g_flux_rows;
+  rc = run_prepare<float>(pa, st);
+  if (rc) return rc;
+  BgArgs B;
+  memset(&B, 0, sizeof B);
+  B.f.imgs = pa.imgs; B.f.n_img = n_img; B.f.hdr = pa.hdr; B.f.tab = (const float*)pa.tab; B.f.cnt = cnt;
+  B.f.cull = g_cull | (g_recur ? 0 : 2); B.f.logtab = g_d_logtab;
+  B.boxes = d_boxes; B.nbr_off = d_nbr_off; B.nbr_idx = d_nbr_idx; B.bg = d_bg; B.max_patch_px = max_patch_px;
+  B.n_src = n_src; B.n_img = n_img; B.tiles_side = (max_box_side + BIN_W - 1) / BIN_W;
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bg_tile_kernel, 256, 0) != cudaSuccess || per_sm < 1)
+    per_sm = 2;
+  bg_tile_kernel<<<g_sm_count * per_sm, 256, 0, st>>>(B);
+  LAUNCH_CHECK();
+  g_last_counters = cnt;
+  return CG_OK;
+}
+
+}  // extern "C"

@@ -21,7 +21,7 @@ import torch
 from . import _ffi
 from ._ffi import (BOX_DTYPE, CG_ITEM_FIXED_BOX, CG_ITEM_FLUX_BAND, CG_ITEM_FLUX_UNIT,
                    CG_LL_CONDITIONAL, CG_LL_POISSON_BG, CG_MAX_IMAGES, CG_NUM_BANDS,
-                   CG_SRC_PLANCK, ITEM_DTYPE, SRC_DTYPE, check)
+                   CG_SRC_EIGEN, CG_SRC_PLANCK, ITEM_DTYPE, SRC_DTYPE, check)
 
 BANDS = ["u", "g", "r", "i", "z"]
 
@@ -150,8 +150,9 @@ class SrcParams(object):
     band->value dict, as the reference accepts both."""
 
     def __init__(self, u, a=None, b=None, t=None, v=None, theta=None, phi=None,
-                 sigma=None, rho=None, fluxes=None, ell=None, d=None, header=None):
+                 sigma=None, rho=None, fluxes=None, ell=None, d=None, header=None, flux_row=None):
         self.a = a
+        self.flux_row = flux_row          # row of the bound flux table (eigen-spectrum route), or None
         self.u = np.asarray(u, dtype=np.float64)
         self.b, self.t = b, t
         self.v = v
@@ -191,7 +192,10 @@ def pack_sources(srcs: Sequence, out: np.ndarray | None = None) -> np.ndarray:
         flags = 0
         if s.fluxes is not None:
             r["flux"] = [s.fluxes[c] for c in BANDS] if isinstance(s.fluxes, dict) else s.fluxes
-        if s.a == 0 and s.t:
+        if getattr(s, "flux_row", None) is not None:
+            flags |= CG_SRC_EIGEN
+            r["flux_row"] = int(s.flux_row)
+        elif s.a == 0 and s.t:
             flags |= CG_SRC_PLANCK
             r["t"] = s.t
             r["b"] = s.b
@@ -961,3 +965,273 @@ def prior_sufficient_stats(resp: torch.Tensor, colors) -> torch.Tensor:
     out = torch.zeros(K * (1 + D + D * (D + 1) // 2), dtype=torch.float64, device=dev)
     check(lib().cg_prior_stats(resp.data_ptr(), c.data_ptr(), N, K, D, out.data_ptr(), stream_ptr()))
     return out
+
+
+# ---------------------------------------------------------------------------
+# device-resident Gibbs sweep over a crowded field (BASELINE config 4)
+# ---------------------------------------------------------------------------
+def bind_flux_table(table: torch.Tensor | None) -> None:
+    """cg_set_flux_table: band fluxes [rows, 5] (float64, nanomaggies, device) for sources
+    flagged CG_SRC_EIGEN (flux_row = row).  Pass None to unbind."""
+    if table is None:
+        check(lib().cg_set_flux_table(None, 0))
+        _state["flux_table"] = None
+        return
+    if table.dtype != torch.float64 or table.dim() != 2 or table.shape[1] != CG_NUM_BANDS or not table.is_cuda:
+        raise ValueError("flux table must be a float64 CUDA tensor of shape [rows, 5]")
+    table = table.contiguous()
+    check(lib().cg_set_flux_table(table.data_ptr(), table.shape[0]))
+    _state["flux_table"] = table            # keep it alive while it is bound
+
+
+class EigenSpectra(object):
+    """Device state of the eigen-spectrum flux model (experiments/redshift/redshift_utils.py:304-323,
+    quasar_infer_photometry.py:31-46): per source z, simplex weights w over the K basis spectra and
+    the magnitude scale m.  project() evaluates mu = project_to_bands(w.B, lam0 (1+z)) m / (1+z) for
+    every row into the bound flux table -- the render reads it from HBM (no host hop per band)."""
+
+    def __init__(self, z, w, m, B, lam0):
+        if not _state["filters"]:
+            load_filter_curves()
+        dev = device()
+        d = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(dev)
+        self.z, self.w, self.m, self.B, self.lam0 = d(np.atleast_1d(z)), d(np.atleast_2d(w)), d(np.atleast_1d(m)), d(B), d(lam0)
+        self.n = self.z.shape[0]
+        self.K, self.V = self.B.shape
+        if self.w.shape != (self.n, self.K) or self.m.shape[0] != self.n or self.lam0.shape[0] != self.V:
+            raise ValueError("z, w, m, B, lam0 disagree on their sizes")
+        self.mu = torch.zeros((self.n, CG_NUM_BANDS), dtype=torch.float64, device=dev)
+        bind_flux_table(self.mu)
+
+    def project(self) -> torch.Tensor:
+        check(lib().cg_eigen_fluxes(self.z.data_ptr(), self.w.data_ptr(), self.m.data_ptr(), self.B.data_ptr(),
+                                    self.lam0.data_ptr(), self.n, self.K, self.V, None, None,
+                                    self.mu.data_ptr(), None, stream_ptr()))
+        return self.mu
+
+
+def static_boxes(images: Sequence[Image], u: np.ndarray, pixel_radius: float) -> np.ndarray:
+    """make_bbox_dict (sources.py:434-455) for every (source, image): boxes [n_src, n_img] BOX_DTYPE."""
+    u = np.asarray(u, dtype=np.float64).reshape(-1, 2)
+    out = np.zeros((u.shape[0], len(images)), dtype=BOX_DTYPE)
+    for b, im in enumerate(images):
+        phi1rad = im.phi_n[1] / 180. * np.pi
+        iwc = np.stack([(u[:, 0] - im.phi_n[0]) * np.cos(phi1rad), u[:, 1] - im.phi_n[1]])
+        px, py = np.dot(im.Ups_n_inv, iwc) + im.rho_n[:, None]
+        H, W = im.shape
+        out["x0"][:, b] = np.maximum(0, np.floor(px - pixel_radius).astype(np.int64))
+        out["x1"][:, b] = np.minimum(W, np.ceil(px + pixel_radius).astype(np.int64))
+        out["y0"][:, b] = np.maximum(0, np.floor(py - pixel_radius).astype(np.int64))
+        out["y1"][:, b] = np.minimum(H, np.ceil(py + pixel_radius).astype(np.int64))
+    return out
+
+
+def active_neighbours(boxes: np.ndarray):
+    """get_active_sources (sources.py:457-472) for every (source, image): CSR (offsets [n_src*n_img+1],
+    indices) of the OTHER sources whose box intersects -- the reference's test, as written:
+    |xa0 - xb0| * 2 < wa + wb and |ya0 - yb0| * 2 < ha + hb.  Sorted by source index."""
+    S, n_img = boxes.shape
+    offs = np.zeros(S * n_img + 1, dtype=np.int32)
+    idx = []
+    for b in range(n_img):
+        x0, y0 = boxes["x0"][:, b].astype(np.int64), boxes["y0"][:, b].astype(np.int64)
+        w = boxes["x1"][:, b].astype(np.int64) - x0
+        h = boxes["y1"][:, b].astype(np.int64) - y0
+        order = np.argsort(x0, kind="stable")
+        xs = x0[order]
+        wmax = int(w.max()) if S else 0
+        for s in range(S):
+            lo = np.searchsorted(xs, x0[s] - wmax, side="left")
+            hi = np.searchsorted(xs, x0[s] + wmax, side="right")
+            c = order[lo:hi]
+            ok = (np.abs(x0[c] - x0[s]) * 2 < w[c] + w[s]) & (np.abs(y0[c] - y0[s]) * 2 < h[c] + h[s]) & (c != s)
+            nb = np.sort(c[ok])
+            idx.append((s * n_img + b, nb))
+    idx.sort(key=lambda t: t[0])
+    flat = []
+    for k, (t, nb) in enumerate(idx):
+        offs[t + 1] = nb.size
+        flat.append(nb)
+    offs = np.cumsum(offs, dtype=np.int64).astype(np.int32)
+    return offs, (np.concatenate(flat).astype(np.int32) if flat else np.zeros(0, dtype=np.int32))
+
+
+class GibbsSweep(object):
+    """One field's sources advanced by full Gibbs sweeps ENTIRELY on the device
+    (CelesteBase.resample_model, models.py:75-83, for all sources at once):
+
+      1. eigen-spectrum fluxes projected into the flux table (A17; Planck stars inside prepare, A16)
+      2. photon allocation for the five bands (models.py:123-160)            cg_field_sample_photons
+      3. epsilon ~ Gamma per image (models.py:156-160)                       cg_resample_epsilon
+      4. fluxes ~ Gamma per source and band (sources.py:327-350)             cg_resample_fluxes
+      5. P proposals per source scored by the conditional likelihood given its photons
+         (Source.log_likelihood, sources.py:134-183), accept/reject on the device from host-supplied
+         log-uniforms, first accepted proposal taken (exact: the sources are independent given z)
+      6. optionally P more proposals scored by the full MH ratio over the cached boxes and
+         backgrounds (calculate_acceptance_logprob, sources.py:275-306; backgrounds =
+         generate_background_patch, :476-483, re-rendered every sweep)
+      7. the field's per-image log-likelihood (celeste.py:237-252)
+
+    Nothing synchronises inside sweep(); stats() reads the results back."""
+
+    DEFAULT_SCALES = (0.05 * 1.1e-4, 0.02, 0.02, 0.02, 3.0, 0.03)    # synth.make_proposals
+
+    def __init__(self, images: Sequence[Image], srcs: np.ndarray, bound_cap: float = 25.0, proposals: int = 16,
+                 pixel_radius: float = 25.0, scales=None, guard: float = 1e-2, eigen: EigenSpectra | None = None,
+                 background_pass: bool = True, a0: float = 5., b0: float = .005, seed: int = 0):
+        self.L = lib()
+        self.images = list(images)
+        self.harr, self.n_img = _handles(self.images)
+        _need_filters(srcs)
+        self.n_src = int(srcs.shape[0])
+        self.P = int(proposals)
+        self.bound_cap, self.pixel_radius = float(bound_cap), float(pixel_radius)
+        self.guard, self.a0, self.b0 = float(guard), float(a0), float(b0)
+        self.eigen = eigen
+        self.background_pass = bool(background_pass)
+        self.scales = np.asarray(self.DEFAULT_SCALES if scales is None else scales, dtype=np.float64)
+        self.seed, self.n_sweeps = int(seed), 0
+        dev = device()
+        side = int(max(2 * bound_cap + 3, 2 * pixel_radius + 2))
+        self.side = side
+        self.max_patch_px = side * side
+        n_items = self.n_src * self.n_img
+        self.n_items = n_items
+        self.d_cur = to_device(srcs)
+        self.d_states = torch.zeros(self.n_src * (self.P + 1) * SRC_DTYPE.itemsize, dtype=torch.uint8, device=dev)
+        self.samp = torch.zeros((max(n_items, 1), self.max_patch_px), dtype=torch.float32, device=dev)
+        self.d_boxes = torch.zeros(max(n_items, 1) * BOX_DTYPE.itemsize, dtype=torch.uint8, device=dev)
+        self.noise = torch.zeros(self.n_img, dtype=torch.float64, device=dev)
+        self.counts = torch.zeros(max(n_items, 1), dtype=torch.float64, device=dev)
+        self.unit = torch.zeros(max(n_items, 1), dtype=torch.float64, device=dev)
+        self.eps = torch.zeros(self.n_img, dtype=torch.float64, device=dev)
+        self.ll = torch.zeros(self.n_img, dtype=torch.float64, device=dev)
+        n_sp = max(self.n_src * self.P, 1)
+        self.delta = [torch.zeros(n_sp, dtype=torch.float64, device=dev) for _ in range(2)]
+        self.accept = [torch.zeros(n_sp, dtype=torch.uint8, device=dev) for _ in range(2)]
+        self.n_guard = torch.zeros(2, dtype=torch.int32, device=dev)
+        self.n_acc = torch.zeros(2, dtype=torch.int32, device=dev)
+        self.stage_u = [PinnedStage(n_sp * 8) for _ in range(2)]
+        tiles = self.n_img * max(int(self.L.cg_field_tiles(im.shape[0], im.shape[1])) for im in self.images)
+        need = lambda kind: int(self.L.cg_sweep_workspace_bytes(kind, self.n_src, self.n_img, self.P,
+                                                                self.max_patch_px, tiles))
+        self.ws_alloc = torch.empty(need(_ffi.CG_WS_SWEEP_ALLOC), dtype=torch.uint8, device=dev)
+        self.ws_score = torch.empty(need(_ffi.CG_WS_SWEEP_SCORE), dtype=torch.uint8, device=dev)
+        self.ws_field = field_workspace(self.images, self.n_src, self.max_patch_px)
+        self.workspace_bytes = self.ws_alloc.numel() + self.ws_score.numel() + self.ws_field.numel() + \
+            self.samp.numel() * 4
+        if self.background_pass:
+            boxes = static_boxes(self.images, srcs["u"], self.pixel_radius)
+            self.h_static = boxes
+            w = (boxes["x1"] - boxes["x0"]).max() if n_items else 0
+            h = (boxes["y1"] - boxes["y0"]).max() if n_items else 0
+            if max(w, h) > side:
+                raise ValueError("static boxes exceed the patch side")
+            offs, idx = active_neighbours(boxes)
+            self.h_nbr = (offs, idx)
+            self.d_static = to_device(boxes.reshape(-1))
+            self.d_nbr_off = torch.from_numpy(offs).to(dev)
+            self.d_nbr_idx = torch.from_numpy(idx if idx.size else np.zeros(1, dtype=np.int32)).to(dev)
+            self.bg = torch.zeros((max(n_items, 1), self.max_patch_px), dtype=torch.float32, device=dev)
+            self.ws_bg = torch.empty(need(_ffi.CG_WS_SWEEP_BACKGROUND), dtype=torch.uint8, device=dev)
+            self.workspace_bytes += self.ws_bg.numel() + self.bg.numel() * 4
+
+    # ---- the individual steps (each one C-ABI call; usable on their own) ---------------
+    def allocate(self, seed: int):
+        check(self.L.cg_field_sample_photons(
+            self.harr, self.n_img, self.d_cur.data_ptr(), self.n_src, self.bound_cap, self.max_patch_px,
+            int(seed) & 0xFFFFFFFFFFFFFFFF, self.samp.data_ptr(), self.d_boxes.data_ptr(), self.noise.data_ptr(),
+            self.counts.data_ptr(), self.unit.data_ptr(), self.ws_alloc.data_ptr(), self.ws_alloc.numel(),
+            stream_ptr()))
+
+    def resample_epsilon(self, seed: int):
+        check(self.L.cg_resample_epsilon(self.harr, self.n_img, self.noise.data_ptr(), self.a0, self.b0,
+                                         int(seed) & 0xFFFFFFFFFFFFFFFF, self.eps.data_ptr(), stream_ptr()))
+
+    def resample_fluxes(self, seed: int):
+        check(self.L.cg_resample_fluxes(self.harr, self.n_img, self.d_cur.data_ptr(), self.n_src,
+                                        self.counts.data_ptr(), self.unit.data_ptr(), self.a0, self.b0,
+                                        int(seed) & 0xFFFFFFFFFFFFFFFF, stream_ptr()))
+
+    def propose(self, seed: int):
+        check(self.L.cg_make_proposals(self.d_cur.data_ptr(), self.n_src, self.P, self.scales.ctypes.data,
+                                       int(seed) & 0xFFFFFFFFFFFFFFFF, self.d_states.data_ptr(), stream_ptr()))
+
+    def score(self, which: int, log_u: np.ndarray):
+        """which = 0: conditional on the allocated photons; 1: full MH ratio with backgrounds."""
+        d_u = self.stage_u[which].upload(np.ascontiguousarray(log_u, dtype=np.float64))
+        if which == 0:
+            mode, boxes, aux = CG_LL_CONDITIONAL, self.d_boxes, self.samp
+        else:
+            mode, boxes, aux = CG_LL_POISSON_BG, self.d_static, self.bg
+        check(self.L.cg_score_proposals_multi(
+            self.harr, self.n_img, self.d_states.data_ptr(), self.n_src, self.P, boxes.data_ptr(), mode,
+            aux.data_ptr(), self.max_patch_px, None, d_u.data_ptr(), self.guard, self.delta[which].data_ptr(),
+            self.accept[which].data_ptr(), self.n_guard[which:].data_ptr(), self.ws_score.data_ptr(),
+            self.ws_score.numel(), stream_ptr()))
+
+    def select(self, which: int):
+        check(self.L.cg_select_proposals(self.d_states.data_ptr(), self.n_src, self.P,
+                                         self.accept[which].data_ptr(), self.d_cur.data_ptr(),
+                                         self.n_acc[which:].data_ptr(), stream_ptr()))
+
+    def backgrounds(self):
+        check(self.L.cg_background_patches(
+            self.harr, self.n_img, self.d_cur.data_ptr(), self.n_src, self.d_static.data_ptr(),
+            self.d_nbr_off.data_ptr(), self.d_nbr_idx.data_ptr(), self.max_patch_px, self.side,
+            self.bg.data_ptr(), self.ws_bg.data_ptr(), self.ws_bg.numel(), stream_ptr()))
+
+    def loglik(self):
+        check(self.L.cg_field_loglik(self.harr, self.n_img, self.d_cur.data_ptr(), self.n_src, self.bound_cap,
+                                     self.max_patch_px, self.ll.data_ptr(), None, self.ws_field.data_ptr(),
+                                     self.ws_field.numel(), stream_ptr()))
+
+    # ---- one sweep -------------------------------------------------------------------------
+    def sweep(self, log_u=None):
+        """log_u: optional pair of host arrays [n_src * P] (conditional pass, background pass);
+        default: drawn from numpy RandomState(seed + sweep index)."""
+        k = self.n_sweeps
+        base = (self.seed + 1) * 1000003 + k * 16
+        n_sp = self.n_src * self.P
+        if log_u is None:
+            rng = np.random.RandomState((self.seed + k) & 0x7fffffff)
+            log_u = (np.log(rng.uniform(size=n_sp)), np.log(rng.uniform(size=n_sp)))
+        if self.eigen is not None:
+            self.eigen.project()
+        self.allocate(base + 1)
+        self.resample_epsilon(base + 2)
+        self.resample_fluxes(base + 3)
+        if self.P > 0 and self.n_src > 0:
+            self.propose(base + 4)
+            self.score(0, log_u[0])
+            self.select(0)
+            if self.background_pass:
+                self.backgrounds()
+                self.propose(base + 5)
+                self.score(1, log_u[1])
+                self.select(1)
+        self.loglik()
+        self.n_sweeps += 1
+
+    def stats(self) -> dict:
+        """Synchronises; refreshes the host copies of epsilon."""
+        torch.cuda.current_stream().synchronize()
+        eps = self.eps.cpu().numpy()
+        for im, e in zip(self.images, eps):
+            check(self.L.cg_image_sync_epsilon(im._h, stream_ptr(), None))
+            im.epsilon = float(e)
+        delta = [d.cpu().numpy() for d in self.delta]
+        if any(np.isnan(d).any() for d in delta) or np.isnan(self.ll.cpu().numpy()).any():
+            last_eval_count()                 # raises with the device's error message when it set one
+            raise RuntimeError("a device error poisoned the sweep results")
+        return dict(loglik=self.ll.cpu().numpy(), epsilon=eps, noise=self.noise.cpu().numpy(),
+                    accepted=self.n_acc.cpu().numpy(), guard=self.n_guard.cpu().numpy())
+
+    def sources(self) -> np.ndarray:
+        return self.d_cur.cpu().numpy().view(SRC_DTYPE).copy()
+
+    def states(self) -> np.ndarray:
+        return self.d_states.cpu().numpy().view(SRC_DTYPE).reshape(self.n_src, self.P + 1).copy()
+
+    def boxes(self) -> np.ndarray:
+        return self.d_boxes.cpu().numpy().view(BOX_DTYPE)[:self.n_items].reshape(self.n_src, self.n_img).copy()

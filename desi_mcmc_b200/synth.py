@@ -123,3 +123,45 @@ def make_proposals(seed, cur, P):
 def image_kwargs(meta):
     return {k: meta[k] for k in ("band", "calib", "gain", "sky", "rho_n", "phi_n", "Ups_n",
                                  "psf_weights", "psf_means", "psf_covars")}
+
+
+def make_eigen_basis(seed=1004, K=4, V=1364):
+    """A17 inputs of the shape of the reference's cache/basis_locked/*K-4_V-1364* fits: a positive
+    rest-frame basis B (K, V) with rows normalised to 1 (quasar_infer_photometry.py:223-224) on a
+    log-spaced wavelength grid lam0 (Angstrom)."""
+    rng = np.random.RandomState(seed)
+    lam0 = np.exp(np.linspace(np.log(700.), np.log(9000.), V))
+    B = np.zeros((K, V))
+    for k in range(K):
+        cont = (lam0 / 2500.) ** rng.uniform(-2., 0.)
+        lines = sum(a * np.exp(-.5 * ((lam0 - c) / w) ** 2)
+                    for a, c, w in zip(rng.uniform(0., 3., 4), rng.uniform(1000., 7000., 4), rng.uniform(20., 200., 4)))
+        B[k] = cont + lines
+    B = B / B.sum(axis=1, keepdims=True)
+    return B, lam0
+
+
+def make_crowded_field(seed=1004, H=1489, W=2048, n_src=5000, star_frac=.1, eigen_frac=.05, K=4):
+    """C4: a galaxy-heavy crowded field.  10 % stars whose fluxes come from the black-body route
+    (T ~ U(3000, 10000) K, planck.py), 5 % point sources whose fluxes come from the eigen-spectrum
+    route (redshift z, simplex weights w, scale m), the rest galaxies with free fluxes.
+    -> dict(seed, images, sources); eigen sources carry s["eigen"] = dict(z, w, m, row)."""
+    rng = np.random.RandomState(seed)
+    metas = [make_image_meta(rng, b, H, W) for b in BANDS]
+    srcs, row = [], 0
+    for _ in range(n_src):
+        r = rng.uniform()
+        if r < star_frac:
+            s = make_source(rng, metas[2], True, planck=True)
+        elif r < star_frac + eigen_frac:
+            s = make_source(rng, metas[2], True)
+            z = rng.uniform(.3, 4.)
+            w = np.exp(rng.normal(size=K))
+            s["eigen"] = dict(z=z, w=w / w.sum(), m=float(np.exp(rng.normal(np.log(5000.), .5)) * (1. + z)), row=row)
+            s["fluxes"] = None                        # a function of (z, w, m): filled by the consumer
+            row += 1
+        else:
+            s = make_source(rng, metas[2], False)
+        s.setdefault("eigen", None)
+        srcs.append(s)
+    return dict(seed=seed, images=metas, sources=srcs, n_eigen=row)

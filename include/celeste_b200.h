@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define CG_ABI_VERSION 1
+#define CG_ABI_VERSION 2
 
 #define CG_MAX_PSF 4      /* PSF mixture components per image (reference: 3, fits_image.py:130-133) */
 #define CG_NUM_BANDS 5    /* u g r i z */
@@ -81,9 +81,14 @@ typedef struct CgSource {
   double rho;          /* axis ratio                                      */
   double t;            /* star temperature (K), used with CG_SRC_PLANCK   */
   double b;            /* star brightness ell/d^2, used with CG_SRC_PLANCK*/
+  int64_t flux_row;    /* row of the bound flux table, used with CG_SRC_EIGEN */
 } CgSource;
 
 #define CG_SRC_PLANCK 1   /* star flux from black-body route (celeste.py:38-40, planck.py:155) */
+#define CG_SRC_EIGEN 2    /* band fluxes (nanomaggies) = row flux_row of the table bound with cg_set_flux_table:
+                             the eigen-spectrum route, experiments/redshift/redshift_utils.py:304-323 and
+                             quasar_infer_photometry.py:31-46 (mu = project_to_bands(w.B, lam0 (1+z)) m / (1+z)),
+                             evaluated by cg_eigen_fluxes into a DEVICE table -- no host hop per band */
 
 /* One unit of render work: a (source, image) pair. */
 typedef struct CgItem {
@@ -125,6 +130,13 @@ double cg_image_radius(const CgImage* img);                /* FitsImage.R */
  * wavelengths (m, sorted) and h_vec = S*lambda/(hc)*dLambda, concatenated. */
 int cg_set_filter_curves(const double* h_wavelengths, const double* h_hvecs,
                          const double* h_sens, const int32_t* h_counts /* [5] */);
+
+/* Binds a device table of band fluxes [n_rows][5] (float64 nanomaggies, e.g. the d_mu output of
+ * cg_eigen_fluxes) for sources flagged CG_SRC_EIGEN.  The pointer is read when a call is
+ * ENQUEUED and travels in that call's kernel arguments; the table contents are read when the
+ * kernels run, so an eigen_flux launch earlier on the same stream feeds the render directly.
+ * d_flux = NULL unbinds.  A flagged source whose row is out of range poisons the results (NaN). */
+int cg_set_flux_table(const double* d_flux, int64_t n_rows);
 
 /* ---- A2: util/like/gmm_like_fast.pyx:130-176 ---------------------------- */
 /* probs[n] = sum_k ws[k] N(x[n]; mus[k], sigs[k]).  All device pointers,
@@ -277,6 +289,81 @@ int cg_sample_source_counts(CgImage* const* imgs, int32_t n_img, int32_t n_src,
                             void* d_workspace, size_t workspace_bytes, void* stream);
 /* sample_binomial (:161-166): count draws of binomial(n, p) -> d_out (float64). */
 int cg_binomial_draws(int64_t n, double p, uint64_t seed, int64_t count, double* d_out, void* stream);
+
+/* ---- device-resident Gibbs sweep over a crowded field (BASELINE config 4) --- */
+/* The per-sweep steps of CelesteBase.resample_model (models.py:75-83) for ALL sources of a field
+ * with no host hop: every array below is a device array owned by the caller.  Items are the cross
+ * product item = src * n_img + img; box-shaped per-item patches are row-major with stride
+ * max_patch_px.  Workspaces: cg_sweep_workspace_bytes(kind, ...), n_tiles as for CG_WS_FIELD. */
+#define CG_WS_SWEEP_ALLOC 4
+#define CG_WS_SWEEP_SCORE 5
+#define CG_WS_SWEEP_BACKGROUND 6
+size_t cg_sweep_workspace_bytes(int32_t kind, int32_t n_src, int32_t n_img, int32_t P, int64_t max_patch_px,
+                                int64_t n_tiles);
+
+/* Field.resample_photons (models.py:123-160) = sample_source_photons_single_image_cython
+ * (celeste_mcmc.py:98-150) + sample_source_counts (celeste_sample_sources.pyx:61-156) for the n_img
+ * images of a field in ONE pass over the 16 x 16 image bins: each bin's sources are rendered into
+ * registers and the pixel's photons split over them and the sky by conditional binomials -- there
+ * is no rate-patch buffer.  Outputs: d_samp [n_items][max_patch_px] photons per source (every pixel
+ * of a box is written), d_boxes [n_items] the boxes (footprints, radius capped by bound_cap),
+ * d_noise_sum [n_img] sky photons, d_counts [n_items] = sum(d_samp[item]) and d_unit_sums [n_items] =
+ * sum of the unit-flux patch over the box (the two statistics Source.resample_fluxes needs,
+ * sources.py:340-342; either may be NULL).  Random numbers as cg_sample_source_counts. */
+int cg_field_sample_photons(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs, int32_t n_src,
+                            double bound_cap, int64_t max_patch_px, uint64_t seed, float* d_samp,
+                            CgBox* d_boxes, double* d_noise_sum, double* d_counts, double* d_unit_sums,
+                            void* d_workspace, size_t workspace_bytes, void* stream);
+
+/* Source.resample_fluxes (sources.py:327-350) for every source: flux[band] ~ Gamma(a0 + sum of its
+ * photons in the band, 1 / (b0 + sum_psf * kappa / calib)), written into d_srcs in place.  Sources
+ * whose fluxes are functions of other parameters (CG_SRC_PLANCK stars, CG_SRC_EIGEN) are skipped.
+ * Philox + Marsaglia-Tsang on the device: distributional parity with numpy.random.gamma. */
+int cg_resample_fluxes(CgImage* const* imgs, int32_t n_img, CgSource* d_srcs, int32_t n_src,
+                       const double* d_counts, const double* d_unit_sums, double a0, double b0, uint64_t seed,
+                       void* stream);
+/* models.py:156-160: epsilon_img ~ Gamma(a0 + noise_sum, 1 / (b0 + H W)), written into the image
+ * descriptor ON THE DEVICE (d_eps_out [n_img] optional); cg_image_sync_epsilon refreshes the host
+ * copy (synchronises the stream). */
+int cg_resample_epsilon(CgImage* const* imgs, int32_t n_img, const double* d_noise_sum, double a0, double b0,
+                        uint64_t seed, double* d_eps_out, void* stream);
+int cg_image_sync_epsilon(CgImage* img, void* stream, double* h_epsilon);
+
+/* P Gaussian perturbations of every source's state: d_states [n_src][P + 1], entry 0 = the current
+ * state.  h_scales[6] = standard deviations of u (degrees), relative flux, theta, rho, phi
+ * (degrees), relative sigma.  (No reference analogue: the reference draws one proposal at a time
+ * on the host, experiments/rjump/test_rjmcmc.py.) */
+int cg_make_proposals(const CgSource* d_cur, int32_t n_src, int32_t P, const double* h_scales, uint64_t seed,
+                      CgSource* d_states, void* stream);
+
+/* A13 / A15 for EVERY source of a field in one call: for source s and proposal p
+ *   delta[s*P + p-1] = sum_img ll(states[s][p]) - sum_img ll(states[s][0]) + d_log_terms[s*P + p-1]
+ *   accept = d_log_u < delta
+ * over the boxes d_boxes[s * n_img + img], with
+ *   mode CG_LL_POISSON_BG   ll = poisson_loglike(nelec crop, d_aux patch + rate, mask)  (sources.py:275-306;
+ *                           d_aux = cached background patches, NULL = epsilon)
+ *   mode CG_LL_CONDITIONAL  ll = Source.log_likelihood given the photon patches d_aux (sources.py:134-183).
+ * Proposals within `guard` of their log-uniform are re-scored in float64 (list of
+ * cg_sweep_guard_cap(n_src, P) entries; overflow poisons d_delta with NaN). */
+int32_t cg_sweep_guard_cap(int32_t n_src, int32_t P);
+int cg_score_proposals_multi(CgImage* const* imgs, int32_t n_img, const CgSource* d_states, int32_t n_src,
+                             int32_t P, const CgBox* d_boxes, int32_t mode, const float* d_aux,
+                             int64_t max_patch_px, const double* d_log_terms, const double* d_log_u,
+                             double guard, double* d_delta, uint8_t* d_accept, int32_t* d_n_guard,
+                             void* d_workspace, size_t workspace_bytes, void* stream);
+/* The accept test of sources.py:258 applied in order: source s moves to its first accepted proposal
+ * (exactly that many sequential MH steps: all P were drawn around the current state). */
+int cg_select_proposals(const CgSource* d_states, int32_t n_src, int32_t P, const uint8_t* d_accept,
+                        CgSource* d_cur, int32_t* d_n_accepted, void* stream);
+
+/* generate_background_patch (sources.py:476-483) for every (source, image): epsilon + the model
+ * patches of the active neighbours of (source, image) (CSR lists d_nbr_off [n_src * n_img + 1], d_nbr_idx
+ * of SOURCE indices; the intersection test of sources.py:457-472 is the caller's) rendered on the source's cached box
+ * d_boxes[s * n_img + img] (sides <= max_box_side) -> d_bg [n_items][max_patch_px]. */
+int cg_background_patches(CgImage* const* imgs, int32_t n_img, const CgSource* d_srcs, int32_t n_src,
+                          const CgBox* d_boxes, const int32_t* d_nbr_off, const int32_t* d_nbr_idx,
+                          int64_t max_patch_px, int32_t max_box_side, float* d_bg,
+                          void* d_workspace, size_t workspace_bytes, void* stream);
 
 /* ---- A16: planck.py:94-158 ----------------------------------------------- */
 /* out[i*5+band] = photons_expected_brightness(T[i], b[i], band); float64. */

@@ -36,7 +36,7 @@ def test_every_declared_symbol_is_exported(lib):
 def test_struct_layouts_match_header(lib):
     from desi_mcmc_b200 import _ffi
     assert C.sizeof(_ffi.CgImageDesc) == 312
-    assert _ffi.SRC_DTYPE.itemsize == 112 and _ffi.SRC_DTYPE.fields["u"][1] == 8
+    assert _ffi.SRC_DTYPE.itemsize == 120 and _ffi.SRC_DTYPE.fields["u"][1] == 8
     assert _ffi.ITEM_DTYPE.itemsize == 32 and _ffi.BOX_DTYPE.itemsize == 16
 
 
