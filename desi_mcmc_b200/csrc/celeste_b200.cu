@@ -1895,7 +1895,7 @@ __global__ void __launch_bounds__(128) mog_logpdf_kernel(const double* x, long l
 
 // one block per output entry e of [K | K*D | K*D(D+1)/2]: fixed-shape tree over the points
 __global__ void __launch_bounds__(256) prior_stats_kernel(const double* resp, const double* c, long long N,
-                                                          int K, int D, double* out) {
+                                                          int K, int D, double* out, const int* mask = nullptr) {
   const int T = D * (D + 1) / 2;
   const int e = blockIdx.x;
   int k, a = -1, b = -1;
@@ -1913,6 +1913,7 @@ __global__ void __launch_bounds__(256) prior_stats_kernel(const double* resp, co
   }
   double s = 0.0;
   for (long long n = threadIdx.x; n < N; n += 256) {
+    if (mask && !mask[n]) continue;
     double v = resp[n * K + k];
     if (a >= 0) v *= c[n * D + a];
     if (b >= 0) v *= c[n * D + b];

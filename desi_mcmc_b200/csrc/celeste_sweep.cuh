@@ -455,6 +455,62 @@ __global__ void __launch_bounds__(256, 2) bg_tile_kernel(BgArgs A) {
   if (lane == 0 && issued) atomicAdd(&a.cnt->issued, issued);
 }
 
+// ---------------------------------------------------------------------------
+// per-sweep statistics a rank contributes to the all-reduce
+// ---------------------------------------------------------------------------
+// colour-space coordinates of the sources of one type (FluxColorMoG, util/dists/flux_prior.py:4-40:
+// [lu - lr, lg - lr, li - lr, lz - lr, lr] of the log fluxes); mask = 0 for the others
+__global__ void flux_colors_kernel(const CgSource* srcs, long long n, int type, double* colors, int* mask) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const CgSource& s = srcs[i];
+  bool ok = (s.type == type);
+  double l[CG_NUM_BANDS];
+#pragma unroll
+  for (int b = 0; b < CG_NUM_BANDS; ++b) {
+    ok = ok && (s.flux[b] > 0.);
+    l[b] = ok ? log(s.flux[b]) : 0.;
+  }
+  mask[i] = ok ? 1 : 0;
+  double* c = colors + i * CG_NUM_BANDS;
+  c[0] = ok ? l[0] - l[2] : 0.;
+  c[1] = ok ? l[1] - l[2] : 0.;
+  c[2] = ok ? l[3] - l[2] : 0.;
+  c[3] = ok ? l[4] - l[2] : 0.;
+  c[4] = ok ? l[2] : 0.;
+}
+
+// dist.SweepStats layout: [0] sum of the per-image log-likelihoods (fixed order), [1:6] sky photons per
+// band, [6] stars, [7] galaxies, then the two prior blocks
+__global__ void sweep_stats_kernel(const double* ll, int n_ll, const double* noise, const int* img_band, int n_noise,
+                                   const CgSource* srcs, long long n_src, const double* prior0,
+                                   const double* prior1, int block, double* vec) {
+  __shared__ int s_cnt[2];
+  if (threadIdx.x < 2) s_cnt[threadIdx.x] = 0;
+  __syncthreads();
+  int c0 = 0, c1 = 0;
+  for (long long i = threadIdx.x; i < n_src; i += blockDim.x) {
+    c0 += srcs[i].type == 0;
+    c1 += srcs[i].type == 1;
+  }
+  atomicAdd(&s_cnt[0], c0);
+  atomicAdd(&s_cnt[1], c1);
+  for (int i = threadIdx.x; i < block; i += blockDim.x) {
+    vec[8 + i] = prior0 ? prior0[i] : 0.;
+    vec[8 + block + i] = prior1 ? prior1[i] : 0.;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0;
+    for (int i = 0; i < n_ll; ++i) t += ll[i];
+    vec[0] = t;
+    for (int b = 0; b < CG_NUM_BANDS; ++b) vec[1 + b] = 0.;
+    for (int i = 0; i < n_noise; ++i) vec[1 + img_band[i]] += noise[i];
+    vec[6] = (double)s_cnt[0];
+    vec[7] = (double)s_cnt[1];
+  }
+}
+
 // ===========================================================================
 // host side
 // ===========================================================================
@@ -730,6 +786,50 @@ int cg_background_patches(CgImage* const* imgs, int32_t n_img, const CgSource* d
   bg_tile_kernel<<<g_sm_count * per_sm, 256, 0, st>>>(B);
   LAUNCH_CHECK();
   g_last_counters = cnt;
+  return CG_OK;
+}
+
+int cg_flux_prior_stats(const CgSource* d_srcs, int64_t n_src, int32_t src_type, const double* d_means,
+                        const double* d_icovs, const double* d_dets, const double* d_pis, int32_t K,
+                        void* d_scratch, size_t scratch_bytes, double* d_logp, double* d_out, void* stream) {
+  NEED_INIT();
+  cudaStream_t st = (cudaStream_t)stream;
+  const int D = CG_NUM_BANDS;
+  if (n_src < 0 || K < 1) return fail(CG_EINVAL, "cg_flux_prior_stats: need n_src >= 0, K >= 1");
+  const size_t need = align_up(sizeof(double) * n_src * D, 256) + align_up(sizeof(double) * n_src * K, 256) +
+                      align_up(sizeof(double) * n_src, 256) + align_up(sizeof(int) * n_src, 256);
+  if (need > scratch_bytes) return fail(CG_ENOMEM, "scratch too small: need %zu bytes, have %zu", need, scratch_bytes);
+  char* base = (char*)d_scratch;
+  double* colors = (double*)base;
+  double* resp = (double*)(base + align_up(sizeof(double) * n_src * D, 256));
+  double* logp = (double*)((char*)resp + align_up(sizeof(double) * n_src * K, 256));
+  int* mask = (int*)((char*)logp + align_up(sizeof(double) * n_src, 256));
+  const int entries = K * (1 + D + D * (D + 1) / 2);
+  if (n_src == 0) { CUDA_TRY(cudaMemsetAsync(d_out, 0, sizeof(double) * entries, st)); return CG_OK; }
+  flux_colors_kernel<<<(unsigned)((n_src + 255) / 256), 256, 0, st>>>(d_srcs, n_src, src_type, colors, mask);
+  LAUNCH_CHECK();
+  mog_logpdf_kernel<<<(unsigned)((n_src + 3) / 4), 128, 0, st>>>(colors, n_src, D, d_means, d_icovs, d_dets, d_pis, K,
+                                                                 d_logp ? d_logp : logp, resp);
+  LAUNCH_CHECK();
+  prior_stats_kernel<<<entries, 256, 0, st>>>(resp, colors, n_src, K, D, d_out, mask);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
+size_t cg_flux_prior_scratch_bytes(int64_t n_src, int32_t K) {
+  return align_up(sizeof(double) * n_src * CG_NUM_BANDS, 256) + align_up(sizeof(double) * n_src * K, 256) +
+         align_up(sizeof(double) * n_src, 256) + align_up(sizeof(int) * n_src, 256) + 256;
+}
+
+int cg_sweep_stats(const double* d_ll, int32_t n_ll, const double* d_noise, const int32_t* d_img_band,
+                   int32_t n_noise, const CgSource* d_srcs, int64_t n_src, const double* d_prior0,
+                   const double* d_prior1, int32_t block, double* d_vec, void* stream) {
+  NEED_INIT();
+  if (!d_ll || !d_vec || n_ll < 0 || block < 0) return fail(CG_EINVAL, "bad argument");
+  if (n_noise > 0 && (!d_noise || !d_img_band)) return fail(CG_EINVAL, "noise sums need the image bands");
+  sweep_stats_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(d_ll, n_ll, d_noise, d_img_band, n_noise, d_srcs, n_src,
+                                                         d_prior0, d_prior1, block, d_vec);
+  LAUNCH_CHECK();
   return CG_OK;
 }
 

@@ -602,7 +602,11 @@ class FieldSet(object):
     through a pinned stage -- the per-step host->device traffic)."""
 
     def __init__(self, image_lists: Sequence[Sequence[Image]], n_src_max: Sequence[int],
-                 bound_cap: float = 0.0, max_patch_px: int | None = None):
+                 bound_cap: float = 0.0, max_patch_px: int | None = None, d_srcs: torch.Tensor | None = None,
+                 h_srcs: torch.Tensor | None = None, ll: torch.Tensor | None = None):
+        """d_srcs / h_srcs / ll: optional views into rank-level buffers (device source bytes, pinned
+        source bytes, device log-likelihoods) so that several sets share one contiguous source array
+        and one log-likelihood vector (engine.SweepPayload reads them as a whole)."""
         self.L = lib()
         self.fields = [list(imgs) for imgs in image_lists]
         F = len(self.fields)
@@ -626,10 +630,14 @@ class FieldSet(object):
                                              self.max_patch_px, tiles))
         self.ws = torch.empty(need, dtype=torch.uint8, device=device())
         nb = int(self.cap_off[-1]) * SRC_DTYPE.itemsize
-        self.d_srcs = torch.zeros(max(nb, 1), dtype=torch.uint8, device=device())
-        self.h_srcs = torch.zeros(max(nb, 1), dtype=torch.uint8).pin_memory()
+        self.d_srcs = d_srcs if d_srcs is not None else torch.zeros(max(nb, 1), dtype=torch.uint8, device=device())
+        self.h_srcs = h_srcs if h_srcs is not None else torch.zeros(max(nb, 1), dtype=torch.uint8).pin_memory()
+        if self.d_srcs.numel() < nb or self.h_srcs.numel() < nb:
+            raise ValueError("source buffers too small for n_src_max")
         self.h_np = self.h_srcs.numpy()
-        self.ll = torch.zeros(self.n_img, dtype=torch.float64, device=device())
+        self.ll = ll if ll is not None else torch.zeros(self.n_img, dtype=torch.float64, device=device())
+        if self.ll.numel() != self.n_img:
+            raise ValueError("ll must have one entry per image")
         self.h_ll = torch.zeros(self.n_img, dtype=torch.float64).pin_memory()
         self.src_off = np.zeros(F + 1, dtype=np.int32)
 
@@ -682,6 +690,9 @@ class FieldSet(object):
         self.loglik_device()
         self.h_ll.copy_(self.ll, non_blocking=True)
         torch.cuda.current_stream().synchronize()
+        if np.isnan(self.h_ll.numpy()).any():      # a device-side error poisons the results (field_tile_final_kernel)
+            last_eval_count()
+            raise RuntimeError("the field log-likelihood is NaN")
         return self.h_ll.numpy()
 
 
@@ -697,7 +708,8 @@ class FieldSweep(object):
     into the captured launches: call ``capture()`` again after ``set_sources``
     changed a count (parameter VALUES may change freely)."""
 
-    def __init__(self, sets: Sequence["FieldSet"], n_streams: int = 2, after=None, io: bool = False):
+    def __init__(self, sets: Sequence["FieldSet"], n_streams: int = 2, after=None, io: bool = False,
+                 parallel=None):
         """after: optional callable enqueued on the current stream after the sets
         of a step (e.g. the all-reduce of the sweep statistics); it is captured
         into the graph with them.  io=True makes the step self-contained end to
@@ -706,6 +718,8 @@ class FieldSweep(object):
         h_ll, so that a replay is ONE driver call including the transfers."""
         self.sets = list(sets)
         self.after = after
+        self.parallel = parallel       # callable enqueued on a forked stream beside the field kernels
+        self._par_stream = torch.cuda.Stream(device=device()) if parallel is not None else None
         self.io = bool(io)
         self.n_streams = max(1, min(int(n_streams), len(self.sets)))
         self._side = [torch.cuda.Stream(device=device()) for _ in range(self.n_streams)] \
@@ -723,20 +737,24 @@ class FieldSweep(object):
                 fs.h_ll.copy_(fs.ll, non_blocking=True)
 
     def _enqueue_compute(self):
+        cur = torch.cuda.current_stream()
+        if self.parallel is not None:          # small independent work (prior statistics) in the shadow
+            self._par_stream.wait_stream(cur)  # of the latency-bound set-up kernels of the field path
+            with torch.cuda.stream(self._par_stream):
+                self.parallel()
         if not self._side:
             for fs in self.sets:
                 fs.loglik_device()
-            if self.after is not None:
-                self.after()
-            return
-        cur = torch.cuda.current_stream()
-        for s in self._side:
-            s.wait_stream(cur)
-        for i, fs in enumerate(self.sets):
-            with torch.cuda.stream(self._side[i % len(self._side)]):
-                fs.loglik_device()
-        for s in self._side:
-            cur.wait_stream(s)
+        else:
+            for s in self._side:
+                s.wait_stream(cur)
+            for i, fs in enumerate(self.sets):
+                with torch.cuda.stream(self._side[i % len(self._side)]):
+                    fs.loglik_device()
+            for s in self._side:
+                cur.wait_stream(s)
+        if self.parallel is not None:
+            cur.wait_stream(self._par_stream)
         if self.after is not None:
             self.after()
 
@@ -1235,3 +1253,54 @@ class GibbsSweep(object):
 
     def boxes(self) -> np.ndarray:
         return self.d_boxes.cpu().numpy().view(BOX_DTYPE)[:self.n_items].reshape(self.n_src, self.n_img).copy()
+
+
+class SweepPayload(object):
+    """What a rank contributes to the per-sweep all-reduce (dist.SweepStats layout), computed on the
+    device from its resident sources and written straight into the collective's send buffer:
+    sum of the per-image log-likelihoods, sky photons per band, star / galaxy counts and the
+    sufficient statistics of the star and galaxy colour priors (cg_flux_prior_stats), SURVEY.md 8e."""
+
+    def __init__(self, d_srcs: torch.Tensor, n_src: int, ll: torch.Tensor, star_prior, gal_prior,
+                 noise: torch.Tensor | None = None, img_bands=None, n_buffers: int = 2):
+        """star_prior / gal_prior: (means [K,5], covs [K,5,5], pis [K]) host arrays."""
+        self.L = lib()
+        dev = device()
+        self.d_srcs, self.n_src, self.ll = d_srcs, int(n_src), ll
+        self.priors = []
+        for means, covs, pis in (star_prior, gal_prior):
+            means = np.ascontiguousarray(means, dtype=np.float64)
+            covs = np.ascontiguousarray(covs, dtype=np.float64)
+            K = means.shape[0]
+            d = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(dev)
+            self.priors.append(dict(K=K, means=d(means), icovs=d(np.linalg.inv(covs)), dets=d(np.linalg.det(covs)),
+                                    pis=d(pis)))
+        self.K = self.priors[0]["K"]
+        if self.priors[1]["K"] != self.K:
+            raise ValueError("both priors must have the same number of components")
+        self.block = self.K * (1 + 5 + 15)
+        self.size = 8 + 2 * self.block
+        self.blocks = [torch.zeros(self.block, dtype=torch.float64, device=dev) for _ in range(2)]
+        nb = int(self.L.cg_flux_prior_scratch_bytes(self.n_src, self.K))
+        self.scratch = [torch.empty(nb, dtype=torch.uint8, device=dev) for _ in range(2)]
+        self.vec = [torch.zeros(self.size, dtype=torch.float64, device=dev) for _ in range(n_buffers)]
+        self.noise = noise
+        self.d_bands = None
+        if noise is not None:
+            self.d_bands = torch.from_numpy(np.ascontiguousarray(img_bands, dtype=np.int32)).to(dev)
+
+    def prior_stats(self):
+        """two launches of three small kernels each; independent of the field kernels"""
+        for t, (pr, blk, scr) in enumerate(zip(self.priors, self.blocks, self.scratch)):
+            check(self.L.cg_flux_prior_stats(self.d_srcs.data_ptr(), self.n_src, t, pr["means"].data_ptr(),
+                                             pr["icovs"].data_ptr(), pr["dets"].data_ptr(), pr["pis"].data_ptr(),
+                                             pr["K"], scr.data_ptr(), scr.numel(), None, blk.data_ptr(), stream_ptr()))
+
+    def pack(self, k: int = 0) -> torch.Tensor:
+        check(self.L.cg_sweep_stats(self.ll.data_ptr(), self.ll.numel(),
+                                    self.noise.data_ptr() if self.noise is not None else None,
+                                    self.d_bands.data_ptr() if self.d_bands is not None else None,
+                                    self.noise.numel() if self.noise is not None else 0,
+                                    self.d_srcs.data_ptr(), self.n_src, self.blocks[0].data_ptr(),
+                                    self.blocks[1].data_ptr(), self.block, self.vec[k].data_ptr(), stream_ptr()))
+        return self.vec[k]

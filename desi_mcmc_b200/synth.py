@@ -165,3 +165,33 @@ def make_crowded_field(seed=1004, H=1489, W=2048, n_src=5000, star_frac=.1, eige
         s.setdefault("eigen", None)
         srcs.append(s)
     return dict(seed=seed, images=metas, sources=srcs, n_eigen=row)
+
+
+def instantiate_crowded(engine, field, B, lam0, bound_cap=25., simulate_seed=None, **sweep_kw):
+    """Device objects of a make_crowded_field dict: images (pixels drawn ON THE DEVICE as
+    Poisson(model image of the field) when simulate_seed is given, else zeros), packed sources,
+    the eigen-spectrum state and the engine.GibbsSweep over them."""
+    import torch
+    dev = engine.device()
+    H, W = field["images"][0]["shape"]
+    imgs = [engine.Image(nelec=torch.zeros((H, W), dtype=torch.float32, device=dev), **image_kwargs(m))
+            for m in field["images"]]
+    srcs = [engine.SrcParams(u=s["u"], a=s["a"], b=s["b"], t=s["t"], theta=s["theta"], phi=s["phi"],
+                             sigma=s["sigma"], rho=s["rho"], fluxes=s["fluxes"],
+                             flux_row=s["eigen"]["row"] if s.get("eigen") else None) for s in field["sources"]]
+    packed = engine.pack_sources(srcs)
+    es = [s["eigen"] for s in field["sources"] if s.get("eigen")]
+    eig = None
+    if es:
+        eig = engine.EigenSpectra([e["z"] for e in es], [e["w"] for e in es], [e["m"] for e in es], B, lam0)
+        eig.project()
+    side = int(2 * bound_cap + 3)
+    if simulate_seed is not None:
+        _, models = engine.field_loglik(imgs, packed, bound_cap=bound_cap, max_patch_px=side * side,
+                                        return_model=True)
+        gen = torch.Generator(device=dev)
+        gen.manual_seed(int(simulate_seed))
+        for im, lam in zip(imgs, models):
+            im.set_nelec(torch.poisson(lam, generator=gen))
+    sweep = engine.GibbsSweep(imgs, packed, bound_cap=bound_cap, eigen=eig, **sweep_kw)
+    return imgs, packed, eig, sweep

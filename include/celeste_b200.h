@@ -399,6 +399,25 @@ int cg_mog_logpdf(const double* d_x, int64_t N, int32_t D,
 int cg_prior_stats(const double* d_resp, const double* d_c, int64_t N, int32_t K, int32_t D,
                    double* d_out, void* stream);
 
+/* ---- per-sweep statistics for the all-reduce ------------------ */
+/* Sufficient statistics of the empirical colour prior over the sources of one type, straight from
+ * the device source array: colours = FluxColorMoG.to_colors(log fluxes) (util/dists/flux_prior.py:4-40),
+ * responsibilities under the K-component mixture (cg_mog_logpdf), then the cg_prior_stats vector
+ * d_out [K (1 + 5 + 15)] -- the M-step inputs of experiments/empirical_priors/make_source_priors.py:76-110.
+ * d_logp [n_src] optional.  Scratch: cg_flux_prior_scratch_bytes(n_src, K). */
+size_t cg_flux_prior_scratch_bytes(int64_t n_src, int32_t K);
+int cg_flux_prior_stats(const CgSource* d_srcs, int64_t n_src, int32_t src_type, const double* d_means,
+                        const double* d_icovs, const double* d_dets, const double* d_pis, int32_t K,
+                        void* d_scratch, size_t scratch_bytes, double* d_logp, double* d_out, void* stream);
+/* Packs the vector a rank contributes to the per-sweep all-reduce:
+ *   [0] sum of d_ll[n_ll] (fixed order)  [1:6] sky photons per band (d_noise[i] belongs to band d_img_band[i])
+ *   [6] stars  [7] galaxies  [8 : 8 + block] d_prior0  [8 + block : 8 + 2 block] d_prior1
+ * written directly into the collective's send buffer d_vec (8 + 2 block doubles): one launch, no
+ * host hop (models.py:75-79 loops the fields; the global quantities are sums over ranks). */
+int cg_sweep_stats(const double* d_ll, int32_t n_ll, const double* d_noise, const int32_t* d_img_band,
+                   int32_t n_noise, const CgSource* d_srcs, int64_t n_src, const double* d_prior0,
+                   const double* d_prior1, int32_t block, double* d_vec, void* stream);
+
 /* ---- instrumentation ------------------------------------------------------ */
 /* Number of kernels launched by this library since cg_init (or last reset). */
 int64_t cg_launch_count(int reset);

@@ -137,3 +137,123 @@ def test_c3_full_batch_properties(engine, oracle):
     want = np.array([oracle.calculate_acceptance_logprob(ocur, p, oimgs, ob, bgs) for p in oprops])
     assert np.array_equal(accept[sub].astype(bool), log_u[sub] < want)
     assert np.max(np.abs(delta[sub] - want)) < 5e-3
+
+
+def test_c4_crowded_field_full_size(engine, oracle):
+    """Config 4 at BASELINE's size: 5000 sources (10 % black-body stars, 5 % eigen-spectrum point
+    sources, galaxies) with footprints forced to ~50 x 50 on a 2048 x 1489 x 5 field, one full Gibbs
+    sweep with 16 proposals per source on the device.  Whole field: every photon of every band is
+    conserved by the allocation, the sweep is finite and its reported log-likelihood is the field
+    likelihood of the state it ends in.  A 200-source subsample against the oracle: footprints bit
+    for bit, rendered rates <= 1e-5 (r band), conditional proposal scores <= 1e-6 of the source's
+    log-likelihood with identical accept / reject; 12 sources x 2 proposals of the full MH ratio
+    (backgrounds from ~16 active neighbours each) likewise."""
+    import os
+    import torch
+    from desi_mcmc_b200 import _ffi
+    from tests.test_gpu_crowded import _capped_box, _capped_patch, _oracle_fluxes
+    oracle.set_filter_tables_npz(os.path.join(_ffi.PKG, "data", "filter_curves.npz"))
+    H, W, S, P = 1489, 2048, 5000, 16
+    field = synth.make_crowded_field(1004, H=H, W=W, n_src=S)
+    B, lam0 = synth.make_eigen_basis(1004)
+    imgs, packed, eig, sw = synth.instantiate_crowded(engine, field, B, lam0, simulate_seed=1004,
+                                                      proposals=P, seed=1004)
+    n_star = sum(1 for s in field["sources"] if s["a"] == 0 and s["t"])
+    assert 400 < n_star < 600 and 200 < field["n_eigen"] < 300
+    n_img = 5
+    nelec_tot = np.array([float(torch.floor(im.nelec.double()).sum().item()) for im in imgs])
+
+    # ---- the sweep, phase by phase, so the intermediate state can be checked ---------------
+    eig.project()
+    sw.allocate(seed=1)
+    counts = sw.counts.cpu().numpy().reshape(S, n_img)
+    assert np.array_equal(sw.noise.cpu().numpy() + counts.sum(0), nelec_tot)          # photon conservation
+    boxes = sw.boxes()
+    sw.resample_epsilon(seed=2)
+    sw.resample_fluxes(seed=3)
+    sw.propose(seed=4)
+    states = sw.states()
+    rng = np.random.RandomState(1004)
+    log_u = np.log(rng.uniform(size=S * P))
+    sw.score(0, log_u)
+    delta = sw.delta[0].cpu().numpy().reshape(S, P)
+    acc = sw.accept[0].cpu().numpy().reshape(S, P).astype(bool)
+    assert np.all(np.isfinite(delta))
+    assert np.array_equal(acc, log_u.reshape(S, P) < delta) or int(sw.n_guard.cpu().numpy()[0]) > 0
+
+    metas = field["images"]
+    oimgs = [oracle.SyntheticImage(nelec=im.nelec.cpu().numpy().astype(np.float64), **synth.image_kwargs(m))
+             for im, m in zip(imgs, metas)]
+
+    def oracle_src(rec, k):
+        s = field["sources"][k]
+        fixed = bool(s.get("eigen")) or (s["a"] == 0 and bool(s["t"]))
+        f = _oracle_fluxes(oracle, s, metas, B, lam0) if fixed else rec["flux"].copy()
+        return oracle.SrcParams(u=rec["u"].copy(), a=int(rec["type"]), theta=float(rec["theta"]),
+                                phi=float(rec["phi"]), sigma=float(rec["sigma"]), rho=float(rec["rho"]), fluxes=f)
+
+    sub = np.random.RandomState(7).choice(S, 200, replace=False)
+    rate_items = engine.make_items(sub, [2] * sub.size)
+    patches, pboxes = engine.render_patches(imgs, states[:, 0].copy(), items=rate_items, bound_cap=25.,
+                                            max_patch_px=sw.max_patch_px)
+    samp_rows = torch.from_numpy(np.concatenate([k * n_img + np.arange(n_img) for k in sub])).to(engine.device())
+    samp = sw.samp[samp_rows].cpu().numpy().reshape(sub.size, n_img, -1)
+    worst_rate, worst_ll, n_dec = 0., 0., 0
+    for j, k in enumerate(sub):
+        o = oracle_src(states[k, 0], k)
+        for b in range(n_img):                                                          # footprints, every band
+            bx = boxes[k, b]
+            assert (bx["x0"], bx["x1"], bx["y0"], bx["y1"]) == _capped_box(oracle, o, oimgs[b], 25.)
+        want, yl, xl = _capped_patch(oracle, o, oimgs[2], 25.)                          # rates, r band
+        got = patches[j, :want.size].cpu().numpy().reshape(want.shape)
+        worst_rate = max(worst_rate, hp.rel_err(got, want, 1e-6 * want.max()))
+        lst = []
+        for b in range(n_img):
+            bx = boxes[k, b]
+            h, w = bx["y1"] - bx["y0"], bx["x1"] - bx["x0"]
+            lst.append((samp[j, b, :h * w].reshape(h, w).astype(np.float64), (bx["y0"], bx["y1"]),
+                        (bx["x0"], bx["x1"]), oimgs[b]))
+        c = oracle.source_log_likelihood(o, lst)
+        p = 1 + (j % P)
+        d_want = oracle.source_log_likelihood(oracle_src(states[k, p], k), lst) - c
+        worst_ll = max(worst_ll, abs(delta[k, p - 1] - d_want) / max(abs(c), 1.))
+        if abs(log_u[k * P + p - 1] - d_want) > 1e-6 * max(abs(c), 1.):
+            assert acc[k, p - 1] == (log_u[k * P + p - 1] < d_want)
+            n_dec += 1
+    assert worst_rate < 1e-5, worst_rate
+    assert worst_ll < 1e-6, worst_ll
+    assert n_dec >= 190
+
+    sw.select(0)
+    sw.backgrounds()
+    sw.propose(seed=5)
+    states = sw.states()
+    sw.score(1, log_u)
+    delta = sw.delta[1].cpu().numpy().reshape(S, P)
+    acc = sw.accept[1].cpu().numpy().reshape(S, P).astype(bool)
+    offs, idx = sw.h_nbr
+    st = sw.h_static
+    worst_ll = 0.
+    for k in sub[:12]:
+        me = oracle_src(states[k, 0], k)
+        bxs, bgs = [], []
+        for b, oi in enumerate(oimgs):
+            bx = st[k, b]
+            xlim, ylim = (int(bx["x0"]), int(bx["x1"])), (int(bx["y0"]), int(bx["y1"]))
+            others = [oracle_src(states[t, 0], t) for t in idx[offs[k * n_img + b]:offs[k * n_img + b + 1]]]
+            bgs.append(oracle.generate_background_patch(me, others, oi, xlim, ylim))
+            bxs.append((xlim, ylim))
+        c = sum(oracle.image_like(me, oi, bx[0], bx[1], g) for oi, bx, g in zip(oimgs, bxs, bgs))
+        for p in (1, P):
+            want = oracle.calculate_acceptance_logprob(me, oracle_src(states[k, p], k), oimgs, bxs, bgs)
+            worst_ll = max(worst_ll, abs(delta[k, p - 1] - want) / max(abs(c), 1.))
+            if abs(log_u[k * P + p - 1] - want) > 1e-6 * max(abs(c), 1.):
+                assert acc[k, p - 1] == (log_u[k * P + p - 1] < want)
+    assert worst_ll < 1e-6, worst_ll
+    sw.select(1)
+    sw.loglik()
+    res = sw.stats()
+    assert np.all(np.isfinite(res["loglik"])) and res["accepted"].min() > 0
+    ll = engine.field_loglik(imgs, sw.sources(), bound_cap=25., max_patch_px=sw.max_patch_px).cpu().numpy()
+    assert np.array_equal(ll, res["loglik"])
+    assert sw.workspace_bytes < 8e9          # ~3.4 GB of workspace + patches for the whole field
