@@ -260,6 +260,11 @@ __device__ __forceinline__ float ex2_approx(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+__device__ __forceinline__ float lg2_approx(float x) {
+  float y;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ float rexp2(float x) { return ex2_approx(x); }
 __device__ __forceinline__ double rexp2(double x) { return exp2(x); }
 __device__ __forceinline__ float rfma(float a, float b, float c) { return fmaf(a, b, c); }
@@ -1541,48 +1546,43 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
       }
 
       if (!have_nx) e_nx = __shfl_sync(0xffffffffu, dnext.x, 0) >= 0 ? list_entry(__shfl_sync(0xffffffffu, dnext.y, 0)) : 0x7fffffff;
-      // Poisson terms.  log(lam) = T[bin] + res (log_accurate): sum x T in float64,
-      // sum x res (|res| < 1/60) and the 4-pixel row sums of lam in fp32, then float64
-      float sres = 0.f;
-      double slam = 0.0;
-      if (q.x + 3 < W && q.yB < H) {                          // interior lane: no bounds tests
+      // Poisson terms.  log(lam) = ln 2 lg2(lam r) - ln r with r = fl(1 / eps): lam r is close to 1 on the
+      // sky-dominated pixels, where lg2.approx is accurate to ~1e-7 ABSOLUTE, so sum x lg2(lam r) can be kept
+      // in fp32 per lane (8 pixels); the dominant term sum x (-ln r) takes the exact sum of the counts and
+      // the float64 logarithm of the ROUNDED r, so the rounding of r cancels.  3 instructions per pixel
+      // (FMUL, MUFU.LG2, FFMA); the float64 table logarithm it replaces cost ~20.
+      const float r_eps = (eps > 0.f) ? __frcp_rn(eps) : 1.f;
+      float s2 = 0.f;
+      double sd = 0.0, slam = 0.0;
 #pragma unroll
-        for (int r = 0; r < 2; ++r) {
+      for (int r = 0; r < 2; ++r) {
+        const int y = r ? q.yB : q.yA;
+        float lr[4];
 #pragma unroll
-          for (int p = 0; p < 4; ++p) {
-            s = fma((double)d[r][p], log_table(lam[r][p], logt), s);
-            sres = fmaf(d[r][p], log_residual(lam[r][p]), sres);
-          }
-          slam += (double)((lam[r][0] + lam[r][1]) + (lam[r][2] + lam[r][3]));
+        for (int p = 0; p < 4; ++p) {
+          s2 = fmaf(d[r][p], lg2_approx(lam[r][p] * r_eps), s2);     // d = 0 outside the image
+          lr[p] = (y < H && q.x + p < W) ? lam[r][p] : 0.f;
         }
-        if (mdl) {
-          float* m0 = mdl + (long long)q.yA * W + q.x;
-          float* m1 = mdl + (long long)q.yB * W + q.x;
-          if (((W & 3) == 0) && (((uintptr_t)mdl & 15) == 0)) {
-            *reinterpret_cast<float4*>(m0) = make_float4(lam[0][0], lam[0][1], lam[0][2], lam[0][3]);
-            *reinterpret_cast<float4*>(m1) = make_float4(lam[1][0], lam[1][1], lam[1][2], lam[1][3]);
-          } else {
+        sd += ((double)d[r][0] + (double)d[r][1]) + ((double)d[r][2] + (double)d[r][3]);
+        slam += (double)((lr[0] + lr[1]) + (lr[2] + lr[3]));
+      }
+      if (mdl) {
+        if (q.x + 3 < W && q.yB < H && ((W & 3) == 0) && (((uintptr_t)mdl & 15) == 0)) {
+          *reinterpret_cast<float4*>(mdl + (long long)q.yA * W + q.x) = make_float4(lam[0][0], lam[0][1], lam[0][2], lam[0][3]);
+          *reinterpret_cast<float4*>(mdl + (long long)q.yB * W + q.x) = make_float4(lam[1][0], lam[1][1], lam[1][2], lam[1][3]);
+        } else {
 #pragma unroll
-            for (int p = 0; p < 4; ++p) { m0[p] = lam[0][p]; m1[p] = lam[1][p]; }
-          }
-        }
-      } else {
-#pragma unroll
-        for (int r = 0; r < 2; ++r) {
-          const int y = r ? q.yB : q.yA;
-          if (y < H) {
+          for (int r = 0; r < 2; ++r) {
+            const int y = r ? q.yB : q.yA;
 #pragma unroll
             for (int p = 0; p < 4; ++p)
-              if (q.x + p < W) {
-                s = fma((double)d[r][p], log_table(lam[r][p], logt), s);
-                sres = fmaf(d[r][p], log_residual(lam[r][p]), sres);
-                slam += (double)lam[r][p];
-                if (mdl) mdl[(long long)y * W + q.x + p] = lam[r][p];
-              }
+              if (y < H && q.x + p < W) mdl[(long long)y * W + q.x + p] = lam[r][p];
           }
         }
       }
-      s += (double)sres - slam;
+      // -ln r in float64 from the rounded r (eps <= 0: r = 1, the logarithm of lam itself)
+      const double l0 = (eps > 0.f) ? -log_accurate(r_eps, logt) : 0.0;
+      s = fma(sd, l0, fma((double)s2, LN2_D, -slam));
     }
     s = warp_sum(s);
     if (lane == 0) a.block_partials[g] = s;

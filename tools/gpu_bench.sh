@@ -25,3 +25,6 @@ if [ "$2" = "ncu" ]; then
   ncu -i gpurun_out/tile_full_${tag}.ncu-rep --page source --csv > gpurun_out/tile_source_${tag}.csv 2>/dev/null
   ncu -i gpurun_out/tile_full_${tag}.ncu-rep --page raw --csv > gpurun_out/tile_raw_${tag}.csv 2>/dev/null
 fi
+if [ "$2" = "ncu" ]; then
+  ncu -i gpurun_out/tile_full_${tag}.ncu-rep --page source --csv --print-source cuda > gpurun_out/tile_cuda_${tag}.csv 2>/dev/null
+fi
