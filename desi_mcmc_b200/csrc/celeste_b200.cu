@@ -143,21 +143,17 @@ struct ImgPtrs {
   const DevImage* p[CG_MAX_IMAGES];
 };
 
-struct ItemHdr {          // 80 bytes; the first 32 are all the field kernel reads (two 16-byte loads)
+struct ItemHdr {
   int x0, x1, y0, y1;  // footprint (half-open)
   int ox, oy;          // local origin (pixel nearest the source centre)
   int K;               // components (0: renders nothing)
-  float flux_f;        // (float)flux
   int img;
   int strip_start, n_strips;   // first partial-sum slot / number of warp tiles
   int aux;
   int flags;
-  int pad0;
   double flux;         // rate multiplier (1 for unit-flux patches)
   double norm_term;    // band_flux * sum(psf weights), sources.py:174
-  int pad1[2];
 };
-static_assert(sizeof(ItemHdr) == 80, "ItemHdr must stay a multiple of 16 bytes (vector loads of its head)");
 
 struct Counters {
   int total_strips;    // partial-sum slots handed out
@@ -171,27 +167,20 @@ struct Counters {
   int pad[2];
 };
 
-// Component table: 64 bytes per component in either precision.
-//   float:  A, B, C, b10 | c01, c00, h, k8 | mx, my, qs, kx | ky, sl, -, -
-//   double: A, B, C, b10, c01, c00, -, -
-//   the quadratic A x^2 + B x y + C y^2 + b10 x + c01 y + c00 in log2 units, footprint-local integer
-//   coordinates; h = 2^(2A), k8 = 2^(8B) (the ratios of the row recurrence, ft_eval2r); then the
-//   culling record: mean (mx, my), peak value qs, kx = 2 Sxx / log2(e), ky = 2 Syy / log2(e)
-//   (half-widths^2 of the level-set bounding box per unit of log2 drop; the SIGN of kx carries
-//   recur_flush_unsafe) and sl = log2(e) / (2 lambda_min(Sigma)) (steepest log2 drop per squared
-//   pixel).  The first 32 bytes of a float row are exactly the 8-float entry of the warps' compacted
-//   tables, so a surviving component is two 16-byte copies.
-template <typename real> struct TabRow { static constexpr int W = (sizeof(real) == 4) ? 16 : 8; };
-#define TAB_WF 16
-#define TAB_BYTES (CG_MAX_COMP * 64)
+// Component table: 12 values per component (three 16-byte loads):
+//   A, B, C, b10 | c01, c00, mx, my | qs, kx, ky, sl
+//   the quadratic A x^2 + B x y + C y^2 + b10 x + c01 y + c00 in log2 units,
+//   footprint-local integer coordinates, followed by the culling record: mean
+//   (mx, my), peak value qs, kx = 2 Sxx / log2(e), ky = 2 Syy / log2(e)
+//   (half-widths^2 of the level-set bounding box per unit of log2 drop) and
+//   sl = log2(e) / (2 lambda_min(Sigma)) (steepest log2 drop per squared pixel).
+#define TAB_W 12
 #ifndef FT_RECUR
 #define FT_RECUR 1          // row recurrence compiled in (run-time switch: CG_OPT_ROW_RECURRENCE)
 #endif
-#ifndef FT_SMALLK
-#define FT_SMALLK 4         // mixtures up to this size are evaluated whole (no culling)
-#endif
 #define FT_RECUR_DMAX 96.f   // largest |log2 ratio of neighbouring pixels| the row recurrence is used for
 #define FT_RECUR_FLOOR -64.f // log2 of the unit-flux rate below which a value lost to underflow does not count
+#define TAB_STRIDE (CG_MAX_COMP * TAB_W)
 static_assert(14 * CG_MAX_PSF <= CG_MAX_COMP, "a galaxy has (6 exp + 8 dev) x n_psf components");
 static_assert(CG_MAX_COMP < 64, "bin-list entries pack item * 64 + K; cull_components owns components lane and lane + 32");
 
@@ -246,7 +235,7 @@ struct PrepArgs {
   double bound_cap;
   long long max_patch_px;
   ItemHdr* hdr;
-  void* tab;                // float or double rows, TAB_BYTES per item
+  void* tab;                // float or double, n_items * TAB_STRIDE
   int2* worklist;
   int worklist_cap;
   Counters* cnt;
@@ -259,10 +248,8 @@ struct PrepArgs {
   int unit_wt;              // warp tiles per work unit (same value in RenderArgs)
   int* tile_count;          // [n_img][max_tiles] (NULL: no binning)
   int* tile_list;           // [n_img][max_tiles][bin_cap]
-  unsigned long long* tile_mask;   // [n_img][max_tiles][bin_cap] survivor masks (field path), or NULL
   int max_tiles;
   int bin_w, bin_h, bin_cap;
-  int cull;                 // library options: bit 0 component culling on, bit 1 row recurrence off
 };
 
 // ---------------------------------------------------------------------------
@@ -271,11 +258,6 @@ struct PrepArgs {
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-__device__ __forceinline__ float lg2_approx(float x) {
-  float y;
-  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
 __device__ __forceinline__ float rexp2(float x) { return ex2_approx(x); }
@@ -546,12 +528,7 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
 
   const int ox = (int)rint(px), oy = (int)rint(py);
   const double Rsq_gal = 23.025850929940457;  // chi2.ppf(1 - 1e-5, 2)
-  real* tab = reinterpret_cast<real*>(reinterpret_cast<char*>(a.tab) + i * (long long)TAB_BYTES);
-  constexpr int TW = TabRow<real>::W;
-  // culling records of the item's components for the per-bin survivor masks (field path)
-  __shared__ __align__(16) float s_cull[4][CG_MAX_COMP * 8];
-  float* const cullrec = s_cull[threadIdx.x >> 5];
-  const bool want_masks = (sizeof(real) == 4) && a.tile_count != nullptr;
+  real* tab = reinterpret_cast<real*>(a.tab) + i * TAB_STRIDE;
 
   double mybound = -1e300;
   for (int c = lane; c < K; c += 32) {
@@ -583,37 +560,25 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
     double k2 = (-LOG2PI_D - .5 * log(det) + log(w)) * LOG2E_D;
     double A = -.5 * LOG2E_D * i00, B = -LOG2E_D * i01, C = -.5 * LOG2E_D * i11;
     double mx = mux - ox, my = muy - oy;
-    real* t = tab + c * TW;
+    real* t = tab + c * TAB_W;
     t[0] = (real)A;
     t[1] = (real)B;
     t[2] = (real)C;
     t[3] = (real)(-2. * A * mx - B * my);
     t[4] = (real)(-B * mx - 2. * C * my);
     t[5] = (real)(A * mx * mx + B * mx * my + C * my * my + k2);
-    if (sizeof(real) == 4) {
-      // (h, k8) from the ROUNDED A, B, exactly as the kernels used to compute them per warp
-      t[6] = (real)ex2_approx(2.f * (float)A);
-      t[7] = (real)ex2_approx(8.f * (float)B);
-      t[8] = (real)mx;
-      t[9] = (real)my;
-      t[10] = (real)k2;
-      // the sign of kx carries recur_flush_unsafe (the value itself is positive)
-      t[11] = (real)(recur_flush_unsafe(A, k2) ? -(2. * s00 / LOG2E_D) : (2. * s00 / LOG2E_D));
-      t[12] = (real)(2. * s11 / LOG2E_D);
+    t[6] = (real)mx;
+    t[7] = (real)my;
+    t[8] = (real)k2;
+    // the sign of t[9] carries recur_flush_unsafe (the value itself is positive)
+    t[9] = (real)(recur_flush_unsafe(A, k2) ? -(2. * s00 / LOG2E_D) : (2. * s00 / LOG2E_D));
+    t[10] = (real)(2. * s11 / LOG2E_D);
+    {
       const double dd = s00 - s11;
       const double lmin = .5 * ((s00 + s11) - sqrt(dd * dd + 4. * s01 * s01));
-      t[13] = (real)(.5 * LOG2E_D / fmax(lmin, 1e-300));
-      t[14] = (real)0; t[15] = (real)0;
-      if (want_masks) {
-        float* cr = cullrec + c * 8;
-        cr[0] = (float)t[8]; cr[1] = (float)t[9]; cr[2] = (float)t[10]; cr[3] = (float)t[11];
-        cr[4] = (float)t[12]; cr[5] = (float)t[13]; cr[6] = fabsf((float)t[0]); cr[7] = fabsf((float)t[1]);
-      }
-    } else {
-      t[6] = (real)0; t[7] = (real)0;
+      t[11] = (real)(.5 * LOG2E_D / fmax(lmin, 1e-300));
     }
   }
-  __syncwarp();
   if (!star) {
     bound = warp_max(mybound);
     if (K == 0) bound = 0;
@@ -701,63 +666,18 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
     const int tya = y0 / bh, tyb = (y1 - 1) / bh;
     const int nx = txb - txa + 1, nt = nx * (tyb - tya + 1);
     for (int j = lane; j < nt; j += 32) {
-      const int tby = tya + j / nx, tbx = txa + (j % nx);
-      const int t = tby * tiles_x + tbx;
+      const int t = (tya + j / nx) * tiles_x + txa + (j % nx);
       const long long slot = (long long)it.img * a.max_tiles + t;
-      // Survivor mask of the item's components on this bin -- cull_components' test, evaluated ONCE
-      // here by one thread per bin instead of by every warp of field_tile_kernel (185 instructions
-      // per (bin, galaxy) there): bit k = component k may exceed 2^-CULL_T of the mixture somewhere
-      // on (footprint ∩ bin); bit 63 = the row recurrence is safe for all survivors; bit 62 = valid.
-      unsigned long long mask = 0ull;
-      if (want_masks) {
-        const float xa = (float)(max(tbx * bw, x0) - ox), xb = (float)(min(tbx * bw + bw, x1) - 1 - ox);
-        const float ya = (float)(max(tby * bh, y0) - oy), yb = (float)(min(tby * bh + bh, y1) - 1 - oy);
-        const bool cull = (a.cull & 1) && K > FT_SMALLK;
-        float lb = -INFINITY;
-        if (cull)
-          for (int k = 0; k < K; ++k) {
-            const float4 c0 = *reinterpret_cast<const float4*>(cullrec + k * 8);
-            const float4 c1 = *reinterpret_cast<const float4*>(cullrec + k * 8 + 4);
-            const float fx = fmaxf(fabsf(xa - c0.x), fabsf(xb - c0.x)), fy = fmaxf(fabsf(ya - c0.y), fabsf(yb - c0.y));
-            const float l = c0.z - c1.y * (fx * fx + fy * fy);
-            if (l == l) lb = fmaxf(lb, l);
-          }
-        const float thr = lb - (CULL_T + 0.5f);
-        bool recur_ok = (a.cull & 1) && K > 1;
-        for (int k = 0; k < K; ++k) {
-          const float4 c0 = *reinterpret_cast<const float4*>(cullrec + k * 8);
-          const float4 c1 = *reinterpret_cast<const float4*>(cullrec + k * 8 + 4);
-          const float fx = fmaxf(fabsf(xa - c0.x), fabsf(xb - c0.x)), fy = fmaxf(fabsf(ya - c0.y), fabsf(yb - c0.y));
-          bool keep = true;
-          if (cull) {
-            const float rho = (c0.z - thr) * 1.0001f;
-            const float dx = fmaxf(0.f, fmaxf(xa - c0.x, c0.x - xb)), dy = fmaxf(0.f, fmaxf(ya - c0.y, c0.y - yb));
-            keep = !(rho < 0.f) && !(dx * dx > rho * fabsf(c0.w)) && !(dy * dy > rho * c1.x);
-          }
-          if (keep) {
-            mask |= 1ull << k;
-            // bound of |q(x+1,y) - q(x,y)| over the rectangle widened by the 3 pixels a lane's group
-            // of 4 may start to the left of it; 8|B| bounds k8
-            float dmx = fmaxf(fmaf(c1.z, 2.f * (fx + 3.f) + 1.f, c1.w * fy), 8.f * c1.w);
-            if (c0.w < 0.f) dmx = INFINITY;                        // recur_flush_unsafe
-            if (!(dmx <= FT_RECUR_DMAX)) recur_ok = false;
-          }
-        }
-        mask |= (1ull << 62) | (recur_ok ? (1ull << 63) : 0ull);
-      }
       const int pos = atomicAdd(&a.tile_count[slot], 1);
       // entry = item * 64 + K (K <= CG_MAX_COMP < 64): the tile kernels weigh a bin
       // without touching the item headers
-      if (pos < cap) {
-        a.tile_list[slot * cap + pos] = (int)i * 64 + K;
-        if (a.tile_mask) a.tile_mask[slot * cap + pos] = mask;
-      }
+      if (pos < cap) a.tile_list[slot * cap + pos] = (int)i * 64 + K;
     }
   }
   if (lane == 0) {
     ItemHdr h;
     h.x0 = x0; h.x1 = x1; h.y0 = y0; h.y1 = y1;
-    h.ox = ox; h.oy = oy; h.K = K; h.img = it.img; h.flux_f = (float)flux; h.pad0 = 0; h.pad1[0] = h.pad1[1] = 0;
+    h.ox = ox; h.oy = oy; h.K = K; h.img = it.img;
     h.strip_start = start; h.n_strips = n_strips;
     h.aux = it.aux; h.flags = it.flags;
     h.flux = flux;
@@ -834,10 +754,10 @@ __device__ __forceinline__ void unit_decode(int q, int cpr, int hp, float r_band
 //   { q_k >= lb - CULL_T } misses the rectangle, i.e. its largest value over
 //   the rectangle is below 2^-CULL_T of the mixture everywhere in it.
 // Survivors are compacted (component order preserved) into the warp's table
-// of 8-float entries (the first 32 bytes of their rows); returns their number.
-// *recur_ok says whether the row recurrence of ft_eval2r/ft_eval1r is safe for every survivor on
-// this rectangle (see FT_RECUR below).  The field path evaluates the same test once per (item, bin)
-// in prepare_kernel and hands field_tile_kernel the result as a 64-bit mask.
+// of 8-float entries; returns their number.
+// The row pair (h, k8) = (2^(2A), 2^(8B)) of each surviving component feeds the
+// row recurrence of ft_eval2r/ft_eval1r; *recur_ok says whether that recurrence is
+// safe for every survivor on this rectangle (see FT_RECUR below).
 // LDG: the table is read from global memory through the read-only path (field kernel: L2)
 // or from shared memory (render_kernel).  xext: pixels a lane may start left of the rectangle.
 template <bool LDG>
@@ -851,22 +771,21 @@ __device__ __forceinline__ int cull_components(const float* gtab, int K, int lan
     const int k = lane + 32 * r;
     qs[r] = -INFINITY; kx[r] = ky[r] = 0.f; dx2[r] = dy2[r] = 0.f; dmx[r] = 0.f;
     if (k < K) {
-      const float4* t4 = reinterpret_cast<const float4*>(gtab + k * TAB_WF);
+      const float4* t4 = reinterpret_cast<const float4*>(gtab + k * TAB_W);
       e0[r] = LDG ? __ldg(t4) : t4[0];
       e1[r] = LDG ? __ldg(t4 + 1) : t4[1];
       const float4 e2 = LDG ? __ldg(t4 + 2) : t4[2];
-      const float2 e3 = LDG ? __ldg(reinterpret_cast<const float2*>(t4 + 3)) : *reinterpret_cast<const float2*>(t4 + 3);
-      const float mx = e2.x, my = e2.y;
-      qs[r] = e2.z; kx[r] = fabsf(e2.w); ky[r] = e3.x;
+      const float mx = e1[r].z, my = e1[r].w;
+      qs[r] = e2.x; kx[r] = fabsf(e2.y); ky[r] = e2.z;
       const float fx = fmaxf(fabsf(xa - mx), fabsf(xb - mx)), fy = fmaxf(fabsf(ya - my), fabsf(yb - my));
-      const float l = qs[r] - e3.y * (fx * fx + fy * fy);
+      const float l = qs[r] - e2.w * (fx * fx + fy * fy);
       if (l == l) lb = fmaxf(lb, l);
       const float dx = fmaxf(0.f, fmaxf(xa - mx, mx - xb)), dy = fmaxf(0.f, fmaxf(ya - my, my - yb));
       dx2[r] = dx * dx; dy2[r] = dy * dy;
       // bound of |q(x+1,y) - q(x,y)| = |2A(x-mx) + B(y-my) + A| over the rectangle widened
       // by the xext pixels a lane's group of 4 may start to the left of it; 8|B| bounds k8
       dmx[r] = fmaxf(fmaf(fabsf(e0[r].x), 2.f * (fx + xext) + 1.f, fabsf(e0[r].y) * fy), 8.f * fabsf(e0[r].y));
-      if (e2.w < 0.f) dmx[r] = INFINITY;                         // recur_flush_unsafe (prepare_kernel)
+      if (e2.y < 0.f) dmx[r] = INFINITY;                         // recur_flush_unsafe (prepare_kernel)
     }
   }
 #pragma unroll
@@ -884,12 +803,12 @@ __device__ __forceinline__ int cull_components(const float* gtab, int K, int lan
   if (keep[0]) {
     float* d = wtab + __popc(m0 & lt) * 8;
     *reinterpret_cast<float4*>(d) = e0[0];
-    *reinterpret_cast<float4*>(d + 4) = e1[0];                   // c01, c00, h, k8
+    *reinterpret_cast<float4*>(d + 4) = make_float4(e1[0].x, e1[0].y, ex2_approx(2.f * e0[0].x), ex2_approx(8.f * e0[0].y));
   }
   if (keep[1]) {
     float* d = wtab + (__popc(m0) + __popc(m1 & lt)) * 8;
     *reinterpret_cast<float4*>(d) = e0[1];
-    *reinterpret_cast<float4*>(d + 4) = e1[1];
+    *reinterpret_cast<float4*>(d + 4) = make_float4(e1[1].x, e1[1].y, ex2_approx(2.f * e0[1].x), ex2_approx(8.f * e0[1].y));
   }
   *recur_ok = !__any_sync(0xffffffffu, (keep[0] && !(dmx[0] <= FT_RECUR_DMAX)) || (keep[1] && !(dmx[1] <= FT_RECUR_DMAX)));
   __syncwarp();
@@ -899,12 +818,11 @@ __device__ __forceinline__ int cull_components(const float* gtab, int K, int lan
 template <typename real, int MODE>
 __global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
   // per-warp staging: the item's component table and the culled, compacted table
-  constexpr int TW = TabRow<real>::W;
-  __shared__ __align__(16) real s_tab_all[(STRIP_THREADS / 32) * CG_MAX_COMP * TW];
+  __shared__ __align__(16) real s_tab_all[(STRIP_THREADS / 32) * TAB_STRIDE];
   __shared__ __align__(16) float s_wtab_all[(sizeof(real) == 4) ? (STRIP_THREADS / 32) * CG_MAX_COMP * 8 : 4];
   const LogTable* const logt = a.logtab;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  real* const s_tab = s_tab_all + warp * CG_MAX_COMP * TW;
+  real* const s_tab = s_tab_all + warp * TAB_STRIDE;
   float* const s_wtab = s_wtab_all + ((sizeof(real) == 4) ? warp * CG_MAX_COMP * 8 : 0);
   const int n_heavy = *((volatile int*)&a.cnt->heavy_strips);
   const int total = n_heavy + *((volatile int*)&a.cnt->light_strips);
@@ -922,10 +840,10 @@ __global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
     const ItemHdr h = a.hdr[item];
     __syncwarp();                 // the warp is done with the tables of its previous unit
     {
-      const float4* g4 = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(a.tab) +
-                                                          (long long)item * TAB_BYTES);
+      const float4* g4 = reinterpret_cast<const float4*>(reinterpret_cast<const real*>(a.tab) +
+                                                          (long long)item * TAB_STRIDE);
       float4* s4 = reinterpret_cast<float4*>(s_tab);
-      const int n4 = h.K * 4;                       // 64 bytes per component
+      const int n4 = h.K * TAB_W * (int)sizeof(real) / 16;
       for (int t = lane; t < n4; t += 32) s4[t] = g4[t];
     }
     __syncwarp();
@@ -950,7 +868,7 @@ __global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
 
       int n = h.K;
       const real* tb = s_tab;
-      int stride = TW;
+      int stride = TAB_W;
       bool recur = false;
       if (sizeof(real) == 4 && (a.cull & 1) && n > 1) {
         const int rmin = __reduce_min_sync(0xffffffffu, active ? row0 : 0x7fffffff);
@@ -1096,10 +1014,9 @@ struct FieldArgs {
   ImgPtrs imgs;
   int n_img;
   const ItemHdr* hdr;
-  const float* tab;        // component tables, TAB_BYTES per item
+  const float* tab;        // component tables, n_items * TAB_STRIDE
   const int* tile_count;   // [n_img][max_tiles] sources listed per 16 x 16 bin
   int* tile_list;          // [n_img][max_tiles][BIN_CAP] entries item * 64 + K (put in source order by bin_order_kernel)
-  unsigned long long* tile_mask;   // [n_img][max_tiles][BIN_CAP] survivor masks of the entries (prepare_kernel)
   int2* order;             // [FT_BUCKETS][tiles_total] (bin id, list length) by weight class
   int* sched;              // [FT_BUCKETS] class sizes, [FT_BUCKETS] work counter (zero on entry)
   double* block_partials;  // [n_img][max_tiles] per-bin sums
@@ -1148,6 +1065,9 @@ struct FieldArgs {
 #endif
 #define FT_PRAGMA_(x) _Pragma(#x)
 #define FT_PRAGMA(x) FT_PRAGMA_(x)
+#ifndef FT_SMALLK
+#define FT_SMALLK 4         // mixtures up to this size are evaluated whole (no culling)
+#endif
 #define FT_LIGHT 2          // classes below this are latency-bound (no galaxy in the bin)
 // bins per claimed work unit by weight class: heavy bins one at a time (balance), sky in bulk
 __device__ __forceinline__ constexpr int ft_chunk(int cls) {
@@ -1180,16 +1100,13 @@ __global__ void __launch_bounds__(256) bin_order_kernel(FieldArgs a) {
         // weigh the bin and put its (atomically appended, hence unordered) list
         // into source order: the tile kernel then takes the entries as they lie
         int* lst = a.tile_list + (long long)g * BIN_CAP;
-        unsigned long long* msk = a.tile_mask + (long long)g * BIN_CAP;
         int w = 0;
         for (int j = 0; j < cnt; ++j) {
           const int key = lst[j];
-          const unsigned long long mk = msk[j];
           w += key & 63;
           int k = j - 1;
-          while (k >= 0 && lst[k] > key) { lst[k + 1] = lst[k]; msk[k + 1] = msk[k]; --k; }
+          while (k >= 0 && lst[k] > key) { lst[k + 1] = lst[k]; --k; }
           lst[k + 1] = key;
-          msk[k + 1] = mk;
         }
         b = ft_bucket(w);
       }
@@ -1348,89 +1265,33 @@ FT_PRAGMA(unroll FT_UNROLL)
 
 struct FtGeom { int X0, Y0, x, yA, yB; };
 
-// cp.async: 16 bytes global -> shared without a register round trip; the copies of a commit group
-// complete asynchronously, so the NEXT source's table is fetched while the current one is evaluated
-__device__ __forceinline__ void cp_async16(float* smem, const void* gmem) {
-  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
-// Stage the components of `item` that survive on this bin (mask from prepare_kernel) into the warp's
-// table wt: component k is copied by lane k & 31 to slot popc(mask below k) -- the order cull_components
-// compacts in.  Asynchronous; returns the number of survivors.
-__device__ __forceinline__ int ft_stage(const FieldArgs& a, int item, unsigned long long mask, int lane, float* wt) {
-  const unsigned m0 = (unsigned)mask, m1 = (unsigned)(mask >> 32) & 0x3fffffffu;
-  const char* g = reinterpret_cast<const char*>(a.tab) + (long long)item * TAB_BYTES;
-  const unsigned lt = (1u << lane) - 1u;
-  if ((m0 >> lane) & 1u) {
-    float* d = wt + __popc(m0 & lt) * 8;
-    const char* src = g + lane * 64;
-    cp_async16(d, src);
-    cp_async16(d + 4, src + 16);
-  }
-  if ((m1 >> lane) & 1u) {
-    float* d = wt + (__popc(m0) + __popc(m1 & lt)) * 8;
-    const char* src = g + (lane + 32) * 64;
-    cp_async16(d, src);
-    cp_async16(d + 4, src + 16);
-  }
-  cp_async_commit();
-  return __popc(m0) + __popc(m1);
-}
-
-// evaluate the n staged components at the lane's pixels -> UNIT-flux values acc0 (row yA), acc1 (row yB),
-// unmasked.  iy0, iy1: rows of the bin the rectangle reaches.
-__device__ __forceinline__ void ft_eval_rates(const float* tb, int n, bool recur, int iy0, int iy1, int2 o,
-                                              const FtGeom& q, int lane, float (&acc0)[4], float (&acc1)[4],
-                                              unsigned long long& issued) {
-  const float x0f = (float)(q.x - o.x);
-  const bool doA = iy0 < q.Y0 + 8, doB = iy1 > q.Y0 + 8;         // which row halves the rectangle reaches
-#pragma unroll
-  for (int p = 0; p < 4; ++p) { acc0[p] = 0.f; acc1[p] = 0.f; }
-  if (recur) {
-    if (doA && doB) ft_eval2r(tb, n, (float)(q.yA - o.y), (float)(q.yB - o.y), x0f, acc0, acc1);
-    else if (doA) ft_eval1r(tb, n, (float)(q.yA - o.y), x0f, acc0);
-    else ft_eval1r(tb, n, (float)(q.yB - o.y), x0f, acc1);
-  } else {
-    float xl[4];
-#pragma unroll
-    for (int p = 0; p < 4; ++p) xl[p] = x0f + (float)p;
-    if (doA && doB) ft_eval2(tb, n, (float)(q.yA - o.y), (float)(q.yB - o.y), xl, acc0, acc1);
-    else if (doA) ft_eval1(tb, n, (float)(q.yA - o.y), xl, acc0);
-    else ft_eval1(tb, n, (float)(q.yB - o.y), xl, acc1);
-  }
-  if (lane == 0) issued += (unsigned long long)n * ((doA && doB) ? 256 : 128);
-}
-
-// one source on the warp's bin WITHOUT a precomputed mask (scan fallback of overflowed bins, the
-// allocation and background kernels): cull the components against the part of the rectangle bx that
-// lies in the bin (tables read through L1/L2), then evaluate.  Returns false (warp-uniform) when bx
-// misses the bin.
+// one source on the warp's bin: cull the components against the part of the rectangle bx that lies
+// in the bin and evaluate the survivors at the lane's pixels -> UNIT-flux values acc0 (row yA) and
+// acc1 (row yB), unmasked (lanes outside bx hold values the caller must not use).  Returns false
+// (warp-uniform) when bx misses the bin.
 __device__ __forceinline__ bool ft_source_rates(const FieldArgs& a, int item, int K, int4 bx, int2 o,
                                                 const FtGeom& q, int lane, float* wtab,
                                                 float (&acc0)[4], float (&acc1)[4], unsigned long long& issued) {
   const int ix0 = max(q.X0, bx.x), ix1 = min(q.X0 + BIN_W, bx.y);
   const int iy0 = max(q.Y0, bx.z), iy1 = min(q.Y0 + BIN_H, bx.w);
   if (ix0 >= ix1 || iy0 >= iy1 || K <= 0) return false;          // warp-uniform
-  const float* gtab = reinterpret_cast<const float*>(reinterpret_cast<const char*>(a.tab) + (long long)item * TAB_BYTES);
+  const float* gtab = a.tab + (long long)item * TAB_STRIDE;
   int n = K;
   bool recur = false;
   __syncwarp();                       // the warp is done reading its previous table
   if ((a.cull & 1) && n > 1 && n <= FT_SMALLK) {
-    // a star's PSF mixture: culling would cost more than the few evaluations it can save
+    // a star's PSF mixture: culling would cost more than the few evaluations it can save;
+    // copy the quadratics, add (h, k8) and the recurrence range check of cull_components
     const float xa = (float)(ix0 - o.x), xb = (float)(ix1 - 1 - o.x), ya = (float)(iy0 - o.y), yb = (float)(iy1 - 1 - o.y);
     float dmx = 0.f;
     if (lane < n) {
-      const float4* t4 = reinterpret_cast<const float4*>(gtab + lane * TAB_WF);
-      const float4 e0 = __ldg(t4), e1 = __ldg(t4 + 1), e2 = __ldg(t4 + 2);
-      if (e2.w < 0.f) dmx = INFINITY;                               // recur_flush_unsafe (prepare_kernel)
-      const float fx = fmaxf(fabsf(xa - e2.x), fabsf(xb - e2.x)), fy = fmaxf(fabsf(ya - e2.y), fabsf(yb - e2.y));
+      const float4* t4 = reinterpret_cast<const float4*>(gtab + lane * TAB_W);
+      const float4 e0 = __ldg(t4), e1 = __ldg(t4 + 1);
+      if (__ldg(gtab + lane * TAB_W + 9) < 0.f) dmx = INFINITY;    // recur_flush_unsafe (prepare_kernel)
+      const float fx = fmaxf(fabsf(xa - e1.z), fabsf(xb - e1.z)), fy = fmaxf(fabsf(ya - e1.w), fabsf(yb - e1.w));
       dmx = fmaxf(dmx, fmaxf(fmaf(fabsf(e0.x), 2.f * (fx + 3.f) + 1.f, fabsf(e0.y) * fy), 8.f * fabsf(e0.y)));
       *reinterpret_cast<float4*>(wtab + lane * 8) = e0;
-      *reinterpret_cast<float4*>(wtab + lane * 8 + 4) = e1;
+      *reinterpret_cast<float4*>(wtab + lane * 8 + 4) = make_float4(e1.x, e1.y, ex2_approx(2.f * e0.x), ex2_approx(8.f * e0.y));
     }
     recur = !__any_sync(0xffffffffu, !(dmx <= FT_RECUR_DMAX)) && FT_RECUR && !(a.cull & 2);
     __syncwarp();
@@ -1441,21 +1302,44 @@ __device__ __forceinline__ bool ft_source_rates(const FieldArgs& a, int item, in
   } else {
     // no culling: copy the quadratics as they are (the eval loops read shared memory only)
     for (int k = lane; k < n; k += 32) {
-      const float4* t4 = reinterpret_cast<const float4*>(gtab + k * TAB_WF);
-      *reinterpret_cast<float4*>(wtab + k * 8) = __ldg(t4);
-      *reinterpret_cast<float4*>(wtab + k * 8 + 4) = __ldg(t4 + 1);
+      const float4* t4 = reinterpret_cast<const float4*>(gtab + k * TAB_W);
+      const float4 e0 = __ldg(t4), e1 = __ldg(t4 + 1);
+      *reinterpret_cast<float4*>(wtab + k * 8) = e0;
+      *reinterpret_cast<float2*>(wtab + k * 8 + 4) = make_float2(e1.x, e1.y);
     }
     __syncwarp();
   }
-  ft_eval_rates(wtab, n, recur, iy0, iy1, o, q, lane, acc0, acc1, issued);
+  const float* tb = wtab;
+  float xl[4];
+#pragma unroll
+  for (int p = 0; p < 4; ++p) xl[p] = (float)(q.x + p - o.x);
+  const bool doA = iy0 < q.Y0 + 8, doB = iy1 > q.Y0 + 8;         // which row halves the footprint reaches
+#pragma unroll
+  for (int p = 0; p < 4; ++p) { acc0[p] = 0.f; acc1[p] = 0.f; }
+  if (doA && doB) {
+    if (recur) ft_eval2r(tb, n, (float)(q.yA - o.y), (float)(q.yB - o.y), xl[0], acc0, acc1);
+    else ft_eval2(tb, n, (float)(q.yA - o.y), (float)(q.yB - o.y), xl, acc0, acc1);
+    if (lane == 0) issued += (unsigned long long)n * 256;
+  } else if (doA) {
+    if (recur) ft_eval1r(tb, n, (float)(q.yA - o.y), xl[0], acc0);
+    else ft_eval1(tb, n, (float)(q.yA - o.y), xl, acc0);
+    if (lane == 0) issued += (unsigned long long)n * 128;
+  } else {
+    if (recur) ft_eval1r(tb, n, (float)(q.yB - o.y), xl[0], acc1);
+    else ft_eval1(tb, n, (float)(q.yB - o.y), xl, acc1);
+    if (lane == 0) issued += (unsigned long long)n * 128;
+  }
   return true;
 }
 
-// add the unit-flux values of a source to lambda inside the rectangle bx
-__device__ __forceinline__ void ft_accumulate(const float (&acc0)[4], const float (&acc1)[4], float fl, int4 bx,
-                                              const FtGeom& q, float (&lam)[2][4]) {
+// ... and add the rates inside the footprint to lambda (the field kernel's use)
+__device__ __forceinline__ void ft_source(const FieldArgs& a, int item, int K, int4 bx, int2 o, float fl,
+                                          const FtGeom& q, int lane, float* wtab,
+                                          float (&lam)[2][4], unsigned long long& issued) {
+  float acc0[4], acc1[4];
+  if (!ft_source_rates(a, item, K, bx, o, q, lane, wtab, acc0, acc1, issued)) return;
   if (min(q.X0 + BIN_W, bx.y) - max(q.X0, bx.x) == BIN_W &&
-      min(q.Y0 + BIN_H, bx.w) - max(q.Y0, bx.z) == BIN_H) {       // the rectangle covers the bin: no masks
+      min(q.Y0 + BIN_H, bx.w) - max(q.Y0, bx.z) == BIN_H) {       // the footprint covers the bin: no masks
 #pragma unroll
     for (int p = 0; p < 4; ++p) {
       lam[0][p] += acc0[p] * fl;
@@ -1472,23 +1356,11 @@ __device__ __forceinline__ void ft_accumulate(const float (&acc0)[4], const floa
   }
 }
 
-// ... cull + evaluate + accumulate in one call (scan fallback, background kernel)
-__device__ __forceinline__ void ft_source(const FieldArgs& a, int item, int K, int4 bx, int2 o, float fl,
-                                          const FtGeom& q, int lane, float* wtab,
-                                          float (&lam)[2][4], unsigned long long& issued) {
-  float acc0[4], acc1[4];
-  if (!ft_source_rates(a, item, K, bx, o, q, lane, wtab, acc0, acc1, issued)) return;
-  ft_accumulate(acc0, acc1, fl, bx, q, lam);
-}
-
 // 3 CTAs x 8 warps per SM at 80 registers (no spills; 4 CTAs at 64 registers spill the pixel counts and measured slower)
 __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldArgs a) {
-  // two compacted tables per warp: the next source's components arrive (cp.async) while the current one
-  // is evaluated; + the row the evaluation loops prefetch past the end
-  __shared__ __align__(16) float s_wtab[FT_THREADS / 32][2][(CG_MAX_COMP + 1) * 8];
+  __shared__ __align__(16) float s_wtab[FT_THREADS / 32][(CG_MAX_COMP + 1) * 8];   // + the prefetch row
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  float* const wtab = s_wtab[warp][0];
-  float* const wtab1 = s_wtab[warp][1];
+  float* const wtab = s_wtab[warp];
   const LogTable* const logt = a.logtab;
 
   // class sizes (written by bin_order_kernel, complete before this launch)
@@ -1542,12 +1414,9 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
   int2 dcur = make_int2(-1, 0);
   if (c0 < total) dcur = load_unit(c0);
   // lane's entry of a bin's source list (descriptor word y = g << 6 | length); overflowed lists are scanned instead
-  unsigned long long m_nx = 0ull;      // ... and its survivor mask (prepare_kernel), fetched with the entry
   auto list_entry = [&](int gy) -> int {
     const int n = gy & 63;
-    const bool ok = n <= BIN_CAP && lane < n;
-    m_nx = ok ? __ldg(a.tile_mask + (long long)(gy >> 6) * BIN_CAP + lane) : 0ull;
-    return ok ? __ldg(a.tile_list + (long long)(gy >> 6) * BIN_CAP + lane) : 0x7fffffff;
+    return (n <= BIN_CAP && lane < n) ? __ldg(a.tile_list + (long long)(gy >> 6) * BIN_CAP + lane) : 0x7fffffff;
   };
   int e_nx = __shfl_sync(0xffffffffu, dcur.x, 0) >= 0 ? list_entry(__shfl_sync(0xffffffffu, dcur.y, 0)) : 0x7fffffff;
 
@@ -1569,7 +1438,6 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
     // this bin's list entry was fetched while the previous bin was processed; fetch the next
     // bin's now if it belongs to this unit (else before the epilogue, from the next unit)
     const int e_cur = e_nx;
-    const unsigned long long m_cur = m_nx;
     bool have_nx = false;
     if (cj + 1 < FT_CHUNK && __shfl_sync(0xffffffffu, dcur.x, (cj + 1) & 31) >= 0) {
       e_nx = list_entry(__shfl_sync(0xffffffffu, dcur.y, (cj + 1) & 31));
@@ -1622,117 +1490,99 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
 #pragma unroll
         for (int p = 0; p < 4; ++p) lam[r][p] = eps;
 
+      // candidates per round, one per lane: the bin's list (one round; lane j owns
+      // entry j) or, when the list overflowed, every source of the image 32 at a
+      // time.  They are taken in source order: rank by value / by lane.
       const bool scan = cnt > BIN_CAP;
-      if (!scan) {
-        // The bin's list, in source order (bin_order_kernel): lane j owns entry j, its survivor mask and
-        // the head of its item header (two 16-byte loads).  The sources are taken in turn; the components
-        // that survive on this bin are staged into the warp's table asynchronously, ONE SOURCE AHEAD of
-        // the evaluation, so the L2 latency of the table rows hides behind the previous source's loop.
-        int4 bx = make_int4(0, 0, 0, 0), h1 = make_int4(0, 0, 0, 0);
-        if (lane < cnt) {
-          const int4* hp = reinterpret_cast<const int4*>(a.hdr + (e_cur >> 6));
-          bx = __ldg(hp);
-          h1 = __ldg(hp + 1);                                   // ox, oy, K, (float)flux
-        }
-        unsigned long long mk = __shfl_sync(0xffffffffu, m_cur, 0);
-        int n_nx = cnt ? ft_stage(a, __shfl_sync(0xffffffffu, e_cur, 0) >> 6, mk, lane, wtab) : 0;
-        for (int r = 0; r < cnt; ++r) {
-          const int n = n_nx;
-          const bool recur = (mk >> 63) && FT_RECUR && !(a.cull & 2);
-          float* const wt = (r & 1) ? wtab1 : wtab;
-          if (r + 1 < cnt) {
-            __syncwarp();                                       // the other table was read two sources ago
-            mk = __shfl_sync(0xffffffffu, m_cur, r + 1);
-            n_nx = ft_stage(a, __shfl_sync(0xffffffffu, e_cur, r + 1) >> 6, mk, lane, (r & 1) ? wtab : wtab1);
-            cp_async_wait<1>();
-          } else {
-            cp_async_wait<0>();
+      const int ns = scan ? a.n_src[img] : 0;
+      const int rounds = scan ? (ns + 31) / 32 : 1;
+      for (int rd = 0; rd < rounds; ++rd) {
+        int e = 0x7fffffff;
+        int4 bx = make_int4(0, 0, 0, 0);
+        int2 o = make_int2(0, 0);
+        float fl = 0.f;
+        bool valid = false;
+        if (!scan) {
+          if (lane < cnt) {
+            e = e_cur;
+            valid = true;
           }
-          __syncwarp();
-          int4 b;
-          b.x = __shfl_sync(0xffffffffu, bx.x, r); b.y = __shfl_sync(0xffffffffu, bx.y, r);
-          b.z = __shfl_sync(0xffffffffu, bx.z, r); b.w = __shfl_sync(0xffffffffu, bx.w, r);
-          const int2 oo = make_int2(__shfl_sync(0xffffffffu, h1.x, r), __shfl_sync(0xffffffffu, h1.y, r));
-          const float fl = __int_as_float(__shfl_sync(0xffffffffu, h1.w, r));
-          float acc0[4], acc1[4];
-          ft_eval_rates(wt, n, recur, max(q.Y0, b.z), min(q.Y0 + BIN_H, b.w), oo, q, lane, acc0, acc1, issued);
-          ft_accumulate(acc0, acc1, fl, b, q, lam);
-        }
-      } else {
-        // overflowed list: every source of the image, 32 at a time, in source order (lane order);
-        // the components are culled here (no precomputed mask)
-        const int ns = a.n_src[img];
-        for (int rd = 0; rd < (ns + 31) / 32; ++rd) {
-          int e = 0x7fffffff;
-          int4 bx = make_int4(0, 0, 0, 0);
-          int2 o = make_int2(0, 0);
-          float fl = 0.f;
-          bool valid = false;
+        } else {
           const int sidx = rd * 32 + lane;
           if (sidx < ns) {
-            const int it = a.item_base[img] + sidx * a.item_stride[img];
-            const ItemHdr* hp = a.hdr + it;
-            bx = *reinterpret_cast<const int4*>(hp);
-            o = *reinterpret_cast<const int2*>(&hp->ox);
-            fl = hp->flux_f;
+            e = (a.item_base[img] + sidx * a.item_stride[img]) * 64;
+            valid = true;
+          }
+        }
+        if (valid) {
+          const ItemHdr* hp = a.hdr + (e >> 6);
+          bx = *reinterpret_cast<const int4*>(hp);
+          o = *reinterpret_cast<const int2*>(&hp->ox);
+          fl = (float)hp->flux;
+          if (scan) {
             const int K = hp->K;
-            e = it * 64 + K;
+            e += K;
             valid = (K > 0) && bx.x < q.X0 + BIN_W && bx.y > q.X0 && bx.z < q.Y0 + BIN_H && bx.w > q.Y0;
           }
-          const unsigned vm = __ballot_sync(0xffffffffu, valid);
-          const int nv = __popc(vm);
-          const int rk = __popc(vm & ((1u << lane) - 1u));
-          for (int r = 0; r < nv; ++r) {
-            const unsigned m = __ballot_sync(0xffffffffu, valid && rk == r);
-            const int sl = __ffs(m) - 1;
-            const int ee = __shfl_sync(0xffffffffu, e, sl);
-            int4 b;
-            b.x = __shfl_sync(0xffffffffu, bx.x, sl); b.y = __shfl_sync(0xffffffffu, bx.y, sl);
-            b.z = __shfl_sync(0xffffffffu, bx.z, sl); b.w = __shfl_sync(0xffffffffu, bx.w, sl);
-            const int2 oo = make_int2(__shfl_sync(0xffffffffu, o.x, sl), __shfl_sync(0xffffffffu, o.y, sl));
-            ft_source(a, ee >> 6, ee & 63, b, oo, __shfl_sync(0xffffffffu, fl, sl), q, lane, wtab, lam, issued);
-          }
+        }
+        const unsigned vm = __ballot_sync(0xffffffffu, valid);
+        const int nv = __popc(vm);
+        const int rk = __popc(vm & ((1u << lane) - 1u));         // lane order = source order (sorted list / scan)
+        for (int r = 0; r < nv; ++r) {
+          const unsigned m = __ballot_sync(0xffffffffu, valid && rk == r);
+          const int sl = __ffs(m) - 1;
+          const int ee = __shfl_sync(0xffffffffu, e, sl);
+          int4 b;
+          b.x = __shfl_sync(0xffffffffu, bx.x, sl); b.y = __shfl_sync(0xffffffffu, bx.y, sl);
+          b.z = __shfl_sync(0xffffffffu, bx.z, sl); b.w = __shfl_sync(0xffffffffu, bx.w, sl);
+          const int2 oo = make_int2(__shfl_sync(0xffffffffu, o.x, sl), __shfl_sync(0xffffffffu, o.y, sl));
+          ft_source(a, ee >> 6, ee & 63, b, oo, __shfl_sync(0xffffffffu, fl, sl), q, lane, wtab, lam, issued);
         }
       }
 
       if (!have_nx) e_nx = __shfl_sync(0xffffffffu, dnext.x, 0) >= 0 ? list_entry(__shfl_sync(0xffffffffu, dnext.y, 0)) : 0x7fffffff;
-      // Poisson terms.  log(lam) = ln 2 lg2(lam r) - ln r with r = fl(1 / eps): lam r is close to 1 on the
-      // sky-dominated pixels, where lg2.approx is accurate to ~1e-7 ABSOLUTE, so sum x lg2(lam r) can be kept
-      // in fp32 per lane (8 pixels); the dominant term sum x (-ln r) takes the exact sum of the counts and
-      // the float64 logarithm of the ROUNDED r, so the rounding of r cancels.  3 instructions per pixel
-      // (FMUL, MUFU.LG2, FFMA); the float64 table logarithm it replaces cost ~20.
-      const float r_eps = (eps > 0.f) ? __frcp_rn(eps) : 1.f;
-      float s2 = 0.f;
-      double sd = 0.0, slam = 0.0;
+      // Poisson terms.  log(lam) = T[bin] + res (log_accurate): sum x T in float64,
+      // sum x res (|res| < 1/60) and the 4-pixel row sums of lam in fp32, then float64
+      float sres = 0.f;
+      double slam = 0.0;
+      if (q.x + 3 < W && q.yB < H) {                          // interior lane: no bounds tests
 #pragma unroll
-      for (int r = 0; r < 2; ++r) {
-        const int y = r ? q.yB : q.yA;
-        float lr[4];
+        for (int r = 0; r < 2; ++r) {
 #pragma unroll
-        for (int p = 0; p < 4; ++p) {
-          s2 = fmaf(d[r][p], lg2_approx(lam[r][p] * r_eps), s2);     // d = 0 outside the image
-          lr[p] = (y < H && q.x + p < W) ? lam[r][p] : 0.f;
+          for (int p = 0; p < 4; ++p) {
+            s = fma((double)d[r][p], log_table(lam[r][p], logt), s);
+            sres = fmaf(d[r][p], log_residual(lam[r][p]), sres);
+          }
+          slam += (double)((lam[r][0] + lam[r][1]) + (lam[r][2] + lam[r][3]));
         }
-        sd += ((double)d[r][0] + (double)d[r][1]) + ((double)d[r][2] + (double)d[r][3]);
-        slam += (double)((lr[0] + lr[1]) + (lr[2] + lr[3]));
-      }
-      if (mdl) {
-        if (q.x + 3 < W && q.yB < H && ((W & 3) == 0) && (((uintptr_t)mdl & 15) == 0)) {
-          *reinterpret_cast<float4*>(mdl + (long long)q.yA * W + q.x) = make_float4(lam[0][0], lam[0][1], lam[0][2], lam[0][3]);
-          *reinterpret_cast<float4*>(mdl + (long long)q.yB * W + q.x) = make_float4(lam[1][0], lam[1][1], lam[1][2], lam[1][3]);
-        } else {
+        if (mdl) {
+          float* m0 = mdl + (long long)q.yA * W + q.x;
+          float* m1 = mdl + (long long)q.yB * W + q.x;
+          if (((W & 3) == 0) && (((uintptr_t)mdl & 15) == 0)) {
+            *reinterpret_cast<float4*>(m0) = make_float4(lam[0][0], lam[0][1], lam[0][2], lam[0][3]);
+            *reinterpret_cast<float4*>(m1) = make_float4(lam[1][0], lam[1][1], lam[1][2], lam[1][3]);
+          } else {
 #pragma unroll
-          for (int r = 0; r < 2; ++r) {
-            const int y = r ? q.yB : q.yA;
+            for (int p = 0; p < 4; ++p) { m0[p] = lam[0][p]; m1[p] = lam[1][p]; }
+          }
+        }
+      } else {
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+          const int y = r ? q.yB : q.yA;
+          if (y < H) {
 #pragma unroll
             for (int p = 0; p < 4; ++p)
-              if (y < H && q.x + p < W) mdl[(long long)y * W + q.x + p] = lam[r][p];
+              if (q.x + p < W) {
+                s = fma((double)d[r][p], log_table(lam[r][p], logt), s);
+                sres = fmaf(d[r][p], log_residual(lam[r][p]), sres);
+                slam += (double)lam[r][p];
+                if (mdl) mdl[(long long)y * W + q.x + p] = lam[r][p];
+              }
           }
         }
       }
-      // -ln r in float64 from the rounded r (eps <= 0: r = 1, the logarithm of lam itself)
-      const double l0 = (eps > 0.f) ? -log_accurate(r_eps, logt) : 0.0;
-      s = fma(sd, l0, fma((double)s2, LN2_D, -slam));
+      s += (double)sres - slam;
     }
     s = warp_sum(s);
     if (lane == 0) a.block_partials[g] = s;
@@ -2522,7 +2372,7 @@ static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; 
 
 struct WsLayout {
   size_t counters, hdr, tab, worklist, partials, item_ll, img_boxes, aux_offsets, tiles;
-  size_t tile_count, done, tile_list, tile_mask, model_ptrs;   // full-field gather (tile_count and done are contiguous)
+  size_t tile_count, done, tile_list, model_ptrs;   // full-field gather (tile_count and done are contiguous)
   size_t tile_zero_bytes, order;
   // second pass (float64 re-score)
   size_t counters2, hdr2, tab2, worklist2, partials2, item_ll2, guard_list;
@@ -2546,7 +2396,7 @@ static WsLayout ws_layout(long long n_items, long long max_patch_px, int with_pa
   L.worklist_cap = (int)cap;
   L.counters = take(sizeof(Counters));
   L.hdr = take(sizeof(ItemHdr) * n_items);
-  L.tab = take((size_t)TAB_BYTES * n_items);
+  L.tab = take(sizeof(float) * TAB_STRIDE * n_items);
   L.worklist = take(sizeof(int2) * (size_t)L.worklist_cap);
   L.partials = take(sizeof(double) * (size_t)L.worklist_cap);
   L.item_ll = take(sizeof(double) * n_items);
@@ -2558,7 +2408,6 @@ static WsLayout ws_layout(long long n_items, long long max_patch_px, int with_pa
     L.done = take(sizeof(int) * CG_MAX_IMAGES);
     L.tile_zero_bytes = (L.done + sizeof(int) * CG_MAX_IMAGES) - L.tile_count;
     L.tile_list = take(sizeof(int) * (size_t)n_tiles_total * BINS_PER_TILE * BIN_CAP);
-    L.tile_mask = take(sizeof(unsigned long long) * (size_t)n_tiles_total * BINS_PER_TILE * BIN_CAP);
     L.order = take(sizeof(int2) * (size_t)n_tiles_total * BINS_PER_TILE * FT_BUCKETS);
     L.model_ptrs = take(sizeof(float*) * CG_MAX_IMAGES);
   }
@@ -2571,7 +2420,7 @@ static WsLayout ws_layout(long long n_items, long long max_patch_px, int with_pa
     L.worklist_cap2 = (int)cap2;
     L.counters2 = take(sizeof(Counters));
     L.hdr2 = take(sizeof(ItemHdr) * L.n_items2);
-    L.tab2 = take((size_t)TAB_BYTES * L.n_items2);
+    L.tab2 = take(sizeof(double) * TAB_STRIDE * L.n_items2);
     L.worklist2 = take(sizeof(int2) * (size_t)L.worklist_cap2);
     L.partials2 = take(sizeof(double) * (size_t)L.worklist_cap2);
     L.item_ll2 = take(sizeof(double) * L.n_items2);
@@ -3047,14 +2896,13 @@ static int field_setup(CgImage* const* imgs, const int32_t* h_img_off, const CgS
   pa.filters = g_d_filters; pa.flux_table = g_flux_table; pa.flux_rows = g_flux_rows;
   pa.out_boxes = d_out_boxes; pa.cap_boxes = d_out_boxes != nullptr;
   pa.tile_count = (int*)(base + L.tile_count); pa.tile_list = (int*)(base + L.tile_list);
-  pa.tile_mask = (unsigned long long*)(base + L.tile_mask); pa.cull = g_cull | (g_recur ? 0 : 2);
   const int max_bins = max_tiles * BINS_PER_TILE;
   pa.max_tiles = max_bins;
   pa.bin_w = BIN_W; pa.bin_h = BIN_H; pa.bin_cap = BIN_CAP;
   rc = run_prepare<float>(pa, st);
   if (rc) return rc;
   fa.imgs = pa.imgs; fa.n_img = n_img; fa.hdr = pa.hdr; fa.tab = (const float*)pa.tab;
-  fa.tile_count = pa.tile_count; fa.tile_list = pa.tile_list; fa.tile_mask = pa.tile_mask;
+  fa.tile_count = pa.tile_count; fa.tile_list = pa.tile_list;
   fa.order = (int2*)(base + L.order); fa.sched = (int*)(base + L.done);
   fa.block_partials = (double*)(base + L.tiles);
   fa.max_tiles = max_bins; fa.tiles_total = max_bins * n_img;
