@@ -17,20 +17,16 @@ def _gmm_device(x, ws, mus, sigs):
 
 
 def mog_loglike(x, means, icovs, dets, pis):
-    """mog.py:5-21: log sum_k pi_k N(x; mu_k, C_k) at the rows of x.  The
-    reference takes inverse covariances and determinants; the device kernel
-    takes covariances, recovered here in closed form (2x2)."""
+    """mog.py:5-21: logsumexp_k[-1/2 d^T icov_k d - log 2 pi - 1/2 log det_k + log pi_k] at the rows
+    of x, as written (inverse covariances and determinants in, log-density out).  Evaluated by the
+    float64 log-space kernel (cg_mog_logpdf), so the far tails stay finite exactly where the
+    reference's logsumexp does (a density evaluated as log(sum exp) underflows to -inf there)."""
     x = np.asarray(x, dtype=np.float64)
     xx = np.atleast_2d(x)
     icovs = np.asarray(icovs, dtype=np.float64)
     if xx.shape[1] != 2 or icovs.shape[1:] != (2, 2):
         raise ValueError("must be two-dimensional!")
-    idet = icovs[:, 0, 0] * icovs[:, 1, 1] - icovs[:, 0, 1] * icovs[:, 1, 0]
-    covs = np.empty_like(icovs)
-    covs[:, 0, 0], covs[:, 1, 1] = icovs[:, 1, 1] / idet, icovs[:, 0, 0] / idet
-    covs[:, 0, 1], covs[:, 1, 0] = -icovs[:, 0, 1] / idet, -icovs[:, 1, 0] / idet
-    with np.errstate(divide="ignore"):
-        lp = np.log(_gmm_device(xx, pis, means, covs))
+    lp = engine.mog_logpdf(xx, means, icovs, dets, pis)
     return lp[0] if x.ndim == 1 else lp
 
 
@@ -64,13 +60,8 @@ class MixtureOfGaussians(object):
             self.chols = np.array([np.linalg.cholesky(c) for c in covs])
 
     def logpdf(self, x):
-        x = np.asarray(x, dtype=np.float64)
-        if self.D != 2:
-            # priors (D = 1, 3, 5): float64 mog_loglike on the device, :61-63 -> :5-21
-            return engine.mog_logpdf(x, self.means, self.icovs, self.dets, self.pis)
-        with np.errstate(divide="ignore"):
-            lp = np.log(_gmm_device(np.atleast_2d(x), self.pis, self.means, self.covs))
-        return lp[0] if x.ndim == 1 else lp
+        # :59-61 -> mog_loglike (:5-21): float64 log-space kernel for every D (finite far tails)
+        return engine.mog_logpdf(np.asarray(x, dtype=np.float64), self.means, self.icovs, self.dets, self.pis)
 
     def responsibilities(self, x):
         """logpdf and r_nk = p(k | x_n) (device tensor [N, K]) -- the E-step of

@@ -15,8 +15,18 @@ def slicesample_gen(init_x, **slice_sample_args):
     One code path serves the sequential driver (slicesample) and the lock-step
     driver (run_lockstep: many chains, one batched device launch per round).
     `rng` (keyword) supplies rand / randn / shuffle; default numpy.random, the
-    reference's global stream."""
+    reference's global stream.
+
+    Guard band (keywords `refine`, `guard`; no reference analogue -- the reference's logprob is
+    float64): the device likelihoods are fp32-rate sums, good to ~1e-3 absolute.  Every comparison of
+    a likelihood with the slice level that falls within `guard` of a tie is decided again with
+    refine(x), a float64 evaluation of the same likelihood (level and value both), so that a chain
+    takes the float64 reference's decisions by construction, not by margin.  `n_refined` (a one-element
+    list, keyword) counts the refinements."""
     rng = slice_sample_args.get('rng', None) or npr
+    refine = slice_sample_args.get('refine', None)
+    guard = slice_sample_args.get('guard', 0.0) if refine is not None else 0.0
+    n_refined = slice_sample_args.get('n_refined', None)
     sigma = slice_sample_args.get('sigma', 1.0)
     step_out = slice_sample_args.get('step_out', True)
     max_steps_out = slice_sample_args.get('max_steps_out', 1000)
@@ -30,6 +40,18 @@ def slicesample_gen(init_x, **slice_sample_args):
         def at(z):
             return direction * z + init_x
 
+        level = {}      # float64 slice level, computed on the first near-tie of this direction
+
+        def above(val, z, llh_s):
+            """val > llh_s, decided in float64 when the two are within the guard band"""
+            if guard > 0. and abs(val - llh_s) < guard:
+                if 'exact' not in level:
+                    level['exact'] = level['log_u'] + refine(at(0.0))
+                if n_refined is not None:
+                    n_refined[0] += 1
+                return refine(at(z)) > level['exact']
+            return val > llh_s
+
         def acceptable(z, llh_s, L, U):
             while (U - L) > 1.1 * sigma:
                 middle = 0.5 * (L + U)
@@ -39,22 +61,23 @@ def slicesample_gen(init_x, **slice_sample_args):
                 else:
                     L = middle
                 if splits:                       # `and` chain of the reference, short-circuit kept
-                    if llh_s >= (yield at(U)):
-                        if llh_s >= (yield at(L)):
+                    if not above((yield at(U)), U, llh_s):
+                        if not above((yield at(L)), L, llh_s):
                             return False
             return True
 
         upper = sigma * rng.rand()
         lower = upper - sigma
-        llh_s = np.log(rng.rand()) + (yield at(0.0))
+        level['log_u'] = np.log(rng.rand())
+        llh_s = level['log_u'] + (yield at(0.0))
         l_steps_out = 0
         u_steps_out = 0
         if step_out:
             if doubling_step:
                 while True:
-                    out = (yield at(lower)) > llh_s
+                    out = above((yield at(lower)), lower, llh_s)
                     if not out:
-                        out = (yield at(upper)) > llh_s
+                        out = above((yield at(upper)), upper, llh_s)
                     if not (out and (l_steps_out + u_steps_out) < max_steps_out):
                         break
                     if rng.rand() < 0.5:
@@ -64,10 +87,10 @@ def slicesample_gen(init_x, **slice_sample_args):
                         u_steps_out += 1
                         upper += (upper - lower)
             else:
-                while (yield at(lower)) > llh_s and l_steps_out < max_steps_out:
+                while above((yield at(lower)), lower, llh_s) and l_steps_out < max_steps_out:
                     l_steps_out += 1
                     lower -= sigma
-                while (yield at(upper)) > llh_s and u_steps_out < max_steps_out:
+                while above((yield at(upper)), upper, llh_s) and u_steps_out < max_steps_out:
                     u_steps_out += 1
                     upper += sigma
         start_upper, start_lower = upper, lower
@@ -76,7 +99,7 @@ def slicesample_gen(init_x, **slice_sample_args):
             new_llh = yield at(new_z)
             if np.isnan(new_llh):
                 raise Exception("Slice sampler got a NaN")
-            if new_llh > llh_s and (yield from acceptable(new_z, llh_s, start_lower, start_upper)):
+            if above(new_llh, new_z, llh_s) and (yield from acceptable(new_z, llh_s, start_lower, start_upper)):
                 break
             elif new_z < 0:
                 lower = new_z

@@ -134,19 +134,24 @@ class Source(object):
             u=p.u if u is None else u, a=p.a, theta=th[0], sigma=th[1], phi=th[2], rho=th[3],
             fluxes=fluxes_of(p) if fluxes is None else np.asarray(fluxes, dtype=np.float64))])
 
-    def log_likelihood(self, u=None, fluxes=None, shape=None):
-        """:134-183, all sampled images of the source in one launch."""
+    def log_likelihood(self, u=None, fluxes=None, shape=None, fp64=False):
+        """:134-183, all sampled images of the source in one launch.  fp64: float64 tables,
+        exponentials and logarithms on the device (the guard-band evaluation of the samplers)."""
         f = fluxes_of(self.params) if fluxes is None else np.asarray(fluxes)
         assert np.all(~np.isnan(f)), 'passing in NAN fluxes.'
         c = self._sample_cache()
         if not c["imgs"]:
             return 0
         ll, _ = engine.items_loglik(c["imgs"], self._record(u, fluxes, shape), c["items_cond"],
-                                    mode=_ffi.CG_LL_CONDITIONAL, aux=c["aux"], aux_offsets=c["offs"])
+                                    mode=_ffi.CG_LL_CONDITIONAL, aux=c["aux"], aux_offsets=c["offs"],
+                                    use_fp64=fp64)
         return float(ll.sum().item())
 
     def location_likelihood(self, u):
         return self.log_likelihood(u=u)
+
+    #: |likelihood - slice level| below which the slice sampler decides in float64 (slicesample_gen)
+    slice_guard = 1e-2
 
     def log_likelihood_isolated(self, u=None, fluxes=None, shape=None):
         """:188-237."""
@@ -198,8 +203,10 @@ class Source(object):
             (logprob_reverse - logprob_proposal) + logdet
 
     def _location_slice_args(self, rng=None):
+        self.n_refined = [0]
         return dict(step=self.du / 5, step_out=False, upper_bound=self.u_upper,
-                    lower_bound=self.u_lower, rng=rng)
+                    lower_bound=self.u_lower, rng=rng, guard=self.slice_guard, n_refined=self.n_refined,
+                    refine=lambda u: self.log_likelihood(u=u, fp64=True))
 
     def resample_location(self, u=None, rng=None):
         """:308-319."""

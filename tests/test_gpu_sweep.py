@@ -190,3 +190,94 @@ def test_batched_resample_equals_per_source_resample(engine, oracle):
     # 12 chains shared their rounds: far fewer launches than 12 separate samplers need
     assert rounds == run_lockstep.last_rounds and launches <= 4 * (rounds + 2)
     print("lock-step rounds", rounds, "kernel launches", launches)
+
+
+def _oracle_chain_step(oracle, osrc, olist, oimgs, rng):
+    """One Source.resample() (sources.py:242-245) driven entirely by the oracle's float64 likelihoods:
+    resample_fluxes (:327-350, unit patches on the natural footprints as compat does) then
+    resample_location (:308-319) with the reference sampler's control flow."""
+    from desi_mcmc_b200.compat.slicesample import slicesample
+    a_0, b_0 = 5., .005
+    counts = np.zeros(5)
+    psf = np.zeros(5)
+    for (z, yl, xl, oi) in olist:
+        b = "ugriz".index(oi.band)
+        counts[b] += np.sum(z)
+        p, _, _ = oracle.compute_scatter_on_pixels(osrc, oi)
+        psf[b] += np.sum(p) * oi.kappa / oi.calib
+    osrc.fluxes = rng.gamma(a_0 + counts, 1. / (b_0 + psf))
+    n_eval = [0]
+
+    def ll(u):
+        n_eval[0] += 1
+        return oracle.source_log_likelihood(osrc, olist, u=u)
+    u, _ = slicesample(osrc.u.copy(), ll, step=None, step_out=False, upper_bound=osrc.u + 1.,
+                       lower_bound=osrc.u - 1., rng=rng)
+    osrc.u = u
+    return n_eval[0]
+
+
+def test_multi_sweep_trace_equals_oracle_driven_chain(engine, oracle):
+    """north_star: identical chain traces for the stated seeds.  Config 1 (star + galaxy, 25x25x5), photon
+    patches held fixed (the allocation is distributional, N1), 12 sweeps of resample_fluxes +
+    resample_location per source from RandomState(1001 + source): the device chain (per source, and all
+    sources in lock-step) against a chain driven by the oracle's float64 likelihoods.  Every slice-sampler
+    decision agrees BY CONSTRUCTION (near-ties are re-decided in float64 on the device, compat.slicesample
+    guard band), so the location traces -- functions of the uniforms alone once the decisions agree --
+    are equal to rounding, and the gamma-conditional fluxes to 1e-6."""
+    from desi_mcmc_b200.compat import sources as S
+    from desi_mcmc_b200.compat.celeste_sample_sources import NativePatch
+    from tests.test_gpu_compat import _Model, _stamp
+    field, gimgs, oimgs, gs, os_ = _stamp(engine, oracle, seed=1001, size=25, nseed=8)
+    prng = np.random.RandomState(5)
+    n_sweeps = 12
+    olists, chains = [], {"dev": [], "lock": []}
+    for si in (0, 1):
+        olist = []
+        for oi in oimgs:
+            p, yl, xl = oracle.gen_src_image_with_fluxes(os_[si], oi)
+            olist.append((prng.poisson(p).astype(np.float64), (int(yl[0]), int(yl[1])), (int(xl[0]), int(xl[1])), oi))
+        olists.append(olist)
+    for name in chains:
+        for si in (0, 1):
+            src = S.Source(hp.gpu_sources(engine, field)[si], _Model())
+            src.sample_image_list = [(NativePatch(z, yl, xl), gi, None) for (z, yl, xl, _), gi in zip(olists[si], gimgs)]
+            chains[name].append(src)
+    osrcs = hp.oracle_sources(oracle, field)
+    rng_o = [np.random.RandomState(1001 + si) for si in (0, 1)]
+    rng_d = [np.random.RandomState(1001 + si) for si in (0, 1)]
+    trace_o, trace_d, n_eval, n_ref = [], [], 0, 0
+    for k in range(n_sweeps):
+        for si in (0, 1):
+            n_eval += _oracle_chain_step(oracle, osrcs[si], olists[si], oimgs, rng_o[si])
+            chains["dev"][si].resample(rng=rng_d[si])
+            n_ref += chains["dev"][si].n_refined[0]
+        trace_o.append(np.concatenate([np.concatenate([o.u, o.fluxes]) for o in osrcs]))
+        trace_d.append(np.concatenate([np.concatenate([s.params.u, s.params.fluxes]) for s in chains["dev"]]))
+    trace_o, trace_d = np.array(trace_o), np.array(trace_d)
+    cols_u = [0, 1, 7, 8]
+    cols_f = [c for c in range(14) if c not in cols_u]
+    assert np.allclose(trace_d[:, cols_u], trace_o[:, cols_u], rtol=0, atol=1e-12)
+    assert np.allclose(trace_d[:, cols_f], trace_o[:, cols_f], rtol=1e-6, atol=0)
+    assert not np.allclose(trace_o[0, cols_u], trace_o[-1, cols_u], rtol=0, atol=1e-9)      # the chains moved
+    assert n_eval > 400                        # hundreds of slice decisions, each one agreed
+    # ... and the lock-step driver (one launch per round for all sources) walks the same trace
+    trace_l = []
+    for k in range(n_sweeps):
+        # resample_sources_batched seeds RandomState(seed + s) afresh: give it the chain's streams instead
+        from desi_mcmc_b200.compat.slicesample import run_lockstep, slicesample_gen
+        bc = S.BatchedConditional(chains["lock"])
+        sums = bc.unit_patch_sums()
+        if k == 0:
+            rng_l = [np.random.RandomState(1001 + si) for si in (0, 1)]
+        for src, rng, ps in zip(chains["lock"], rng_l, sums):
+            src.resample_fluxes(rng=rng, psf_sums_by_image=ps)
+        bc.refresh()
+        gens = [slicesample_gen(src.params.u.copy(), **src._location_slice_args(rng)) for src, rng in zip(chains["lock"], rng_l)]
+        for src, (u, ll) in zip(chains["lock"], run_lockstep(gens, bc.loglik)):
+            src.params.u = u
+        trace_l.append(np.concatenate([np.concatenate([s.params.u, s.params.fluxes]) for s in chains["lock"]]))
+    trace_l = np.array(trace_l)
+    assert np.allclose(trace_l[:, cols_u], trace_d[:, cols_u], rtol=0, atol=1e-13)
+    assert np.allclose(trace_l[:, cols_f], trace_d[:, cols_f], rtol=1e-12, atol=0)
+    print("oracle evaluations", n_eval, "float64 refinements on the device chain", n_ref)
