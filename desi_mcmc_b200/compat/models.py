@@ -82,6 +82,12 @@ class CelesteBase(object):
         from .sources import resample_sources_batched
         return resample_sources_batched(self.srcs, seed=seed)
 
+    def resample_sources_on_device(self, seed=0, rngs=None):
+        """resample_sources with every source's location slice sampler run on the device in ONE
+        launch (sources.resample_sources_on_device; bit-identical to the loops above)."""
+        from .sources import resample_sources_on_device
+        return resample_sources_on_device(self.srcs, seed=seed, rngs=rngs)
+
     # ---- model image / likelihood (:88-108) -----------------------------------
     def render_model_image(self, fimg, xlim=None, ylim=None, exclude=None):
         """epsilon + sum of the sources' model patches on fimg (full frame, or

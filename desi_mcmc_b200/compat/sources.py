@@ -412,3 +412,77 @@ def resample_sources_batched(srcs, seed=0):
     for src, (u, ll) in zip(srcs, res):
         src.params.u = u
     return run_lockstep.last_rounds
+
+
+def resample_sources_on_device(srcs, seed=0, rngs=None, n_uniforms=160):
+    """Source.resample() for every source with the location slice samplers run ON THE DEVICE
+    (cg_slice_sample_locations: one launch for all sources, however many shrink rounds they take;
+    SURVEY.md 8f N2).  Source s draws from rngs[s] (default RandomState(seed + s)) in the reference's
+    order: gamma conditionals of the fluxes, the coordinate shuffle, then the sampler's uniforms -- a
+    block of n_uniforms is handed to the device and the generator is advanced by exactly the number
+    consumed, so the stream continues as if the loop had run on the host.  A source the device flags
+    (block exhausted, comparison inside the float64 guard band, NaN) is redone by the lock-step host
+    sampler from the same generator state.  The result equals resample_sources_batched / the
+    per-source loop bit for bit.  -> dict(device=..., fallback=..., evals=...)."""
+    from .slicesample import run_lockstep, slicesample_gen
+    srcs = list(srcs)
+    for src in srcs:
+        assert len(src.sample_image_list) != 0, "resample source needs sampled images"
+    if rngs is None:
+        rngs = [np.random.RandomState(seed + s) for s in range(len(srcs))]
+    bc = BatchedConditional(srcs)
+    sums = bc.unit_patch_sums()
+    for src, rng, ps in zip(srcs, rngs, sums):
+        src.resample_fluxes(rng=rng, psf_sums_by_image=ps)
+    bc.refresh()
+    n_img = len(bc.imgs)
+    S = len(srcs)
+    uniform_layout = all(len(src.sample_image_list) == n_img and
+                         all(fi is bi for (_, fi, _), bi in zip(src.sample_image_list, bc.imgs)) for src in srcs)
+    if not uniform_layout or n_img > 8:
+        gens = [slicesample_gen(src.params.u.copy(), **src._location_slice_args(rng)) for src, rng in zip(srcs, rngs)]
+        for src, (u, ll) in zip(srcs, run_lockstep(gens, bc.loglik)):
+            src.params.u = u
+        return dict(device=0, fallback=S, evals=0)
+    # device layout: photon patches and boxes item-major with a common stride
+    stride = int(bc.max_patch_px)
+    photons = torch.zeros((S * n_img, stride), dtype=torch.float32, device=engine.device())
+    boxes = np.zeros(S * n_img, dtype=_ffi.BOX_DTYPE)
+    flat = bc.aux.cpu().numpy()
+    host = np.zeros((S * n_img, stride), dtype=np.float32)
+    for k in range(S * n_img):
+        bx = bc.items["box"][k]
+        n = int((bx[1] - bx[0]) * (bx[3] - bx[2]))
+        host[k, :n] = flat[bc.offs[k]:bc.offs[k] + n]
+        boxes[k] = tuple(int(v) for v in bx)
+    photons.copy_(torch.from_numpy(host))
+    before, after, order, uni = [], [], np.zeros((S, 2), dtype=np.int32), np.zeros((S, n_uniforms))
+    for s, rng in enumerate(rngs):
+        before.append(rng.get_state())
+        o = [0, 1]
+        rng.shuffle(o)                               # slicesample.py:228-230
+        order[s] = o
+        after.append(rng.get_state())
+        uni[s] = rng.random_sample(n_uniforms)
+    recs = bc.records()
+    d_srcs = engine.to_device(recs)
+    d_boxes = engine.to_device(boxes)
+    ll, used, status, evals = engine.slice_sample_locations(bc.imgs, d_srcs, S, d_boxes, photons, stride, uni, order,
+                                                            sigma=1.0, guard=Source.slice_guard)
+    new = d_srcs.cpu().numpy().view(_ffi.SRC_DTYPE)
+    redo = []
+    for s, (src, rng) in enumerate(zip(srcs, rngs)):
+        if status[s] == 0:
+            src.params.u = new["u"][s].copy()
+            rng.set_state(after[s])
+            rng.random_sample(int(used[s]))          # the draws the device consumed
+        else:
+            rng.set_state(before[s])
+            redo.append(s)
+    if redo:
+        sub = BatchedConditional([srcs[s] for s in redo])
+        sub.refresh()
+        gens = [slicesample_gen(srcs[s].params.u.copy(), **srcs[s]._location_slice_args(rngs[s])) for s in redo]
+        for s, (u, l) in zip(redo, run_lockstep(gens, sub.loglik)):
+            srcs[s].params.u = u
+    return dict(device=S - len(redo), fallback=len(redo), evals=int(evals.sum()), status=status)

@@ -421,54 +421,21 @@ __device__ double planck_photons_per_joule_warp(const FilterTables* f, double T,
   return warp_sum(acc);  // lane 0 holds the sum
 }
 
-// ---------------------------------------------------------------------------
-// prepare: one warp per item
-// ---------------------------------------------------------------------------
+// The float64 part of one (source, image) item, by one WARP: pixel position, galaxy transformation,
+// the convolved component table (rows written to `tab`: global memory in prepare_kernel, shared
+// memory in the on-device samplers) and the footprint radius.  prepare_kernel and
+// slice_location_kernel share it, so the tables -- and everything computed from them -- are
+// bit-identical on both paths.
+struct ItemGeom {
+  double px, py, bound, flux;
+  int K, ox, oy, err;
+  bool star, trunc_box;
+};
 template <typename real>
-__global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
-  const int lane = threadIdx.x & 31;
-  const long long i = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
-  if (i >= a.n_items) return;
-
-  CgItem it;
-  if (a.items) {
-    it = a.items[i];
-  } else if (a.implicit_mode == 0) {
-    it.src = (int)(i / a.n_img);
-    it.img = (int)(i % a.n_img);
-    it.flags = a.default_flags;
-    it.aux = -1;
-    it.box[0] = it.box[1] = it.box[2] = it.box[3] = 0;
-  } else if (a.implicit_mode == 3) {
-    int f = 0;
-    while (f + 1 < a.fb.n_fields && i >= a.fb.item_off[f + 1]) ++f;
-    const int local = (int)i - a.fb.item_off[f];
-    const int ni = a.fb.img_off[f + 1] - a.fb.img_off[f];
-    it.src = a.fb.src_off[f] + local / ni;
-    it.img = a.fb.img_off[f] + local % ni;
-    it.flags = a.default_flags;
-    it.aux = -1;
-    it.box[0] = it.box[1] = it.box[2] = it.box[3] = 0;
-  } else {
-    int g = (int)(i / a.n_img);
-    it.img = (int)(i % a.n_img);
-    if (a.implicit_mode == 2) {
-      int cnt = *a.ind_count;
-      if (g > cnt) return;
-      it.src = (g == 0) ? 0 : a.ind_list[g - 1];
-    } else {
-      it.src = g;
-    }
-    it.flags = a.default_flags | CG_ITEM_FIXED_BOX;
-    it.aux = a.aux_per_img ? it.img : -1;
-    const CgBox b = a.img_boxes[it.img];
-    it.box[0] = b.x0; it.box[1] = b.x1; it.box[2] = b.y0; it.box[3] = b.y1;
-  }
-
-  const DevImage& im = *a.imgs.p[it.img];
-  const CgSource& s = a.srcs[it.src];
+__device__ __forceinline__ ItemGeom item_table(const DevImage& im, const CgSource& s, int flags, int lane, real* tab) {
+  ItemGeom g;
+  g.err = 0;
   const int H = im.H, W = im.W;
-
   // v_s = image.equa2pixel(u)                       (fits_image.py:166-174)
   const double phi1rad = im.phi_n[1] / 180. * PI_D;
   const double iwc0 = (s.u[0] - im.phi_n[0]) * cos(phi1rad);
@@ -493,7 +460,7 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
   } else {
     // cd: FitsImage.cd_at_pixel (fits_image.py:196-216) or header CD
     double cd[4];
-    if (it.flags & CG_ITEM_HEADER_CD) {
+    if (flags & CG_ITEM_HEADER_CD) {
       cd[0] = im.ups[0]; cd[1] = im.ups[1]; cd[2] = im.ups[2]; cd[3] = im.ups[3];
     } else {
       double ra0, dec0, rax, decx, ray, decy;
@@ -519,16 +486,15 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
     Wm[0] = Ti[0] * Ti[0] + Ti[1] * Ti[1];
     Wm[1] = Ti[2] * Ti[2] + Ti[3] * Ti[3];
     Wm[2] = Ti[0] * Ti[2] + Ti[1] * Ti[3];
-    if (it.flags & CG_ITEM_PROF_EXP) { n_exp = 6; n_dev = 0; }
-    else if (it.flags & CG_ITEM_PROF_DEV) { n_exp = 0; n_dev = 8; }
+    if (flags & CG_ITEM_PROF_EXP) { n_exp = 6; n_dev = 0; }
+    else if (flags & CG_ITEM_PROF_DEV) { n_exp = 0; n_dev = 8; }
     else { n_exp = 6; n_dev = 8; th_exp = s.theta; th_dev = 1. - s.theta; }
     K = (n_exp + n_dev) * n_psf;
-    trunc_box = (it.flags & CG_ITEM_TRUNC_BOX) != 0;
+    trunc_box = (flags & CG_ITEM_TRUNC_BOX) != 0;
   }
 
   const int ox = (int)rint(px), oy = (int)rint(py);
   const double Rsq_gal = 23.025850929940457;  // chi2.ppf(1 - 1e-5, 2)
-  real* tab = reinterpret_cast<real*>(a.tab) + i * TAB_STRIDE;
 
   double mybound = -1e300;
   for (int c = lane; c < K; c += 32) {
@@ -583,6 +549,97 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
     bound = warp_max(mybound);
     if (K == 0) bound = 0;
   }
+  g.px = px; g.py = py; g.bound = bound; g.K = K; g.ox = ox; g.oy = oy; g.star = star; g.trunc_box = trunc_box;
+  g.flux = 0.0;
+  return g;
+}
+
+// rate multiplier of an item (celeste.py:38-45,80-81,91-92; planck.py:155-158), by one warp
+__device__ __forceinline__ double item_flux(const DevImage& im, const CgSource& s, int flags, int lane, bool star,
+                                            const FilterTables* filters, const double* flux_table,
+                                            long long flux_rows, ItemGeom& g) {
+  // flux (celeste.py:38-45,80-81,91-92; planck.py:155-158)
+  double flux;
+  if (flags & CG_ITEM_FLUX_UNIT) {
+    flux = 1.0;
+  } else if (s.flags & CG_SRC_EIGEN) {
+    // eigen-spectrum route: the band flux was projected on the device (eigen_flux_kernel) and is read
+    // from HBM here -- redshift_utils.py:304-323 feeding celeste.py:80-81,91-92
+    if (flux_table && s.flux_row >= 0 && s.flux_row < flux_rows) {
+      flux = (flux_table[s.flux_row * CG_NUM_BANDS + im.band] / im.calib) * im.kappa;
+    } else {
+      flux = (double)NAN;
+      g.err = 4;
+    }
+  } else if (star && (s.flags & CG_SRC_PLANCK) && s.t != 0.0) {
+    double ppj = planck_photons_per_joule_warp(filters, s.t, im.band, lane);
+    ppj = __shfl_sync(0xffffffffu, ppj, 0);
+    const double c_ = 299792458.0;
+    const double m_per_ly = c_ * 31556952.;
+    const double lens_area = .75 * PI_D * (1.25 * 1.25);
+    double lens_watts = lens_area * s.b * (3.846 * 1e26) / (m_per_ly * m_per_ly);
+    flux = ppj * lens_watts * 54.;
+  } else {
+    flux = (s.flux[im.band] / im.calib) * im.kappa;
+  }
+
+  return flux;
+}
+
+// ---------------------------------------------------------------------------
+// prepare: one warp per item
+// ---------------------------------------------------------------------------
+template <typename real>
+__global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
+  const int lane = threadIdx.x & 31;
+  const long long i = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (i >= a.n_items) return;
+
+  CgItem it;
+  if (a.items) {
+    it = a.items[i];
+  } else if (a.implicit_mode == 0) {
+    it.src = (int)(i / a.n_img);
+    it.img = (int)(i % a.n_img);
+    it.flags = a.default_flags;
+    it.aux = -1;
+    it.box[0] = it.box[1] = it.box[2] = it.box[3] = 0;
+  } else if (a.implicit_mode == 3) {
+    int f = 0;
+    while (f + 1 < a.fb.n_fields && i >= a.fb.item_off[f + 1]) ++f;
+    const int local = (int)i - a.fb.item_off[f];
+    const int ni = a.fb.img_off[f + 1] - a.fb.img_off[f];
+    it.src = a.fb.src_off[f] + local / ni;
+    it.img = a.fb.img_off[f] + local % ni;
+    it.flags = a.default_flags;
+    it.aux = -1;
+    it.box[0] = it.box[1] = it.box[2] = it.box[3] = 0;
+  } else {
+    int g = (int)(i / a.n_img);
+    it.img = (int)(i % a.n_img);
+    if (a.implicit_mode == 2) {
+      int cnt = *a.ind_count;
+      if (g > cnt) return;
+      it.src = (g == 0) ? 0 : a.ind_list[g - 1];
+    } else {
+      it.src = g;
+    }
+    it.flags = a.default_flags | CG_ITEM_FIXED_BOX;
+    it.aux = a.aux_per_img ? it.img : -1;
+    const CgBox b = a.img_boxes[it.img];
+    it.box[0] = b.x0; it.box[1] = b.x1; it.box[2] = b.y0; it.box[3] = b.y1;
+  }
+
+  const DevImage& im = *a.imgs.p[it.img];
+  const CgSource& s = a.srcs[it.src];
+  const int H = im.H, W = im.W;
+
+  real* tab = reinterpret_cast<real*>(a.tab) + i * TAB_STRIDE;
+  ItemGeom geo = item_table<real>(im, s, it.flags, lane, tab);
+  const double px = geo.px, py = geo.py;
+  const int K = geo.K, ox = geo.ox, oy = geo.oy;
+  const bool star = geo.star, trunc_box = geo.trunc_box;
+  double bound = geo.bound;
   if (a.bound_cap > 0) bound = fmin(bound, a.bound_cap);
 
   int x0, x1, y0, y1;
@@ -605,30 +662,8 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
   // max_patch_px; the fused field path (no work list) clips the footprint to the image and is done
   if ((a.worklist != nullptr || a.cap_boxes) && npx > a.max_patch_px) { err = 1; x1 = x0; y1 = y0; npx = 0; }
 
-  // flux (celeste.py:38-45,80-81,91-92; planck.py:155-158)
-  double flux;
-  if (it.flags & CG_ITEM_FLUX_UNIT) {
-    flux = 1.0;
-  } else if (s.flags & CG_SRC_EIGEN) {
-    // eigen-spectrum route: the band flux was projected on the device (eigen_flux_kernel) and is read
-    // from HBM here -- redshift_utils.py:304-323 feeding celeste.py:80-81,91-92
-    if (a.flux_table && s.flux_row >= 0 && s.flux_row < a.flux_rows) {
-      flux = (a.flux_table[s.flux_row * CG_NUM_BANDS + im.band] / im.calib) * im.kappa;
-    } else {
-      flux = (double)NAN;
-      err = 4;
-    }
-  } else if (star && (s.flags & CG_SRC_PLANCK) && s.t != 0.0) {
-    double ppj = planck_photons_per_joule_warp(a.filters, s.t, im.band, lane);
-    ppj = __shfl_sync(0xffffffffu, ppj, 0);
-    const double c_ = 299792458.0;
-    const double m_per_ly = c_ * 31556952.;
-    const double lens_area = .75 * PI_D * (1.25 * 1.25);
-    double lens_watts = lens_area * s.b * (3.846 * 1e26) / (m_per_ly * m_per_ly);
-    flux = ppj * lens_watts * 54.;
-  } else {
-    flux = (s.flux[im.band] / im.calib) * im.kappa;
-  }
+  const double flux = item_flux(im, s, it.flags, lane, star, a.filters, a.flux_table, a.flux_rows, geo);
+  if (geo.err) err = geo.err;
 
   const int wbox = x1 - x0, hbox = y1 - y0;
   const int cpr = (wbox + PIX_PER_THREAD - 1) / PIX_PER_THREAD;
@@ -815,6 +850,146 @@ __device__ __forceinline__ int cull_components(const float* gtab, int K, int lan
   return __popc(m0) + __popc(m1);
 }
 
+// One WARP TILE (32 lane units = 256 pixels) of an item: cull the item's components against the
+// tile, evaluate, and either write the patch (MODE_PATCH) or return the tile's likelihood terms summed
+// over the warp (lane 0 holds the sum).  Shared by render_kernel and the on-device samplers.
+template <typename real, int MODE>
+__device__ __forceinline__ double render_warp_tile(const RenderArgs& a, const ItemHdr& h, long long item,
+                                                   const real* s_tab, float* s_wtab, int wt, int lane, int wbox,
+                                                   int hbox, int cpr, int hp, int n_lu, float r_band,
+                                                   const DevImage* imp, real fl, const LogTable* logt,
+                                                   unsigned long long& issued) {
+  const int q = wt * 32 + lane;
+  const bool active = q < n_lu;
+  int row0 = 0, row1 = 0, cx = 0;
+  if (active) unit_decode(q, cpr, hp, r_band, &row0, &row1, &cx);
+  const bool two = active && row1 < hbox;
+  const int npx = active ? min(PIX_PER_THREAD, wbox - cx) : 0;
+
+  int n = h.K;
+  const real* tb = s_tab;
+  int stride = TAB_W;
+  bool recur = false;
+  if (sizeof(real) == 4 && (a.cull & 1) && n > 1) {
+    const int rmin = __reduce_min_sync(0xffffffffu, active ? row0 : 0x7fffffff);
+    const int rmax = __reduce_max_sync(0xffffffffu, active ? (two ? row1 : row0) : -1);
+    const int cmin = __reduce_min_sync(0xffffffffu, active ? cx : 0x7fffffff);
+    const int cmax = __reduce_max_sync(0xffffffffu, active ? cx + npx - 1 : -1);
+    __syncwarp();             // the warp is done reading the culled table of the previous tile
+    n = cull_components<false>(reinterpret_cast<const float*>(s_tab), n, lane,
+                               (float)(h.x0 + cmin - h.ox), (float)(h.x0 + cmax - h.ox),
+                               (float)(h.y0 + rmin - h.oy), (float)(h.y0 + rmax - h.oy), 0.f, s_wtab, &recur);
+    recur = recur && FT_RECUR && !(a.cull & 2);
+    tb = reinterpret_cast<const real*>(s_wtab);
+    stride = 8;
+  }
+  if (lane == 0) issued += (unsigned long long)n * WT_PIX;
+
+  real acc0[PIX_PER_THREAD], acc1[PIX_PER_THREAD];
+#pragma unroll
+  for (int p = 0; p < PIX_PER_THREAD; ++p) { acc0[p] = (real)0; acc1[p] = (real)0; }
+  {
+    const real y0l = (real)(h.y0 + row0 - h.oy), y1l = (real)(h.y0 + row1 - h.oy);
+    const real xl0 = (real)(h.x0 + cx - h.ox);
+    real xl[PIX_PER_THREAD];
+#pragma unroll
+    for (int p = 0; p < PIX_PER_THREAD; ++p) xl[p] = xl0 + (real)p;
+    if (sizeof(real) == 4 && recur) {
+      // row recurrence: 2 exp2 per row of 4 pixels (the rows of a lane are not a fixed
+      // distance apart here, so each row takes its own neighbour ratio)
+      const real tx = (real)2 * xl0 + (real)1;
+#if FT_PACKED
+      f32x2 pacc[PIX_PER_THREAD];         // (row0, row1) pairs: FMUL2 / FADD2, see ft_eval2r
+#pragma unroll
+      for (int p = 0; p < PIX_PER_THREAD; ++p) pacc[p] = pk2(0.f, 0.f);
+#endif
+#pragma unroll 2
+      for (int k = 0; k < n; ++k, tb += 8) {
+        const real A = tb[0], B = tb[1], C = tb[2], b10 = tb[3], c01 = tb[4], c00 = tb[5], hh = tb[6];
+        const real b1a = rfma(B, y0l, b10), b1b = rfma(B, y1l, b10);
+        const real c1a = rfma(rfma(C, y0l, c01), y0l, c00);
+        const real c1b = rfma(rfma(C, y1l, c01), y1l, c00);
+        const real ea = rexp2(rfma(rfma(A, xl0, b1a), xl0, c1a)), ga = rexp2(rfma(A, tx, b1a));
+        const real eb = rexp2(rfma(rfma(A, xl0, b1b), xl0, c1b)), gb = rexp2(rfma(A, tx, b1b));
+#if FT_PACKED
+        recur_row4x2(pk2((float)ea, (float)eb), pk2((float)ga, (float)gb), pk2((float)hh, (float)hh), pacc);
+#else
+        recur_row4(ea, ga, hh, acc0);
+        recur_row4(eb, gb, hh, acc1);
+#endif
+      }
+#if FT_PACKED
+#pragma unroll
+      for (int p = 0; p < PIX_PER_THREAD; ++p) {
+        float lo, hi;
+        unpk2(pacc[p], lo, hi);
+        acc0[p] = (real)lo; acc1[p] = (real)hi;
+      }
+#endif
+      n = 0;
+    }
+#pragma unroll 2
+    for (int k = 0; k < n; ++k, tb += stride) {
+      const real A = tb[0], B = tb[1], C = tb[2], b10 = tb[3], c01 = tb[4], c00 = tb[5];
+      const real b1a = rfma(B, y0l, b10), b1b = rfma(B, y1l, b10);
+      const real c1a = rfma(rfma(C, y0l, c01), y0l, c00);
+      const real c1b = rfma(rfma(C, y1l, c01), y1l, c00);
+#pragma unroll
+      for (int p = 0; p < PIX_PER_THREAD; ++p) {
+        acc0[p] += rexp2(rfma(rfma(A, xl[p], b1a), xl[p], c1a));
+        acc1[p] += rexp2(rfma(rfma(A, xl[p], b1b), xl[p], c1b));
+      }
+    }
+  }
+
+  if (MODE == MODE_PATCH) {
+    if (active) {
+      float* out = a.patches + (long long)item * a.max_patch_px + (long long)row0 * wbox + cx;
+#pragma unroll
+      for (int p = 0; p < PIX_PER_THREAD; ++p)
+        if (p < npx) out[p] = (float)(acc0[p] * fl);
+      if (two) {
+        out += (long long)(row1 - row0) * wbox;
+#pragma unroll
+        for (int p = 0; p < PIX_PER_THREAD; ++p)
+          if (p < npx) out[p] = (float)(acc1[p] * fl);
+      }
+    }
+  } else {
+    double s = 0.0;
+    if (active) {
+      const DevImage& im = *imp;
+      const real eps = (real)im.epsilon;
+      const bool use_mask = im.mask && !(h.flags & CG_ITEM_NO_MASK);
+#pragma unroll
+      for (int rr = 0; rr < 2; ++rr) {
+        if (rr == 1 && !two) break;
+        const int row = rr ? row1 : row0;
+        const long long poff = (long long)row * wbox + cx;
+        const float* auxp = (h.aux >= 0) ? a.aux + (a.aux_offsets ? a.aux_offsets[h.aux] : (a.aux_stride ? (long long)h.aux * a.aux_stride : a.aux_off_v[h.aux])) + poff : nullptr;
+        const long long ioff = (long long)(h.y0 + row) * im.W + (h.x0 + cx);
+#pragma unroll
+        for (int p = 0; p < PIX_PER_THREAD; ++p) {
+          if (p < npx) {
+            const real v = fl * (rr ? acc1[p] : acc0[p]);
+            if (MODE == MODE_POISSON) {
+              const real lam = (auxp ? (real)auxp[p] : eps) + v;
+              const bool good = (lam > (real)0) && (!use_mask || im.mask[ioff + p] != 0.f);
+              if (good) s += (double)im.nelec[ioff + p] * log_accurate(lam, logt) - (double)lam;
+            } else {      // MODE_COND, sources.py:171-174
+              if (v >= (real)1.17549435e-38f) s += log_accurate(v, logt) * (double)auxp[p];
+              if (a.cond_sum) s -= (double)v;     // celeste_galaxy_conditionals.py:41
+            }
+          }
+        }
+      }
+    }
+    s = warp_sum(s);
+    return s;
+  }
+  return 0.0;
+}
+
 template <typename real, int MODE>
 __global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
   // per-warp staging: the item's component table and the culled, compacted table
@@ -859,134 +1034,9 @@ __global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
 
 #pragma unroll 1
     for (int wt = wt0; wt < wt_end; ++wt) {
-      const int q = wt * 32 + lane;
-      const bool active = q < n_lu;
-      int row0 = 0, row1 = 0, cx = 0;
-      if (active) unit_decode(q, cpr, hp, r_band, &row0, &row1, &cx);
-      const bool two = active && row1 < hbox;
-      const int npx = active ? min(PIX_PER_THREAD, wbox - cx) : 0;
-
-      int n = h.K;
-      const real* tb = s_tab;
-      int stride = TAB_W;
-      bool recur = false;
-      if (sizeof(real) == 4 && (a.cull & 1) && n > 1) {
-        const int rmin = __reduce_min_sync(0xffffffffu, active ? row0 : 0x7fffffff);
-        const int rmax = __reduce_max_sync(0xffffffffu, active ? (two ? row1 : row0) : -1);
-        const int cmin = __reduce_min_sync(0xffffffffu, active ? cx : 0x7fffffff);
-        const int cmax = __reduce_max_sync(0xffffffffu, active ? cx + npx - 1 : -1);
-        __syncwarp();             // the warp is done reading the culled table of the previous tile
-        n = cull_components<false>(reinterpret_cast<const float*>(s_tab), n, lane,
-                                   (float)(h.x0 + cmin - h.ox), (float)(h.x0 + cmax - h.ox),
-                                   (float)(h.y0 + rmin - h.oy), (float)(h.y0 + rmax - h.oy), 0.f, s_wtab, &recur);
-        recur = recur && FT_RECUR && !(a.cull & 2);
-        tb = reinterpret_cast<const real*>(s_wtab);
-        stride = 8;
-      }
-      if (lane == 0) issued += (unsigned long long)n * WT_PIX;
-
-      real acc0[PIX_PER_THREAD], acc1[PIX_PER_THREAD];
-#pragma unroll
-      for (int p = 0; p < PIX_PER_THREAD; ++p) { acc0[p] = (real)0; acc1[p] = (real)0; }
-      {
-        const real y0l = (real)(h.y0 + row0 - h.oy), y1l = (real)(h.y0 + row1 - h.oy);
-        const real xl0 = (real)(h.x0 + cx - h.ox);
-        real xl[PIX_PER_THREAD];
-#pragma unroll
-        for (int p = 0; p < PIX_PER_THREAD; ++p) xl[p] = xl0 + (real)p;
-        if (sizeof(real) == 4 && recur) {
-          // row recurrence: 2 exp2 per row of 4 pixels (the rows of a lane are not a fixed
-          // distance apart here, so each row takes its own neighbour ratio)
-          const real tx = (real)2 * xl0 + (real)1;
-#if FT_PACKED
-          f32x2 pacc[PIX_PER_THREAD];         // (row0, row1) pairs: FMUL2 / FADD2, see ft_eval2r
-#pragma unroll
-          for (int p = 0; p < PIX_PER_THREAD; ++p) pacc[p] = pk2(0.f, 0.f);
-#endif
-#pragma unroll 2
-          for (int k = 0; k < n; ++k, tb += 8) {
-            const real A = tb[0], B = tb[1], C = tb[2], b10 = tb[3], c01 = tb[4], c00 = tb[5], hh = tb[6];
-            const real b1a = rfma(B, y0l, b10), b1b = rfma(B, y1l, b10);
-            const real c1a = rfma(rfma(C, y0l, c01), y0l, c00);
-            const real c1b = rfma(rfma(C, y1l, c01), y1l, c00);
-            const real ea = rexp2(rfma(rfma(A, xl0, b1a), xl0, c1a)), ga = rexp2(rfma(A, tx, b1a));
-            const real eb = rexp2(rfma(rfma(A, xl0, b1b), xl0, c1b)), gb = rexp2(rfma(A, tx, b1b));
-#if FT_PACKED
-            recur_row4x2(pk2((float)ea, (float)eb), pk2((float)ga, (float)gb), pk2((float)hh, (float)hh), pacc);
-#else
-            recur_row4(ea, ga, hh, acc0);
-            recur_row4(eb, gb, hh, acc1);
-#endif
-          }
-#if FT_PACKED
-#pragma unroll
-          for (int p = 0; p < PIX_PER_THREAD; ++p) {
-            float lo, hi;
-            unpk2(pacc[p], lo, hi);
-            acc0[p] = (real)lo; acc1[p] = (real)hi;
-          }
-#endif
-          n = 0;
-        }
-#pragma unroll 2
-        for (int k = 0; k < n; ++k, tb += stride) {
-          const real A = tb[0], B = tb[1], C = tb[2], b10 = tb[3], c01 = tb[4], c00 = tb[5];
-          const real b1a = rfma(B, y0l, b10), b1b = rfma(B, y1l, b10);
-          const real c1a = rfma(rfma(C, y0l, c01), y0l, c00);
-          const real c1b = rfma(rfma(C, y1l, c01), y1l, c00);
-#pragma unroll
-          for (int p = 0; p < PIX_PER_THREAD; ++p) {
-            acc0[p] += rexp2(rfma(rfma(A, xl[p], b1a), xl[p], c1a));
-            acc1[p] += rexp2(rfma(rfma(A, xl[p], b1b), xl[p], c1b));
-          }
-        }
-      }
-
-      if (MODE == MODE_PATCH) {
-        if (active) {
-          float* out = a.patches + (long long)item * a.max_patch_px + (long long)row0 * wbox + cx;
-#pragma unroll
-          for (int p = 0; p < PIX_PER_THREAD; ++p)
-            if (p < npx) out[p] = (float)(acc0[p] * fl);
-          if (two) {
-            out += (long long)(row1 - row0) * wbox;
-#pragma unroll
-            for (int p = 0; p < PIX_PER_THREAD; ++p)
-              if (p < npx) out[p] = (float)(acc1[p] * fl);
-          }
-        }
-      } else {
-        double s = 0.0;
-        if (active) {
-          const DevImage& im = *imp;
-          const real eps = (real)im.epsilon;
-          const bool use_mask = im.mask && !(h.flags & CG_ITEM_NO_MASK);
-#pragma unroll
-          for (int rr = 0; rr < 2; ++rr) {
-            if (rr == 1 && !two) break;
-            const int row = rr ? row1 : row0;
-            const long long poff = (long long)row * wbox + cx;
-            const float* auxp = (h.aux >= 0) ? a.aux + (a.aux_offsets ? a.aux_offsets[h.aux] : (a.aux_stride ? (long long)h.aux * a.aux_stride : a.aux_off_v[h.aux])) + poff : nullptr;
-            const long long ioff = (long long)(h.y0 + row) * im.W + (h.x0 + cx);
-#pragma unroll
-            for (int p = 0; p < PIX_PER_THREAD; ++p) {
-              if (p < npx) {
-                const real v = fl * (rr ? acc1[p] : acc0[p]);
-                if (MODE == MODE_POISSON) {
-                  const real lam = (auxp ? (real)auxp[p] : eps) + v;
-                  const bool good = (lam > (real)0) && (!use_mask || im.mask[ioff + p] != 0.f);
-                  if (good) s += (double)im.nelec[ioff + p] * log_accurate(lam, logt) - (double)lam;
-                } else {      // MODE_COND, sources.py:171-174
-                  if (v >= (real)1.17549435e-38f) s += log_accurate(v, logt) * (double)auxp[p];
-                  if (a.cond_sum) s -= (double)v;     // celeste_galaxy_conditionals.py:41
-                }
-              }
-            }
-          }
-        }
-        s = warp_sum(s);
-        if (lane == 0) a.partials[h.strip_start + wt] = s;
-      }
+      const double s = render_warp_tile<real, MODE>(a, h, item, s_tab, s_wtab, wt, lane, wbox, hbox, cpr, hp, n_lu,
+                                                    r_band, imp, fl, logt, issued);
+      if (MODE != MODE_PATCH && lane == 0) a.partials[h.strip_start + wt] = s;
     }
     wk = __shfl_sync(0xffffffffu, nxt, 0);
   }

@@ -456,6 +456,130 @@ __global__ void __launch_bounds__(256, 2) bg_tile_kernel(BgArgs A) {
 }
 
 // ---------------------------------------------------------------------------
+// N2: the location slice sampler of every source in ONE launch
+// ---------------------------------------------------------------------------
+// Source.resample_location (sources.py:308-319) = slicesample(u, location_likelihood, step_out=False,
+// compwise) (util/infer/slicesample.py:89-247).  One CTA per source, one warp per image: the CTA runs
+// the sampler's whole control flow -- per direction: bracket [upper - sigma, upper], slice level
+// log(rand) + ll(0), shrink until a point above the level is drawn -- and evaluates every likelihood
+// it needs itself: each warp builds its image's component table in shared memory (item_table, the
+// float64 code prepare_kernel runs), renders the fixed box against the source's photon patch
+// (render_warp_tile<MODE_COND>) and the CTA sums the images in order.  The same device functions, the
+// same order of sums as the lock-step path (cg_items_loglik): the likelihood values, hence the
+// decisions and the trace, are bit-identical to it.
+// Random numbers are HOST-supplied, in the reference's call order: ord[s] = the shuffled coordinate
+// order, uni[s][0..B) = the uniforms the sampler draws one after the other (log_uni = their float64
+// logarithms, taken on the host so that the slice level matches numpy's).  A source that runs out of
+// uniforms, meets a NaN, or has a comparison inside the guard band stops with a status: the host
+// redoes that source with the lock-step sampler (float64 refinement) from the same RNG state.
+#define SLICE_MAX_IMG 8
+struct SliceArgs {
+  ImgPtrs imgs;
+  int n_img, n_src, B;
+  CgSource* srcs;              // in: current state; out: u replaced for status 0
+  const CgBox* boxes;          // [n_src * n_img] the photon patches' boxes
+  const float* aux;            // photon patches, item-major, stride aux_stride
+  long long aux_stride;
+  const double* uni;           // [n_src][B]
+  const double* log_uni;       // [n_src][B]
+  const int* ord;              // [n_src][2]
+  double sigma, guard;
+  double* ll_out;              // [n_src] likelihood at the accepted point
+  int* n_used;                 // [n_src] uniforms consumed
+  int* status;                 // [n_src] 0 ok, 1 out of uniforms, 2 guard band, 3 NaN, 4 shrank to zero
+  int* n_evals;                // [n_src] likelihood evaluations
+  const FilterTables* filters;
+  const double* flux_table;
+  long long flux_rows;
+  const LogTable* logtab;
+  int cull;
+};
+
+__global__ void __launch_bounds__(32 * SLICE_MAX_IMG) slice_location_kernel(SliceArgs A) {
+  __shared__ __align__(16) float s_tab_all[SLICE_MAX_IMG][TAB_STRIDE];
+  __shared__ __align__(16) float s_wtab_all[SLICE_MAX_IMG][CG_MAX_COMP * 8];
+  __shared__ double s_ll[SLICE_MAX_IMG];
+  const int s = blockIdx.x;
+  if (s >= A.n_src) return;
+  const int lane = threadIdx.x & 31, b = threadIdx.x >> 5;       // warp b <-> image b
+  const DevImage& im = *A.imgs.p[b];
+  float* const s_tab = s_tab_all[b];
+  float* const s_wtab = s_wtab_all[b];
+  CgSource src = A.srcs[s];
+  const CgBox box0 = A.boxes[(long long)s * A.n_img + b];
+  // the fixed box, clipped to the image as prepare_kernel clips CG_ITEM_FIXED_BOX
+  ItemHdr h;
+  h.x0 = max(box0.x0, 0); h.y0 = max(box0.y0, 0); h.x1 = min(box0.x1, im.W); h.y1 = min(box0.y1, im.H);
+  if (h.x1 <= h.x0 || h.y1 <= h.y0) { h.x1 = h.x0; h.y1 = h.y0; }
+  h.img = b; h.aux = s * A.n_img + b; h.flags = CG_ITEM_FLUX_BAND | CG_ITEM_FIXED_BOX; h.strip_start = 0;
+  const int wbox = h.x1 - h.x0, hbox = h.y1 - h.y0;
+  const int cpr = (wbox + PIX_PER_THREAD - 1) / PIX_PER_THREAD;
+  const int hp = (hbox / (2 * TILE_R)) * TILE_R + ((hbox % (2 * TILE_R)) + 1) / 2;
+  const int n_lu = cpr * hp;
+  const int n_strips = (int)(((long long)hp * cpr + 31) / 32);
+  const float r_band = __frcp_rn((float)max(cpr * TILE_R, 1));
+  RenderArgs ra;                       // only the fields render_warp_tile<MODE_COND> reads
+  ra.cull = A.cull; ra.aux = A.aux; ra.aux_offsets = nullptr; ra.aux_stride = A.aux_stride; ra.cond_sum = 0;
+  ra.patches = nullptr; ra.max_patch_px = 0;
+  unsigned long long issued = 0;
+  int evals = 0;
+
+  // Source.log_likelihood(u = x) summed over the images (sources.py:134-183)
+  auto loglik = [&](double x0, double x1) -> double {
+    src.u[0] = x0; src.u[1] = x1;
+    __syncthreads();                   // every warp is done with the previous evaluation's tables and s_ll
+    ItemGeom g = item_table<float>(im, src, h.flags, lane, s_tab);
+    const double flux = item_flux(im, src, h.flags, lane, g.star, A.filters, A.flux_table, A.flux_rows, g);
+    h.ox = g.ox; h.oy = g.oy; h.K = g.K; h.flux = flux; h.norm_term = flux * im.psf_wsum;
+    __syncwarp();
+    double t = 0.0;
+    if (g.K > 0 || true) {
+      for (int wt = 0; wt < n_strips; ++wt)         // the order items_finalize_kernel sums the strips in
+        t += render_warp_tile<float, MODE_COND>(ra, h, 0, s_tab, s_wtab, wt, lane, wbox, hbox, cpr, hp, n_lu, r_band,
+                                                &im, (float)flux, A.logtab, issued);
+    }
+    if (lane == 0) s_ll[b] = t - h.norm_term;         // CG_LL_CONDITIONAL (sources.py:174)
+    __syncthreads();
+    double tot = 0.0;
+    for (int k = 0; k < A.n_img; ++k) tot += s_ll[k];  // image order: the lock-step driver's sum
+    ++evals;
+    return tot;
+  };
+
+  const double* U = A.uni + (long long)s * A.B;
+  const double* LU = A.log_uni + (long long)s * A.B;
+  double x[2] = {src.u[0], src.u[1]};
+  int idx = 0, st = 0;
+  double ll_new = 0.0;
+  for (int dd = 0; dd < 2 && st == 0; ++dd) {
+    const int d = A.ord[s * 2 + dd];
+    if (idx + 2 > A.B) { st = 1; break; }
+    double upper = A.sigma * U[idx++];                      // slicesample.py:155-156
+    double lower = upper - A.sigma;
+    const double llh_s = LU[idx++] + loglik(x[0], x[1]);    // :159
+    for (;;) {                                              // :181-198 (step_out = False)
+      if (idx >= A.B) { st = 1; break; }
+      const double z = (upper - lower) * U[idx++] + lower;
+      const double xt0 = (d == 0 ? 1.0 : 0.0) * z + x[0], xt1 = (d == 1 ? 1.0 : 0.0) * z + x[1];
+      ll_new = loglik(xt0, xt1);
+      if (ll_new != ll_new) { st = 3; break; }
+      if (A.guard > 0. && fabs(ll_new - llh_s) < A.guard) { st = 2; break; }
+      if (ll_new > llh_s) { x[0] = xt0; x[1] = xt1; break; }
+      else if (z < 0) lower = z;
+      else if (z > 0) upper = z;
+      else { st = 4; break; }
+    }
+  }
+  if (threadIdx.x == 0) {
+    A.status[s] = st;
+    A.n_used[s] = idx;
+    A.n_evals[s] = evals;
+    A.ll_out[s] = ll_new;
+    if (st == 0) { A.srcs[s].u[0] = x[0]; A.srcs[s].u[1] = x[1]; }
+  }
+}
+
+// ---------------------------------------------------------------------------
 // per-sweep statistics a rank contributes to the all-reduce
 // ---------------------------------------------------------------------------
 // colour-space coordinates of the sources of one type (FluxColorMoG, util/dists/flux_prior.py:4-40:
@@ -829,6 +953,32 @@ int cg_sweep_stats(const double* d_ll, int32_t n_ll, const double* d_noise, cons
   if (n_noise > 0 && (!d_noise || !d_img_band)) return fail(CG_EINVAL, "noise sums need the image bands");
   sweep_stats_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(d_ll, n_ll, d_noise, d_img_band, n_noise, d_srcs, n_src,
                                                          d_prior0, d_prior1, block, d_vec);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
+int cg_slice_sample_locations(CgImage* const* imgs, int32_t n_img, CgSource* d_srcs, int32_t n_src,
+                              const CgBox* d_boxes, const float* d_photons, int64_t max_patch_px,
+                              const double* d_uniforms, const double* d_log_uniforms, const int32_t* d_order,
+                              int32_t n_uniforms, double sigma, double guard, double* d_ll, int32_t* d_n_used,
+                              int32_t* d_status, int32_t* d_n_evals, void* stream) {
+  NEED_INIT();
+  SliceArgs A;
+  memset(&A, 0, sizeof A);
+  int rc = fill_imgs(imgs, n_img, &A.imgs);
+  if (rc) return rc;
+  if (n_img > SLICE_MAX_IMG) return fail(CG_EINVAL, "at most %d images per source in the on-device sampler", SLICE_MAX_IMG);
+  if (n_src <= 0) return CG_OK;
+  if (!d_srcs || !d_boxes || !d_photons || !d_uniforms || !d_log_uniforms || !d_order || !d_ll || !d_n_used ||
+      !d_status || !d_n_evals)
+    return fail(CG_EINVAL, "null argument");
+  if (n_uniforms < 4) return fail(CG_EINVAL, "at least 4 uniforms per source");
+  A.n_img = n_img; A.n_src = n_src; A.B = n_uniforms; A.srcs = d_srcs; A.boxes = d_boxes; A.aux = d_photons;
+  A.aux_stride = max_patch_px; A.uni = d_uniforms; A.log_uni = d_log_uniforms; A.ord = d_order; A.sigma = sigma;
+  A.guard = guard; A.ll_out = d_ll; A.n_used = d_n_used; A.status = d_status; A.n_evals = d_n_evals;
+  A.filters = g_d_filters; A.flux_table = g_flux_table; A.flux_rows = g_flux_rows; A.logtab = g_d_logtab;
+  A.cull = g_cull | (g_recur ? 0 : 2);
+  slice_location_kernel<<<n_src, 32 * n_img, 0, (cudaStream_t)stream>>>(A);
   LAUNCH_CHECK();
   return CG_OK;
 }

@@ -1304,3 +1304,33 @@ class SweepPayload(object):
                                     self.d_srcs.data_ptr(), self.n_src, self.blocks[0].data_ptr(),
                                     self.blocks[1].data_ptr(), self.block, self.vec[k].data_ptr(), stream_ptr()))
         return self.vec[k]
+
+
+def slice_sample_locations(images: Sequence[Image], d_srcs: torch.Tensor, n_src: int, d_boxes: torch.Tensor,
+                           photons: torch.Tensor, max_patch_px: int, uniforms: np.ndarray, order: np.ndarray,
+                           sigma: float = 1.0, guard: float = 1e-2):
+    """N2: cg_slice_sample_locations -- Source.resample_location for every source in ONE launch.
+    d_srcs: device CgSource bytes (updated in place for the sources that finish); d_boxes: device CgBox
+    bytes [n_src * n_img]; photons: [n_src * n_img, max_patch_px] float32 device patches; uniforms
+    [n_src, B] float64 host array in the sampler's draw order; order [n_src, 2] int32 coordinate order.
+    Returns host arrays (ll, n_used, status, n_evals)."""
+    harr, n_img = _handles(images)
+    dev = device()
+    uniforms = np.ascontiguousarray(uniforms, dtype=np.float64)
+    if uniforms.shape[0] != n_src or order.shape != (n_src, 2):
+        raise ValueError("uniforms / order must have one row per source")
+    with np.errstate(divide="ignore"):
+        logs = np.log(uniforms)
+    d_u = torch.from_numpy(uniforms).to(dev)
+    d_lu = torch.from_numpy(logs).to(dev)
+    d_ord = torch.from_numpy(np.ascontiguousarray(order, dtype=np.int32)).to(dev)
+    ll = torch.zeros(n_src, dtype=torch.float64, device=dev)
+    used = torch.zeros(n_src, dtype=torch.int32, device=dev)
+    status = torch.zeros(n_src, dtype=torch.int32, device=dev)
+    evals = torch.zeros(n_src, dtype=torch.int32, device=dev)
+    check(lib().cg_slice_sample_locations(harr, n_img, d_srcs.data_ptr(), int(n_src), d_boxes.data_ptr(),
+                                          photons.data_ptr(), int(max_patch_px), d_u.data_ptr(), d_lu.data_ptr(),
+                                          d_ord.data_ptr(), uniforms.shape[1], float(sigma), float(guard),
+                                          ll.data_ptr(), used.data_ptr(), status.data_ptr(), evals.data_ptr(),
+                                          stream_ptr()))
+    return ll.cpu().numpy(), used.cpu().numpy(), status.cpu().numpy(), evals.cpu().numpy()

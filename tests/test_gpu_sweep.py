@@ -281,3 +281,54 @@ def test_multi_sweep_trace_equals_oracle_driven_chain(engine, oracle):
     assert np.allclose(trace_l[:, cols_u], trace_d[:, cols_u], rtol=0, atol=1e-13)
     assert np.allclose(trace_l[:, cols_f], trace_d[:, cols_f], rtol=1e-12, atol=0)
     print("oracle evaluations", n_eval, "float64 refinements on the device chain", n_ref)
+
+
+def test_on_device_slice_sampler_equals_lockstep(engine, oracle):
+    """N2: cg_slice_sample_locations runs every source's slice sampler in ONE launch (the sampler's
+    control flow and its likelihood evaluations inside the kernel, host-supplied uniforms in the
+    reference's draw order).  Three sweeps with persistent per-source generators: locations, fluxes
+    and the generators' states equal those of the lock-step host driver bit for bit; the location
+    phase costs one launch however many shrink rounds the chains need."""
+    from desi_mcmc_b200.compat import models
+    from desi_mcmc_b200.compat.slicesample import run_lockstep
+
+    def build():
+        field = synth.make_field(91, H=96, W=128, n_src=12, star_frac=.5, margin=12)
+        nelec = hp.simulate_nelec(oracle, field, 9)
+        gimgs = hp.gpu_images(engine, field, nelec)
+        m = models.Celeste()
+        m.add_field({im.band: im for im in gimgs})
+        m.initialize_sources(init_src_params=hp.gpu_sources(engine, field))
+        m.field_list[0].resample_photons(m.srcs, random_state=np.random.RandomState(21))
+        return m
+
+    a, b = build(), build()
+    rng_a = [np.random.RandomState(100 + s) for s in range(len(a.srcs))]
+    rng_b = [np.random.RandomState(100 + s) for s in range(len(b.srcs))]
+    from desi_mcmc_b200.compat import sources as S
+    from desi_mcmc_b200.compat.slicesample import slicesample_gen
+    tot_dev, tot_evals = 0, 0
+    for sweep in range(3):
+        # host lock-step driver with the persistent generators (resample_sources_batched's body)
+        bc = S.BatchedConditional(a.srcs)
+        for src, rng, ps in zip(a.srcs, rng_a, bc.unit_patch_sums()):
+            src.resample_fluxes(rng=rng, psf_sums_by_image=ps)
+        bc.refresh()
+        gens = [slicesample_gen(src.params.u.copy(), **src._location_slice_args(rng)) for src, rng in zip(a.srcs, rng_a)]
+        for src, (u, ll) in zip(a.srcs, run_lockstep(gens, bc.loglik)):
+            src.params.u = u
+        rounds = run_lockstep.last_rounds
+        engine.launch_count(reset=True)
+        st = b.resample_sources_on_device(rngs=rng_b)
+        launches = engine.launch_count()
+        tot_dev += st["device"]
+        tot_evals += st["evals"]
+        for sa, sb, ra, rb in zip(a.srcs, b.srcs, rng_a, rng_b):
+            assert np.array_equal(sa.params.u, sb.params.u)
+            assert np.array_equal(sa.params.fluxes, sb.params.fluxes)
+            assert ra.random_sample() == rb.random_sample()          # the streams continue in step
+        # unit-patch render (2 launches) + ONE sampler launch + the lock-step rounds of any fallback
+        assert st["fallback"] > 0 or launches <= 4
+        assert rounds >= 10
+    assert tot_dev >= 30 and tot_evals > 300
+    print("device-sampled", tot_dev, "of", 3 * len(a.srcs), "likelihood evaluations in the kernel", tot_evals)
