@@ -371,6 +371,18 @@ def bench_crowded(engine, synth, steps, pk, with_cpu):
             evals[name] = engine.last_eval_count()
             if prof:
                 render_evals += evals[name]
+    # N2: the location slice samplers of all 5000 sources in one launch (not part of the sweep above)
+    sw.allocate(7)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    status, sl_evals = sw.slice_locations(seed=11)
+    torch.cuda.synchronize()
+    slice_s = time.perf_counter() - t0
+    slice_leg = {"what": "Source.resample_location (sources.py:308-319) for all 5000 sources in ONE launch "
+                         "(cg_slice_sample_locations), host-supplied uniforms; wall clock incl. the upload of the uniforms",
+                 "ms": slice_s * 1e3, "likelihood_evaluations": int(sl_evals.sum()),
+                 "evaluations_per_s": float(sl_evals.sum() / slice_s),
+                 "sources_finished_on_device": int((status == 0).sum()), "sources_flagged": int((status != 0).sum())}
     # backgrounds: every active neighbour rendered on the target's box (sources.py:481)
     offs, idx = sw.h_nbr
     st = sw.h_static
@@ -397,6 +409,7 @@ def bench_crowded(engine, synth, steps, pk, with_cpu):
            "sweep_ms": ms, "sweep_ms_host_clock": wall * 1e3, "value": evals_sweep / (ms * 1e-3), "unit": "evals/s",
            "proposals_per_s": 2 * S * P / (ms * 1e-3), "evals_per_sweep": evals_sweep, "evals_by_phase": evals,
            "phase_ms": {k: round(v, 3) for k, v in ph.items()}, "workspace_bytes": int(sw.workspace_bytes),
+           "slice_sampler_on_device": slice_leg,
            "h2d_bytes_per_sweep": 2 * S * P * 8, "accepted_last_sweep": res["accepted"].tolist(),
            "guard_rescored_last_sweep": res["guard"].tolist(),
            "roofline": _roofline("render_kernel<float, COND | POISSON> (the two scoring passes: %.0f%% of the sweep)" %

@@ -1199,6 +1199,20 @@ class GibbsSweep(object):
             self.d_nbr_off.data_ptr(), self.d_nbr_idx.data_ptr(), self.max_patch_px, self.side,
             self.bg.data_ptr(), self.ws_bg.data_ptr(), self.ws_bg.numel(), stream_ptr()))
 
+    def slice_locations(self, seed: int, n_uniforms: int = 160, sigma: float = 1.0):
+        """Source.resample_location (sources.py:308-319) for every source given the allocated photons, the
+        slice samplers run on the device in ONE launch (cg_slice_sample_locations).  The uniforms come from
+        one host RandomState(seed): row s of a [n_src, n_uniforms] block is source s's stream.  Sources the
+        device flags (status != 0: out of uniforms, float64 guard band, NaN) keep their location this sweep.
+        Returns (status, n_evals) host arrays."""
+        rng = np.random.RandomState(int(seed) & 0x7fffffff)
+        order = np.where(rng.uniform(size=(self.n_src, 1)) < .5, [[0, 1]], [[1, 0]]).astype(np.int32)
+        uni = rng.random_sample((self.n_src, n_uniforms))
+        ll, used, status, evals = slice_sample_locations(self.images, self.d_cur, self.n_src, self.d_boxes, self.samp,
+                                                         self.max_patch_px, uni, order, sigma=sigma, guard=self.guard)
+        self.slice_stats = dict(ll=ll, used=used, status=status, evals=evals)
+        return status, evals
+
     def loglik(self):
         check(self.L.cg_field_loglik(self.harr, self.n_img, self.d_cur.data_ptr(), self.n_src, self.bound_cap,
                                      self.max_patch_px, self.ll.data_ptr(), None, self.ws_field.data_ptr(),
