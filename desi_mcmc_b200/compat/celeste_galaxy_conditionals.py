@@ -107,10 +107,18 @@ def galaxy_source_like_batch(ths, Z_s, images, use_fp64=False):
     aux = torch.from_numpy(np.concatenate(zs)).to(engine.device())
     ll, boxes = engine.items_loglik(images, rec, items, mode=_ffi.CG_LL_CONDITIONAL_SUM, aux=aux,
                                     aux_offsets=offs, use_fp64=use_fp64)
-    for n in range(n_img):
-        b = boxes[n]
-        if (b["y1"] - b["y0"]) * (b["x1"] - b["x0"]) != zs[n].size:
-            raise ValueError("Z_s[%d] does not match the galaxy footprint on image %d" % (n, n))
+    # EVERY variant's footprint must have the shape of its photon patch: a finite-difference variant
+    # whose int() truncation lands one pixel off would index the patch with the wrong row stride
+    # (the reference raises a shape mismatch in `Z_s[n] * np.log(lam)`, :41)
+    for p in range(P):
+        for n in range(n_img):
+            b = boxes[p * n_img + n]
+            shp = (int(b["y1"] - b["y0"]), int(b["x1"] - b["x0"]))
+            ok = (shp == tuple(np.shape(Z_s[n]))) if np.ndim(Z_s[n]) == 2 else (shp[0] * shp[1] == np.size(Z_s[n]))
+            if not ok:
+                raise ValueError("operands could not be broadcast together: Z_s[%d] has shape %s, the footprint of "
+                                 "parameter vector %d on image %d is %s" %
+                                 (n, tuple(np.shape(Z_s[n])), p, n, (int(b["y1"] - b["y0"]), int(b["x1"] - b["x0"]))))
     return ll.cpu().numpy().reshape(P, n_img).sum(axis=1)
 
 

@@ -450,3 +450,43 @@ def test_field_loglik_scan_rounds(engine, oracle):
         assert hp.rel_err(models[i].cpu().numpy(), lam, 1.0) < RATE_RTOL
         want = oracle.celeste_likelihood(osrcs, img)
         assert abs(ll[i] - want) <= LL_RTOL * abs(want)
+
+
+def test_score_proposals_bright_source_guard(engine, oracle):
+    """A bright source (> 1e6 photo-electrons in its box): the fp32 error of a score grows with the
+    counts it multiplies, so the automatic guard band widens with sqrt(sum nelec^2) and the decisions
+    still equal the float64 oracle's; with the band disabled the raw fp32 scores are measurably off."""
+    P, size = 64, 32
+    field = synth.make_stamp(1003, size=size, n_star=1, n_gal=1)
+    for s in field["sources"]:
+        s["fluxes"] = np.asarray(s["fluxes"]) * 400.           # ~1e6 - 1e7 electrons per band
+    nelec = hp.simulate_nelec(oracle, field, 5)
+    assert sum(float(n.sum()) for n in nelec) > 5e6
+    gimgs = hp.gpu_images(engine, field, nelec)
+    oimgs = hp.oracle_images(oracle, field, nelec)
+    cur, other = field["sources"][1], field["sources"][0]
+    props, _ = synth.make_proposals(77, cur, P)
+    ocur = hp.oracle_sources(oracle, [cur])[0]
+    oother = hp.oracle_sources(oracle, [other])
+    oprops = hp.oracle_sources(oracle, props)
+    boxes, bgs, gboxes = [], [], []
+    for img in oimgs:
+        xlim, ylim = oracle.make_bbox(ocur, img, pixel_radius=12)
+        boxes.append((xlim, ylim))
+        bgs.append(oracle.generate_background_patch(ocur, oother, img, xlim, ylim))
+        gboxes.append((xlim[0], xlim[1], ylim[0], ylim[1]))
+    want = np.array([oracle.calculate_acceptance_logprob(ocur, p, oimgs, boxes, bgs) for p in oprops])
+    # log-uniforms placed NEAR the scores: every decision is a close call
+    rng = np.random.RandomState(4)
+    log_u = want + rng.normal(0., .05, size=P)
+    packed = engine.pack_sources(hp.gpu_sources(engine, [cur] + props))
+    auto = engine.ProposalScorer(gimgs, gboxes, bgs, max_proposals=P)
+    assert auto.guard > 1e-2                                   # widened by the counts
+    delta, accept, n_guard = auto.score(packed, log_u)
+    assert np.array_equal(accept, log_u < want)
+    assert n_guard > 0
+    raw = engine.ProposalScorer(gimgs, gboxes, bgs, max_proposals=P, guard=0.0)
+    d_raw, _, _ = raw.score(packed, log_u)
+    err = np.max(np.abs(d_raw - want))
+    print("auto guard %.3g, re-scored %d of %d, raw fp32 |delta error| %.3g" % (auto.guard, n_guard, P, err))
+    assert err < auto.guard                                     # the band covers the fp32 error
