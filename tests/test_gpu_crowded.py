@@ -346,3 +346,59 @@ def test_full_sweeps_are_reproducible_and_consistent(engine, oracle):
         ll = engine.field_loglik(gimgs, sw.sources(), bound_cap=25., max_patch_px=sw.max_patch_px).cpu().numpy()
         assert np.array_equal(ll, st["loglik"])
     assert out[0][0] == out[1][0] and np.array_equal(out[0][1], out[1][1]) and np.array_equal(out[0][2], out[1][2])
+
+
+def test_geweke_joint_distribution_of_allocation_and_flux_update(engine, oracle):
+    """Geweke's joint-distribution test (the method of experiments/rjump/geweke_test.py:94-121) for the
+    device transition "allocate photons, then redraw the fluxes": the successive-conditional simulator
+    (image | flux from the model on the host, flux' | image from the DEVICE kernels) must leave the
+    prior Gamma(a0, 1/b0) invariant.  First and second moments of the flux in the band that has data,
+    with batch-means standard errors; the bands without data must be exact prior draws."""
+    import torch
+    from desi_mcmc_b200 import _ffi
+    a0, b0 = 5., .005
+    size = 25
+    field = synth.make_stamp(1001, size=size, n_star=1, n_gal=0)
+    meta = dict(field["images"][2])
+    meta["calib"] = 40.                                    # weak data: ~100 photons at the prior mean
+    img = engine.Image(nelec=np.zeros((size, size)), **synth.image_kwargs(meta))
+    star = field["sources"][0]
+    rec = engine.pack_sources([engine.SrcParams(u=star["u"], a=0, fluxes=np.full(5, a0 / b0))])
+    sw = engine.GibbsSweep([img], rec, bound_cap=25., proposals=0, background_pass=False)
+    unit, boxes = engine.render_patches([img], rec, default_flags=_ffi.CG_ITEM_FLUX_UNIT, bound_cap=25.)
+    bx = boxes[0]
+    h, w = int(bx["y1"] - bx["y0"]), int(bx["x1"] - bx["x0"])
+    psi = unit[0, :h * w].cpu().numpy().astype(np.float64).reshape(h, w)
+    c = img.kappa / img.calib
+    rng = np.random.RandomState(2026)
+    n_iter, burn = 2400, 200
+    f = rng.gamma(a0, 1. / b0)
+    trace = np.zeros((n_iter, 5))
+    cur = rec.copy()
+    for it in range(n_iter):
+        lam = np.full((size, size), img.epsilon)
+        lam[bx["y0"]:bx["y1"], bx["x0"]:bx["x1"]] += f * c * psi
+        img.set_nelec(rng.poisson(lam).astype(np.float32))
+        cur["flux"][0, :] = f
+        sw.d_cur.copy_(torch.from_numpy(cur.view(np.uint8).reshape(-1)))
+        sw.allocate(seed=10 * it + 1)
+        sw.resample_fluxes(seed=10 * it + 2)
+        trace[it] = sw.sources()["flux"][0]
+        f = trace[it, 2]
+    tr = trace[burn:]
+    mean, second = a0 / b0, a0 * (a0 + 1) / b0 ** 2
+
+    def batch_se(x, nb=20):
+        m = x[:len(x) // nb * nb].reshape(nb, -1).mean(axis=1)
+        return m.std(ddof=1) / np.sqrt(nb)
+    z1 = (tr[:, 2].mean() - mean) / batch_se(tr[:, 2])
+    z2 = ((tr[:, 2] ** 2).mean() - second) / batch_se(tr[:, 2] ** 2)
+    print("Geweke z-scores (band with data): mean %.2f, second moment %.2f; lag-1 autocorrelation %.2f" %
+          (z1, z2, np.corrcoef(tr[:-1, 2], tr[1:, 2])[0, 1]))
+    assert abs(z1) < 4. and abs(z2) < 4.
+    for b in (0, 1, 3, 4):                                 # no image in these bands: independent prior draws
+        x = tr[:, b]
+        assert abs(x.mean() - mean) < 4.5 * np.sqrt(a0) / b0 / np.sqrt(len(x))
+        assert abs(x.var() / (a0 / b0 ** 2) - 1) < .15
+    # the chain actually depends on the data: photons were allocated to the source
+    assert sw.counts.cpu().numpy().sum() > 0
