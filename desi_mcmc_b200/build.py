@@ -15,6 +15,7 @@ ROOT = os.path.dirname(PKG)
 SRC = os.path.join(PKG, "csrc", "celeste_b200.cu")
 HDR = os.path.join(ROOT, "include", "celeste_b200.h")
 LIB = os.path.join(PKG, "libceleste_b200.so")
+LIB_CHECKED = os.path.join(PKG, "libceleste_b200_checked.so")   # -DCG_CHECKED: bounds asserts in the kernels
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -42,7 +43,13 @@ def needs_build() -> bool:
     return any(os.path.getmtime(p) > t for p in deps)
 
 
-def build(force: bool = False, verbose: bool = False, ptxas_info: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, ptxas_info: bool = False, checked: bool = False) -> str:
+    if checked:
+        cmd = [_nvcc(), *NVCC_FLAGS, "-DCG_CHECKED", "-I", os.path.join(ROOT, "include"), SRC, "-o", LIB_CHECKED]
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+        return LIB_CHECKED
     if not force and not needs_build():
         return LIB
     cmd = [_nvcc(), *NVCC_FLAGS, "-I", os.path.join(ROOT, "include"), SRC, "-o", LIB]
@@ -59,4 +66,7 @@ def build(force: bool = False, verbose: bool = False, ptxas_info: bool = False) 
 
 
 if __name__ == "__main__":
-    print(build(force=True, verbose=True, ptxas_info="-v" in sys.argv))
+    if "--checked" in sys.argv:
+        print(build(checked=True))
+    else:
+        print(build(force=True, verbose=True, ptxas_info="-v" in sys.argv))

@@ -70,6 +70,23 @@ static int fail(int code, const char* fmt, ...) {
       return fail(CG_ECUDA, "kernel launch failed: %s (%s:%d)",                   \
                   cudaGetErrorString(_e), __FILE__, __LINE__);                    \
   } while (0)
+// Checked build (python -m desi_mcmc_b200.build --checked -> libceleste_b200_checked.so, loaded when
+// CG_CHECKED=1): every index into a workspace array, a shared-memory table or a box-shaped patch is
+// asserted in the kernels; a violation prints its source line and traps (the launch fails with an
+// "unspecified launch failure", which the tests see).  compute-sanitizer is closed on this GPU pool
+// (profiles/r02_sanitizer_refused.log); this is the bounds evidence that can be produced here.
+#ifdef CG_CHECKED
+#define CG_CHECK(cond)                                                                       \
+  do {                                                                                       \
+    if (!(cond)) {                                                                           \
+      printf("CG_CHECK failed: %s (%s:%d) block %d thread %d\n", #cond, __FILE__, __LINE__,  \
+             (int)blockIdx.x, (int)threadIdx.x);                                             \
+      __trap();                                                                              \
+    }                                                                                        \
+  } while (0)
+#else
+#define CG_CHECK(cond) ((void)0)
+#endif
 #define NEED_INIT()                                                               \
   do {                                                                            \
     if (g_device < 0) return fail(CG_ESTATE, "cg_init() has not been called");    \
@@ -690,6 +707,7 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
   if (listed && start + n_strips <= a.worklist_cap)
     for (int j = lane; j < n_units; j += 32) {
       const int slot = heavy ? (wpos + j) : (a.worklist_cap - 1 - (wpos + j));
+      CG_CHECK(slot >= 0 && slot < a.worklist_cap);
       a.worklist[slot] = make_int2((int)i, j * a.unit_wt);   // (item, first warp tile of the unit)
     }
   // bin the footprint into the image tiles it overlaps (full-field gather)
@@ -706,6 +724,7 @@ __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
       const int pos = atomicAdd(&a.tile_count[slot], 1);
       // entry = item * 64 + K (K <= CG_MAX_COMP < 64): the tile kernels weigh a bin
       // without touching the item headers
+      CG_CHECK(t >= 0 && t < a.max_tiles && K <= CG_MAX_COMP);
       if (pos < cap) a.tile_list[slot * cap + pos] = (int)i * 64 + K;
     }
   }
@@ -835,6 +854,7 @@ __device__ __forceinline__ int cull_components(const float* gtab, int K, int lan
   const unsigned m0 = __ballot_sync(0xffffffffu, keep[0]);
   const unsigned m1 = __ballot_sync(0xffffffffu, keep[1]);
   const unsigned lt = (1u << lane) - 1u;
+  CG_CHECK(K <= CG_MAX_COMP && __popc(m0) + __popc(m1) <= CG_MAX_COMP);
   if (keep[0]) {
     float* d = wtab + __popc(m0 & lt) * 8;
     *reinterpret_cast<float4*>(d) = e0[0];
@@ -944,6 +964,7 @@ __device__ __forceinline__ double render_warp_tile(const RenderArgs& a, const It
 
   if (MODE == MODE_PATCH) {
     if (active) {
+      CG_CHECK((long long)(two ? row1 : row0) * wbox + cx + npx <= a.max_patch_px && row0 >= 0 && cx >= 0);
       float* out = a.patches + (long long)item * a.max_patch_px + (long long)row0 * wbox + cx;
 #pragma unroll
       for (int p = 0; p < PIX_PER_THREAD; ++p)
@@ -1008,6 +1029,7 @@ __global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
   wk = __shfl_sync(0xffffffffu, wk, 0);
   while (wk < total) {
     const int slot = (wk < n_heavy) ? wk : (a.worklist_cap - 1 - (wk - n_heavy));
+    CG_CHECK(slot >= 0 && slot < a.worklist_cap);
     const int2 w = a.worklist[slot];
     const int item = w.x, wt0 = w.y;
     int nxt = 0;
@@ -1036,6 +1058,7 @@ __global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
     for (int wt = wt0; wt < wt_end; ++wt) {
       const double s = render_warp_tile<real, MODE>(a, h, item, s_tab, s_wtab, wt, lane, wbox, hbox, cpr, hp, n_lu,
                                                     r_band, imp, fl, logt, issued);
+      CG_CHECK(h.strip_start + wt < a.worklist_cap && wt < h.n_strips);
       if (MODE != MODE_PATCH && lane == 0) a.partials[h.strip_start + wt] = s;
     }
     wk = __shfl_sync(0xffffffffu, nxt, 0);
@@ -1481,6 +1504,7 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
     if (dsc < 0) break;
     const int cnt = gy & 63, g = gy >> 6;
     const int img = dsc >> 24;
+    CG_CHECK(img >= 0 && img < a.n_img && g >= 0 && g < a.tiles_total);
     const DevImage& im = *a.imgs.p[img];
     const int H = im.H, W = im.W;
     FtGeom q;
@@ -1586,6 +1610,7 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
           b.x = __shfl_sync(0xffffffffu, bx.x, sl); b.y = __shfl_sync(0xffffffffu, bx.y, sl);
           b.z = __shfl_sync(0xffffffffu, bx.z, sl); b.w = __shfl_sync(0xffffffffu, bx.w, sl);
           const int2 oo = make_int2(__shfl_sync(0xffffffffu, o.x, sl), __shfl_sync(0xffffffffu, o.y, sl));
+          CG_CHECK((ee & 63) <= CG_MAX_COMP && b.x >= 0 && b.y <= im.W && b.z >= 0 && b.w <= im.H);
           ft_source(a, ee >> 6, ee & 63, b, oo, __shfl_sync(0xffffffffu, fl, sl), q, lane, wtab, lam, issued);
         }
       }

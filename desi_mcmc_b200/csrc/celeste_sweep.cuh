@@ -192,6 +192,7 @@ __global__ void __launch_bounds__(256, 2) alloc_tile_kernel(AllocTileArgs A) {
                     left[r][p] -= (int)got;
                   }
                   if (own) { draw += 1ull << (8 * (r * 4 + p)); tot[r][p] -= (double)rate; }
+                  CG_CHECK((long long)(y - bx.z) * wbox + (x - bx.x) < A.max_patch_px && y >= bx.z && x >= bx.x);
                   A.samp[(long long)item * A.max_patch_px + (long long)(y - bx.z) * wbox + (x - bx.x)] = (float)got;
                   got_sum += got;
                   unit_sum += acc[r][p];
@@ -437,11 +438,13 @@ __global__ void __launch_bounds__(256, 2) bg_tile_kernel(BgArgs A) {
     const int4 bx = make_int4(box.x0, box.x1, box.y0, box.y1);
     for (int j = A.nbr_off[target]; j < A.nbr_off[target + 1]; ++j) {
       const int item = A.nbr_idx[j] * A.n_img + b;
+      CG_CHECK(A.nbr_idx[j] >= 0 && A.nbr_idx[j] < A.n_src);
       const ItemHdr* hp = a.hdr + item;
       const int2 o = *reinterpret_cast<const int2*>(&hp->ox);
       ft_source(a, item, hp->K, bx, o, (float)hp->flux, q, lane, wtab, lam, issued);
     }
     const int wbox = box.x1 - box.x0;
+    CG_CHECK((long long)(box.y1 - box.y0) * wbox <= A.max_patch_px);
     float* out = A.bg + target * A.max_patch_px;
 #pragma unroll
     for (int r = 0; r < 2; ++r) {

@@ -943,7 +943,7 @@ def eigen_fluxes(z, w, m, B, lam0, fluxes=None, fluxes_ivar=None):
     if w.shape[1] != K:
         raise ValueError("weights and basis disagree on K")
     dev = device()
-    d = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(dev)
+    d = lambda a: torch.from_numpy(np.array(a, dtype=np.float64, order="C")).to(dev)   # a writable copy
     d_z, d_w, d_m, d_B, d_l = d(z), d(w), d(m), d(B), d(lam0)
     mu = torch.zeros((Cn, CG_NUM_BANDS), dtype=torch.float64, device=dev)
     ll, d_f, d_iv = None, None, None
