@@ -781,7 +781,7 @@ def main():
     if world > 1:
         # Tear-down: graphs first, then the communicator.  A stalled tear-down must be VISIBLE: the
         # watchdog ends the process with a non-zero status.
-        wd = threading.Timer(60.0, lambda: (sys.stderr.write("NCCL tear-down stalled\n"), os._exit(3)))
+        wd = threading.Timer(300.0, lambda: (sys.stderr.write("NCCL tear-down stalled\n"), os._exit(3)))
         wd.daemon = True
         wd.start()
         torch.cuda.synchronize()

@@ -2022,7 +2022,7 @@ struct Philox {
     ctr[0] = c0; ctr[1] = lo1; ctr[2] = c2; ctr[3] = lo0;
   }
   // uniform in (0, 1) with 53 random bits, from counter value (a, b, c, d)
-  __device__ __forceinline__ double uniform(uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  __device__ __noinline__ double uniform(uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
     ctr[0] = a; ctr[1] = b; ctr[2] = c; ctr[3] = d;
     uint32_t k0 = key[0], k1 = key[1];
 #pragma unroll
@@ -2040,7 +2040,10 @@ struct Philox {
 // small, else outwards from the mode (Kemp 1986), whose expected number of
 // steps is O(sqrt(n p q)).  deps/randomkit/distributions.c:239-449 switches
 // between inversion and BTPE rejection; both sample the same law.
-__device__ double binomial_from_uniform(long long n, double p, double U) {
+// (__noinline__: the allocation kernels draw at 8 unrolled pixel sites per lane; inlined, the body --
+// exp, log1p, three lgamma -- is replicated at every site and the kernel stalls on instruction fetch:
+// ncu showed 24.8 warps waiting on `no_instruction` per issue before, profiles/r02_prof_alloc_*.)
+__device__ __noinline__ double binomial_from_uniform(long long n, double p, double U) {
   if (n <= 0 || !(p > 0.)) return 0.;
   if (p >= 1.) return (double)n;
   const bool flip = p > 0.5;
