@@ -176,7 +176,7 @@ struct Counters {
   int total_strips;    // partial-sum slots handed out
   int work_counter;
   int guard_count;
-  int err_flag;        // 1: footprint larger than max_patch_px, 2: guard list overflow, 3: work list overflow, 4: CG_SRC_EIGEN row outside the flux table
+  int err_flag;        // 1: footprint larger than max_patch_px, 2: guard list overflow, 3: work list overflow, 4: CG_SRC_EIGEN row outside the flux table, 5: CG_SRC_PLANCK without filter curves
   unsigned long long evals;    // algorithmic: footprint pixels x components
   unsigned long long issued;   // lane-evaluations actually issued after culling (warp granular)
   int heavy_strips;    // work units of galaxies, listed from the front of the work list
@@ -532,8 +532,16 @@ __device__ __forceinline__ ItemGeom item_table(const DevImage& im, const CgSourc
       s00 = var * Wm[0] + im.psf_cov[k][0];
       s11 = var * Wm[1] + im.psf_cov[k][1];
       s01 = var * Wm[2] + im.psf_cov[k][2];
-      double dist = sqrt(im.psf_mu[k][0] * im.psf_mu[k][0] + im.psf_mu[k][1] * im.psf_mu[k][1]);
-      mybound = fmax(mybound, major_axis(s00, s11, s01, Rsq_gal) + dist);
+      // The footprint radius is the max over components of (major axis + |psf mean|)
+      // (bounding_box.py:27-31).  For a fixed PSF component the major axis grows with the profile
+      // variance (var W is positive definite), so the maximum sits on the profile component of largest
+      // variance -- the LAST one of the included profiles (dev 8.40 > exp 1.50): only those n_psf
+      // components pay for the 4 square roots and 7 divisions of major_axis; the value is the one
+      // the full loop would return.
+      if (j == n_exp + n_dev - 1) {
+        double dist = sqrt(im.psf_mu[k][0] * im.psf_mu[k][0] + im.psf_mu[k][1] * im.psf_mu[k][1]);
+        mybound = fmax(mybound, major_axis(s00, s11, s01, Rsq_gal) + dist);
+      }
     }
     mux = px + im.psf_mu[k][0];
     muy = py + im.psf_mu[k][1];
@@ -588,6 +596,9 @@ __device__ __forceinline__ double item_flux(const DevImage& im, const CgSource& 
       flux = (double)NAN;
       g.err = 4;
     }
+  } else if (star && (s.flags & CG_SRC_PLANCK) && s.t != 0.0 && !filters->loaded) {
+    flux = (double)NAN;                 // cg_set_filter_curves has not been called: fail loudly, not with a dark star
+    g.err = 5;
   } else if (star && (s.flags & CG_SRC_PLANCK) && s.t != 0.0) {
     double ppj = planck_photons_per_joule_warp(filters, s.t, im.band, lane);
     ppj = __shfl_sync(0xffffffffu, ppj, 0);
@@ -2609,7 +2620,8 @@ int64_t cg_last_eval_count(void* stream) {
     fail(CG_ENOMEM, c.err_flag == 1 ? "a footprint exceeded max_patch_px"
                                     : (c.err_flag == 2 ? "guard list overflow"
                                     : (c.err_flag == 3 ? "work list overflow"
-                                                       : "a CG_SRC_EIGEN source points outside the bound flux table")));
+                                    : (c.err_flag == 4 ? "a CG_SRC_EIGEN source points outside the bound flux table"
+                                                       : "a CG_SRC_PLANCK star was rendered before cg_set_filter_curves"))));
     return -(int64_t)c.err_flag;
   }
   return (int64_t)c.evals;

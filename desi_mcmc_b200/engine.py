@@ -382,8 +382,10 @@ def _srcs_dev(srcs):
     if isinstance(srcs, torch.Tensor):
         return srcs, srcs.numel() // SRC_DTYPE.itemsize
     if isinstance(srcs, np.ndarray) and srcs.dtype == SRC_DTYPE:
+        _need_filters(srcs)
         return to_device(srcs), srcs.shape[0]
     arr = pack_sources(list(srcs))
+    _need_filters(arr)                       # black-body stars need the filter curves on the device
     return to_device(arr), arr.shape[0]
 
 

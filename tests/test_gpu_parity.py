@@ -490,3 +490,24 @@ def test_score_proposals_bright_source_guard(engine, oracle):
     err = np.max(np.abs(d_raw - want))
     print("auto guard %.3g, re-scored %d of %d, raw fp32 |delta error| %.3g" % (auto.guard, n_guard, P, err))
     assert err < auto.guard                                     # the band covers the fp32 error
+
+
+def test_planck_without_filter_curves_fails_loudly(engine):
+    """A black-body star rendered before cg_set_filter_curves must not come out dark: the device
+    flags it and the synchronising entry points raise (the engine loads the packaged curves itself
+    whenever it packs or receives a CG_SRC_PLANCK source; this drives the C ABI past that)."""
+    import torch
+    from desi_mcmc_b200 import _ffi
+    field = synth.make_field(80, H=64, W=64, n_src=2, star_frac=1.0, planck_frac=1.0, margin=20)
+    gimgs = hp.gpu_images(engine, field, [np.full((64, 64), 400.)] * 5)
+    packed = engine.pack_sources(hp.gpu_sources(engine, field))
+    assert np.all(packed["flags"] & _ffi.CG_SRC_PLANCK)
+    _ffi.check(engine.lib().cg_shutdown())              # drops the device filter table
+    engine._state.update(device=None, filters=False)
+    engine.init(0)
+    gimgs = hp.gpu_images(engine, field, [np.full((64, 64), 400.)] * 5)
+    d_srcs = engine.to_device(packed)                    # device bytes: the engine does not inspect them
+    with pytest.raises(MemoryError):
+        engine.field_loglik(gimgs, d_srcs)
+    ll = engine.field_loglik(gimgs, packed).cpu().numpy()       # a host array: the curves are loaded first
+    assert np.all(np.isfinite(ll))
