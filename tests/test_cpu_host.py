@@ -159,3 +159,32 @@ def test_bench_reference_arm_runs():
     line = json.loads(res.stdout.strip().splitlines()[-1])
     assert line["impl"] == "reference" and line["value"] > 0 and line["unit"] == "evals/s"
     assert line["cpu_baseline"]["kind"] in ("reference", "port") and line["e2e"]["h2d_bytes_per_step"] == 0
+
+
+def test_static_boxes_and_active_neighbours_follow_the_reference():
+    """Host logic of the crowded-field sweep: engine.static_boxes == make_bbox_dict (sources.py:434-455,
+    oracle.make_bbox) and engine.active_neighbours == get_active_sources' intersection test
+    (sources.py:457-472), brute force."""
+    import types
+    from desi_mcmc_b200 import engine, synth
+    from oracle import ref_cpu as ref
+    field = synth.make_crowded_field(5, H=300, W=340, n_src=150)
+    imgs_o = [ref.SyntheticImage(nelec=np.zeros((300, 340)), **synth.image_kwargs(m)) for m in field["images"]]
+    imgs = [types.SimpleNamespace(phi_n=o.phi_n, rho_n=o.rho_n, Ups_n_inv=o.Ups_n_inv, shape=(300, 340)) for o in imgs_o]
+    u = np.array([s["u"] for s in field["sources"]])
+    boxes = engine.static_boxes(imgs, u, 25.)
+    for k in range(0, 150, 7):
+        src = ref.SrcParams(u=u[k], a=0, fluxes=np.ones(5))
+        for b, o in enumerate(imgs_o):
+            xlim, ylim = ref.make_bbox(src, o, 25.)
+            bx = boxes[k, b]
+            assert (bx["x0"], bx["x1"], bx["y0"], bx["y1"]) == (xlim[0], xlim[1], ylim[0], ylim[1])
+    offs, idx = engine.active_neighbours(boxes)
+    assert offs.shape == (150 * 5 + 1,) and offs[-1] == idx.size and idx.size > 150
+    for k in range(0, 150, 11):
+        for b in range(5):
+            a = boxes[k, b]
+            want = [t for t in range(150) if t != k and
+                    abs(int(a["x0"]) - int(boxes[t, b]["x0"])) * 2 < (a["x1"] - a["x0"]) + (boxes[t, b]["x1"] - boxes[t, b]["x0"]) and
+                    abs(int(a["y0"]) - int(boxes[t, b]["y0"])) * 2 < (a["y1"] - a["y0"]) + (boxes[t, b]["y1"] - boxes[t, b]["y0"])]
+            assert list(idx[offs[k * 5 + b]:offs[k * 5 + b + 1]]) == want
