@@ -380,9 +380,12 @@ def bench_crowded(engine, synth, steps, pk, with_cpu):
     slice_s = time.perf_counter() - t0
     slice_leg = {"what": "Source.resample_location (sources.py:308-319) for all 5000 sources in ONE launch "
                          "(cg_slice_sample_locations), host-supplied uniforms; wall clock incl. the upload of the uniforms",
-                 "ms": slice_s * 1e3, "likelihood_evaluations": int(sl_evals.sum()),
-                 "evaluations_per_s": float(sl_evals.sum() / slice_s),
-                 "sources_finished_on_device": int((status == 0).sum()), "sources_flagged": int((status != 0).sum())}
+                 "ms": slice_s * 1e3, "kernel_ms": sw.slice_stats["kernel_ms"],
+                 "likelihood_evaluations": int(sl_evals.sum()),
+                 "evaluations_per_s": float(sl_evals.sum() / (sw.slice_stats["kernel_ms"] * 1e-3)),
+                 "uniforms_per_source": {"block": 256, "max_used": int(sw.slice_stats["used"].max())},
+                 "sources_finished_on_device": int((status == 0).sum()),
+                 "comparisons_decided_in_float64": int(sw.slice_stats["refined"].sum())}
     # backgrounds: every active neighbour rendered on the target's box (sources.py:481)
     offs, idx = sw.h_nbr
     st = sw.h_static

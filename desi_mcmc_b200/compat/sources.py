@@ -420,9 +420,9 @@ def resample_sources_on_device(srcs, seed=0, rngs=None, n_uniforms=160):
     SURVEY.md 8f N2).  Source s draws from rngs[s] (default RandomState(seed + s)) in the reference's
     order: gamma conditionals of the fluxes, the coordinate shuffle, then the sampler's uniforms -- a
     block of n_uniforms is handed to the device and the generator is advanced by exactly the number
-    consumed, so the stream continues as if the loop had run on the host.  A source the device flags
-    (block exhausted, comparison inside the float64 guard band, NaN) is redone by the lock-step host
-    sampler from the same generator state.  The result equals resample_sources_batched / the
+    consumed, so the stream continues as if the loop had run on the host.  Comparisons inside the
+    float64 guard band are decided in the kernel; a source the device flags (block exhausted, NaN) is
+    redone by the lock-step host sampler from the same generator state.  The result equals resample_sources_batched / the
     per-source loop bit for bit.  -> dict(device=..., fallback=..., evals=...)."""
     from .slicesample import run_lockstep, slicesample_gen
     srcs = list(srcs)

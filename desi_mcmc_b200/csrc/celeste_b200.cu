@@ -884,8 +884,22 @@ __device__ __forceinline__ int cull_components(const float* gtab, int K, int lan
 // One WARP TILE (32 lane units = 256 pixels) of an item: cull the item's components against the
 // tile, evaluate, and either write the patch (MODE_PATCH) or return the tile's likelihood terms summed
 // over the warp (lane 0 holds the sum).  Shared by render_kernel and the on-device samplers.
-template <typename real, int MODE>
-__device__ __forceinline__ double render_warp_tile(const RenderArgs& a, const ItemHdr& h, long long item,
+// where the auxiliary patch of an item starts
+__device__ __forceinline__ long long aux_offset_of(const RenderArgs& a, int idx) {
+  return a.aux_offsets ? a.aux_offsets[idx] : (a.aux_stride ? (long long)idx * a.aux_stride : a.aux_off_v[idx]);
+}
+// the few fields render_warp_tile reads, for kernels that do not carry a whole RenderArgs
+struct TileArgs {
+  int cull, cond_sum;
+  float* patches;
+  long long max_patch_px;
+  const float* aux;
+  long long aux_stride;
+};
+__device__ __forceinline__ long long aux_offset_of(const TileArgs& a, int idx) { return (long long)idx * a.aux_stride; }
+
+template <typename real, int MODE, typename Args>
+__device__ __forceinline__ double render_warp_tile(const Args& a, const ItemHdr& h, long long item,
                                                    const real* s_tab, float* s_wtab, int wt, int lane, int wbox,
                                                    int hbox, int cpr, int hp, int n_lu, float r_band,
                                                    const DevImage* imp, real fl, const LogTable* logt,
@@ -998,7 +1012,7 @@ __device__ __forceinline__ double render_warp_tile(const RenderArgs& a, const It
         if (rr == 1 && !two) break;
         const int row = rr ? row1 : row0;
         const long long poff = (long long)row * wbox + cx;
-        const float* auxp = (h.aux >= 0) ? a.aux + (a.aux_offsets ? a.aux_offsets[h.aux] : (a.aux_stride ? (long long)h.aux * a.aux_stride : a.aux_off_v[h.aux])) + poff : nullptr;
+        const float* auxp = (h.aux >= 0) ? a.aux + aux_offset_of(a, h.aux) + poff : nullptr;
         const long long ioff = (long long)(h.y0 + row) * im.W + (h.x0 + cx);
 #pragma unroll
         for (int p = 0; p < PIX_PER_THREAD; ++p) {

@@ -473,8 +473,10 @@ __global__ void __launch_bounds__(256, 2) bg_tile_kernel(BgArgs A) {
 // Random numbers are HOST-supplied, in the reference's call order: ord[s] = the shuffled coordinate
 // order, uni[s][0..B) = the uniforms the sampler draws one after the other (log_uni = their float64
 // logarithms, taken on the host so that the slice level matches numpy's).  A source that runs out of
-// uniforms, meets a NaN, or has a comparison inside the guard band stops with a status: the host
-// redoes that source with the lock-step sampler (float64 refinement) from the same RNG state.
+// uniforms or meets a NaN stops with a status: the host redoes that source with the lock-step sampler
+// from the same RNG state.  A comparison inside the guard band is decided in the kernel by float64
+// evaluations of level and value (item_table<double> / render_warp_tile<double>: the use_fp64 path of
+// cg_items_loglik), exactly as compat.slicesample does on the host.
 #define SLICE_MAX_IMG 8
 struct SliceArgs {
   ImgPtrs imgs;
@@ -489,8 +491,9 @@ struct SliceArgs {
   double sigma, guard;
   double* ll_out;              // [n_src] likelihood at the accepted point
   int* n_used;                 // [n_src] uniforms consumed
-  int* status;                 // [n_src] 0 ok, 1 out of uniforms, 2 guard band, 3 NaN, 4 shrank to zero
+  int* status;                 // [n_src] 0 ok, 1 out of uniforms, 3 NaN, 4 shrank to zero
   int* n_evals;                // [n_src] likelihood evaluations
+  int* n_refined;              // [n_src] comparisons decided in float64 (may be NULL)
   const FilterTables* filters;
   const double* flux_table;
   long long flux_rows;
@@ -498,16 +501,16 @@ struct SliceArgs {
   int cull;
 };
 
+#define SLICE_WARP_BYTES (CG_MAX_COMP * TAB_W * 8 + (CG_MAX_COMP + 1) * 8 * 4)   /* float64-sized table + compacted table */
 __global__ void __launch_bounds__(32 * SLICE_MAX_IMG) slice_location_kernel(SliceArgs A) {
-  __shared__ __align__(16) float s_tab_all[SLICE_MAX_IMG][TAB_STRIDE];
-  __shared__ __align__(16) float s_wtab_all[SLICE_MAX_IMG][CG_MAX_COMP * 8];
+  extern __shared__ __align__(16) unsigned char s_dyn[];           // n_img x SLICE_WARP_BYTES
   __shared__ double s_ll[SLICE_MAX_IMG];
   const int s = blockIdx.x;
   if (s >= A.n_src) return;
   const int lane = threadIdx.x & 31, b = threadIdx.x >> 5;       // warp b <-> image b
   const DevImage& im = *A.imgs.p[b];
-  float* const s_tab = s_tab_all[b];
-  float* const s_wtab = s_wtab_all[b];
+  unsigned char* const my = s_dyn + (size_t)b * SLICE_WARP_BYTES;
+  float* const s_wtab = reinterpret_cast<float*>(my + CG_MAX_COMP * TAB_W * 8);
   CgSource src = A.srcs[s];
   const CgBox box0 = A.boxes[(long long)s * A.n_img + b];
   // the fixed box, clipped to the image as prepare_kernel clips CG_ITEM_FIXED_BOX
@@ -521,26 +524,26 @@ __global__ void __launch_bounds__(32 * SLICE_MAX_IMG) slice_location_kernel(Slic
   const int n_lu = cpr * hp;
   const int n_strips = (int)(((long long)hp * cpr + 31) / 32);
   const float r_band = __frcp_rn((float)max(cpr * TILE_R, 1));
-  RenderArgs ra;                       // only the fields render_warp_tile<MODE_COND> reads
-  ra.cull = A.cull; ra.aux = A.aux; ra.aux_offsets = nullptr; ra.aux_stride = A.aux_stride; ra.cond_sum = 0;
-  ra.patches = nullptr; ra.max_patch_px = 0;
+  TileArgs ra;
+  ra.cull = A.cull; ra.cond_sum = 0; ra.patches = nullptr; ra.max_patch_px = 0; ra.aux = A.aux; ra.aux_stride = A.aux_stride;
   unsigned long long issued = 0;
-  int evals = 0;
+  int evals = 0, refined = 0;
 
-  // Source.log_likelihood(u = x) summed over the images (sources.py:134-183)
-  auto loglik = [&](double x0, double x1) -> double {
+  // Source.log_likelihood(u = x) summed over the images (sources.py:134-183); tag = float: the fp32 path
+  // of cg_items_loglik; tag = double: its use_fp64 path (the guard band's evaluation)
+  auto loglik = [&](auto tag, double x0, double x1) -> double {
+    typedef decltype(tag) real;
+    real* const s_tab = reinterpret_cast<real*>(my);
     src.u[0] = x0; src.u[1] = x1;
     __syncthreads();                   // every warp is done with the previous evaluation's tables and s_ll
-    ItemGeom g = item_table<float>(im, src, h.flags, lane, s_tab);
+    ItemGeom g = item_table<real>(im, src, h.flags, lane, s_tab);
     const double flux = item_flux(im, src, h.flags, lane, g.star, A.filters, A.flux_table, A.flux_rows, g);
     h.ox = g.ox; h.oy = g.oy; h.K = g.K; h.flux = flux; h.norm_term = flux * im.psf_wsum;
     __syncwarp();
     double t = 0.0;
-    if (g.K > 0 || true) {
-      for (int wt = 0; wt < n_strips; ++wt)         // the order items_finalize_kernel sums the strips in
-        t += render_warp_tile<float, MODE_COND>(ra, h, 0, s_tab, s_wtab, wt, lane, wbox, hbox, cpr, hp, n_lu, r_band,
-                                                &im, (float)flux, A.logtab, issued);
-    }
+    for (int wt = 0; wt < n_strips; ++wt)         // the order items_finalize_kernel sums the strips in
+      t += render_warp_tile<real, MODE_COND>(ra, h, 0, s_tab, s_wtab, wt, lane, wbox, hbox, cpr, hp, n_lu, r_band,
+                                             &im, (real)flux, A.logtab, issued);
     if (lane == 0) s_ll[b] = t - h.norm_term;         // CG_LL_CONDITIONAL (sources.py:174)
     __syncthreads();
     double tot = 0.0;
@@ -559,15 +562,24 @@ __global__ void __launch_bounds__(32 * SLICE_MAX_IMG) slice_location_kernel(Slic
     if (idx + 2 > A.B) { st = 1; break; }
     double upper = A.sigma * U[idx++];                      // slicesample.py:155-156
     double lower = upper - A.sigma;
-    const double llh_s = LU[idx++] + loglik(x[0], x[1]);    // :159
+    const double log_u = LU[idx++];
+    const double llh_s = log_u + loglik(0.f, x[0], x[1]);   // :159
+    double level64 = 0.0;
+    bool have64 = false;
     for (;;) {                                              // :181-198 (step_out = False)
       if (idx >= A.B) { st = 1; break; }
       const double z = (upper - lower) * U[idx++] + lower;
       const double xt0 = (d == 0 ? 1.0 : 0.0) * z + x[0], xt1 = (d == 1 ? 1.0 : 0.0) * z + x[1];
-      ll_new = loglik(xt0, xt1);
+      ll_new = loglik(0.f, xt0, xt1);
       if (ll_new != ll_new) { st = 3; break; }
-      if (A.guard > 0. && fabs(ll_new - llh_s) < A.guard) { st = 2; break; }
-      if (ll_new > llh_s) { x[0] = xt0; x[1] = xt1; break; }
+      bool above = ll_new > llh_s;
+      if (A.guard > 0. && fabs(ll_new - llh_s) < A.guard) {
+        // inside the guard band: level and value again in float64 (compat.slicesample's `above`)
+        if (!have64) { level64 = log_u + loglik(0., x[0], x[1]); have64 = true; }
+        above = loglik(0., xt0, xt1) > level64;
+        ++refined;
+      }
+      if (above) { x[0] = xt0; x[1] = xt1; break; }
       else if (z < 0) lower = z;
       else if (z > 0) upper = z;
       else { st = 4; break; }
@@ -578,6 +590,7 @@ __global__ void __launch_bounds__(32 * SLICE_MAX_IMG) slice_location_kernel(Slic
     A.n_used[s] = idx;
     A.n_evals[s] = evals;
     A.ll_out[s] = ll_new;
+    if (A.n_refined) A.n_refined[s] = refined;
     if (st == 0) { A.srcs[s].u[0] = x[0]; A.srcs[s].u[1] = x[1]; }
   }
 }
@@ -964,7 +977,7 @@ int cg_slice_sample_locations(CgImage* const* imgs, int32_t n_img, CgSource* d_s
                               const CgBox* d_boxes, const float* d_photons, int64_t max_patch_px,
                               const double* d_uniforms, const double* d_log_uniforms, const int32_t* d_order,
                               int32_t n_uniforms, double sigma, double guard, double* d_ll, int32_t* d_n_used,
-                              int32_t* d_status, int32_t* d_n_evals, void* stream) {
+                              int32_t* d_status, int32_t* d_n_evals, int32_t* d_n_refined, void* stream) {
   NEED_INIT();
   SliceArgs A;
   memset(&A, 0, sizeof A);
@@ -981,7 +994,11 @@ int cg_slice_sample_locations(CgImage* const* imgs, int32_t n_img, CgSource* d_s
   A.guard = guard; A.ll_out = d_ll; A.n_used = d_n_used; A.status = d_status; A.n_evals = d_n_evals;
   A.filters = g_d_filters; A.flux_table = g_flux_table; A.flux_rows = g_flux_rows; A.logtab = g_d_logtab;
   A.cull = g_cull | (g_recur ? 0 : 2);
-  slice_location_kernel<<<n_src, 32 * n_img, 0, (cudaStream_t)stream>>>(A);
+  A.n_refined = d_n_refined;
+  const size_t smem = (size_t)n_img * SLICE_WARP_BYTES;
+  if (smem > 48 * 1024)
+    CUDA_TRY(cudaFuncSetAttribute(slice_location_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  slice_location_kernel<<<n_src, 32 * n_img, smem, (cudaStream_t)stream>>>(A);
   LAUNCH_CHECK();
   return CG_OK;
 }

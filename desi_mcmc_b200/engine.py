@@ -1215,18 +1215,24 @@ class GibbsSweep(object):
             self.d_nbr_off.data_ptr(), self.d_nbr_idx.data_ptr(), self.max_patch_px, self.side,
             self.bg.data_ptr(), self.ws_bg.data_ptr(), self.ws_bg.numel(), stream_ptr()))
 
-    def slice_locations(self, seed: int, n_uniforms: int = 160, sigma: float = 1.0):
+    def slice_locations(self, seed: int, n_uniforms: int = 256, sigma: float = 1.0):
         """Source.resample_location (sources.py:308-319) for every source given the allocated photons, the
         slice samplers run on the device in ONE launch (cg_slice_sample_locations).  The uniforms come from
-        one host RandomState(seed): row s of a [n_src, n_uniforms] block is source s's stream.  Sources the
-        device flags (status != 0: out of uniforms, float64 guard band, NaN) keep their location this sweep.
+        one host RandomState(seed): row s of a [n_src, n_uniforms] block is source s's stream.  Near-ties
+        are decided in float64 inside the kernel; a source that exhausts its block or meets a NaN (status
+        != 0, not expected with the default block) raises.
         Returns (status, n_evals) host arrays."""
         rng = np.random.RandomState(int(seed) & 0x7fffffff)
         order = np.where(rng.uniform(size=(self.n_src, 1)) < .5, [[0, 1]], [[1, 0]]).astype(np.int32)
         uni = rng.random_sample((self.n_src, n_uniforms))
         ll, used, status, evals = slice_sample_locations(self.images, self.d_cur, self.n_src, self.d_boxes, self.samp,
                                                          self.max_patch_px, uni, order, sigma=sigma, guard=self.guard)
-        self.slice_stats = dict(ll=ll, used=used, status=status, evals=evals)
+        self.slice_stats = dict(ll=ll, used=used, status=status, evals=evals,
+                                refined=slice_sample_locations.last_refined,
+                                kernel_ms=slice_sample_locations.last_kernel_ms)
+        if np.any(status != 0):
+            raise RuntimeError("on-device slice sampler: %d sources stopped with status %s (raise n_uniforms)" %
+                               (int((status != 0).sum()), sorted(set(status[status != 0].tolist()))))
         return status, evals
 
     def loglik(self):
@@ -1358,9 +1364,15 @@ def slice_sample_locations(images: Sequence[Image], d_srcs: torch.Tensor, n_src:
     used = torch.zeros(n_src, dtype=torch.int32, device=dev)
     status = torch.zeros(n_src, dtype=torch.int32, device=dev)
     evals = torch.zeros(n_src, dtype=torch.int32, device=dev)
+    refined = torch.zeros(n_src, dtype=torch.int32, device=dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
     check(lib().cg_slice_sample_locations(harr, n_img, d_srcs.data_ptr(), int(n_src), d_boxes.data_ptr(),
                                           photons.data_ptr(), int(max_patch_px), d_u.data_ptr(), d_lu.data_ptr(),
                                           d_ord.data_ptr(), uniforms.shape[1], float(sigma), float(guard),
                                           ll.data_ptr(), used.data_ptr(), status.data_ptr(), evals.data_ptr(),
-                                          stream_ptr()))
+                                          refined.data_ptr(), stream_ptr()))
+    e1.record()
+    slice_sample_locations.last_refined = refined.cpu().numpy()
+    slice_sample_locations.last_kernel_ms = e0.elapsed_time(e1)
     return ll.cpu().numpy(), used.cpu().numpy(), status.cpu().numpy(), evals.cpu().numpy()

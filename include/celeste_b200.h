@@ -408,15 +408,16 @@ int cg_prior_stats(const double* d_resp, const double* d_c, int64_t N, int32_t K
  * d_order [n_src][2] the shuffled coordinate order, d_uniforms / d_log_uniforms [n_src][n_uniforms]
  * the uniforms the sampler consumes one after the other and their logarithms.  Outputs per source:
  * the new location written into d_srcs (status 0 only), d_ll the likelihood there, d_n_used the
- * uniforms consumed (to advance the host generator by exactly that many), d_n_evals, d_status:
- * 0 done; 1 ran out of uniforms; 2 a comparison fell within `guard` of a tie (decide it in float64:
- * redo the source on the host path); 3 NaN likelihood; 4 shrank to zero (the reference raises).
+ * uniforms consumed (to advance the host generator by exactly that many), d_n_evals, d_n_refined
+ * (optional: comparisons that fell within `guard` of a tie and were decided by float64 evaluations of
+ * level and value inside the kernel), d_status: 0 done; 1 ran out of uniforms (redo the source on the
+ * host path); 3 NaN likelihood; 4 shrank to zero (the reference raises).
  * Likelihood values, decisions and traces are bit-identical to the lock-step path (cg_items_loglik). */
 int cg_slice_sample_locations(CgImage* const* imgs, int32_t n_img, CgSource* d_srcs, int32_t n_src,
                               const CgBox* d_boxes, const float* d_photons, int64_t max_patch_px,
                               const double* d_uniforms, const double* d_log_uniforms, const int32_t* d_order,
                               int32_t n_uniforms, double sigma, double guard, double* d_ll, int32_t* d_n_used,
-                              int32_t* d_status, int32_t* d_n_evals, void* stream);
+                              int32_t* d_status, int32_t* d_n_evals, int32_t* d_n_refined, void* stream);
 
 /* ---- per-sweep statistics for the all-reduce ------------------ */
 /* Sufficient statistics of the empirical colour prior over the sources of one type, straight from
