@@ -16,6 +16,8 @@ import numpy as np
 PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(PKG, "libceleste_b200_checked.so" if os.environ.get("CG_CHECKED") == "1"
                         else "libceleste_b200.so")     # CG_CHECKED=1: the build with bounds asserts in the kernels
+if os.environ.get("CG_LIB_VARIANT"):                   # kernel experiments: libceleste_b200_<variant>.so (tools/gpu_variant.sh)
+    LIB_PATH = os.path.join(PKG, "libceleste_b200_%s.so" % os.environ["CG_LIB_VARIANT"])
 
 CG_ABI_VERSION = 2
 CG_MAX_PSF = 4

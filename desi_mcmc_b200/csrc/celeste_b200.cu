@@ -203,6 +203,9 @@ static_assert(CG_MAX_COMP < 64, "bin-list entries pack item * 64 + K; cull_compo
 
 #define STRIP_THREADS 256
 #define PIX_PER_THREAD 4
+#ifndef PREP_WARPS
+#define PREP_WARPS 4        // items (warps) per prepare_kernel CTA
+#endif
 // Work decomposition of a footprint.  A LANE UNIT is two 4-pixel chunks in
 // the same columns of two rows of a 16-row tile band (rows r and r + R/2 of a
 // band of R rows); lane units are numbered in TILE-MAJOR order (tiles of
@@ -324,20 +327,41 @@ __device__ __forceinline__ f32x2 pk2(float lo, float hi) {
 __device__ __forceinline__ void unpk2(f32x2 v, float& lo, float& hi) {
   asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
 }
-__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
-  f32x2 r;
-  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-  return r;
-}
 __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
   f32x2 r;
   asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
   return r;
 }
-__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+__device__ __forceinline__ f32x2 mul2_raw(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 add2_raw(f32x2 a, f32x2 b) {
   f32x2 r;
   asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
   return r;
+}
+#ifndef FT_FMA_ONLY
+#define FT_FMA_ONLY 0
+#endif
+// FT_FMA_ONLY: products and sums issued as FFMA2 (a * b + (-0) and a * 1 + b round exactly like
+// a * b and a + b, signed zeros included)
+// (the constants live in constant memory so that ptxas cannot fold the FFMA2 back into FMUL2 / FADD2)
+__constant__ unsigned long long c_pk_negz = 0x8000000080000000ull, c_pk_one = 0x3f8000003f800000ull;
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+#if FT_FMA_ONLY
+  return fma2(a, b, c_pk_negz);
+#else
+  return mul2_raw(a, b);
+#endif
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+#if FT_FMA_ONLY
+  return fma2(a, c_pk_one, b);
+#else
+  return add2_raw(a, b);
+#endif
 }
 // recur_row4 on two rows at once: e = (row r, row r + 8), likewise g and acc; h the same on both
 __device__ __forceinline__ void recur_row4x2(f32x2 e, f32x2 g, f32x2 h, f32x2 (&acc)[4]) {
@@ -620,7 +644,7 @@ __device__ __forceinline__ double item_flux(const DevImage& im, const CgSource& 
 template <typename real>
 __global__ void __launch_bounds__(128) prepare_kernel(PrepArgs a) {
   const int lane = threadIdx.x & 31;
-  const long long i = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
+  const long long i = (long long)blockIdx.x * PREP_WARPS + (threadIdx.x >> 5);
   if (i >= a.n_items) return;
 
   CgItem it;
@@ -1154,8 +1178,14 @@ struct FieldArgs {
 #ifndef FT_THREADS
 #define FT_THREADS 256
 #endif
+#ifndef FT_STAGE_D
+#define FT_STAGE_D 0        // pixel counts staged in shared memory by cp.async (0: held in registers, 3 CTAs/SM)
+#endif
+#ifndef FT_LAUNCH_THREADS
+#define FT_LAUNCH_THREADS FT_THREADS   // fewer warps per CTA leave registers for the next set's prepare_kernel to co-reside
+#endif
 #ifndef FT_MINB
-#define FT_MINB 3
+#define FT_MINB (FT_STAGE_D ? 4 : 3)
 #endif
 #define FT_CHUNK 8
 #ifndef FT_UNROLL
@@ -1457,6 +1487,11 @@ __device__ __forceinline__ void ft_source(const FieldArgs& a, int item, int K, i
 // 3 CTAs x 8 warps per SM at 80 registers (no spills; 4 CTAs at 64 registers spill the pixel counts and measured slower)
 __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldArgs a) {
   __shared__ __align__(16) float s_wtab[FT_THREADS / 32][(CG_MAX_COMP + 1) * 8];   // + the prefetch row
+#if FT_STAGE_D
+  // the bin's pixel counts wait in shared memory (cp.async) until the epilogue: 8 registers fewer
+  // through the source loop, which is what lets the kernel run 4 CTAs per SM at 64 registers
+  __shared__ __align__(16) float4 s_d[FT_THREADS / 32][2][32];
+#endif
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float* const wtab = s_wtab[warp];
   const LogTable* const logt = a.logtab;
@@ -1545,6 +1580,40 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
     q.x = q.X0 + (lane & 3) * 4; q.yA = q.Y0 + (lane >> 2); q.yB = q.yA + 8;
 
     // pixel counts: independent of the source list, issue the loads first
+#if FT_STAGE_D
+    {
+      const bool vec = ((W & 3) == 0) && (((uintptr_t)im.nelec & 15) == 0);
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const int y = r ? q.yB : q.yA;
+        float4* dst = &s_d[warp][r][lane];
+        if (y < H && q.x < W) {
+          const float* rp = im.nelec + (long long)y * W + q.x;
+          if (vec) {
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(rp) : "memory");
+          } else {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            v.x = rp[0];
+            if (q.x + 1 < W) v.y = rp[1];
+            if (q.x + 2 < W) v.z = rp[2];
+            if (q.x + 3 < W) v.w = rp[3];
+            *dst = v;
+          }
+        } else {
+          *dst = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+#define FT_LOAD_D()                                                             \
+    float d[2][4];                                                              \
+    {                                                                           \
+      asm volatile("cp.async.wait_group 0;" ::: "memory");                      \
+      const float4 v0 = s_d[warp][0][lane], v1 = s_d[warp][1][lane];            \
+      d[0][0] = v0.x; d[0][1] = v0.y; d[0][2] = v0.z; d[0][3] = v0.w;           \
+      d[1][0] = v1.x; d[1][1] = v1.y; d[1][2] = v1.z; d[1][3] = v1.w;           \
+    }
+#else
     float d[2][4];
     {
       const bool vec = ((W & 3) == 0) && (((uintptr_t)im.nelec & 15) == 0);
@@ -1566,6 +1635,8 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
         }
       }
     }
+#define FT_LOAD_D()
+#endif
     const float eps = (float)im.epsilon;
     float* mdl = a.model ? a.model[img] : nullptr;
     double s = 0.0;
@@ -1574,6 +1645,7 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
       if (!have_nx) e_nx = __shfl_sync(0xffffffffu, dnext.x, 0) >= 0 ? list_entry(__shfl_sync(0xffffffffu, dnext.y, 0)) : 0x7fffffff;
       // no source reaches this bin: lambda = epsilon on every pixel, so its terms
       // are log(eps) * sum(x) - n * eps -- one log per warp instead of one per pixel
+      FT_LOAD_D()
       double sd = 0.0;
       int npx = 0;
 #pragma unroll
@@ -1643,6 +1715,7 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
       if (!have_nx) e_nx = __shfl_sync(0xffffffffu, dnext.x, 0) >= 0 ? list_entry(__shfl_sync(0xffffffffu, dnext.y, 0)) : 0x7fffffff;
       // Poisson terms.  log(lam) = T[bin] + res (log_accurate): sum x T in float64,
       // sum x res (|res| < 1/60) and the 4-pixel row sums of lam in fp32, then float64
+      FT_LOAD_D()
       float sres = 0.f;
       double slam = 0.0;
       if (q.x + 3 < W && q.yB < H) {                          // interior lane: no bounds tests
@@ -2364,6 +2437,23 @@ __global__ void __launch_bounds__(256) fma2_probe_kernel(float* out, int iters) 
   if (s == 123.456f) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// which = 8 / 9: packed FMUL2 / FADD2 chains, counted like which = 7
+template <int OP>
+__global__ void __launch_bounds__(256) pk2_probe_kernel(float* out, int iters) {
+  f32x2 v[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v[j] = pk2(0.5f + 0.001f * (float)(threadIdx.x + j), 0.25f + 0.001f * (float)(threadIdx.x + j));
+  const f32x2 a = OP == 0 ? pk2(0.9999f, 1.0001f) : pk2(1e-7f, -1e-7f);
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = OP == 0 ? mul2_raw(v[j], a) : add2_raw(v[j], a);
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { float lo, hi; unpk2(v[j], lo, hi); s += lo + hi; }
+  if (s == 123.456f) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 // Instruction-mix probes: the inner loop of field_tile_kernel / render_kernel in
 // isolation (no global memory, every lane busy), to measure what fraction of
 // the MUFU peak this MIX can reach on the device.  VAR 2: the full loop (table
@@ -2877,8 +2967,8 @@ static int run_prepare(const PrepArgs& pa_in, cudaStream_t st) {
   if (pa_in.n_items == 0) return CG_OK;
   PrepArgs pa = pa_in;
   pa.unit_wt = choose_unit_wt(pa.n_items);
-  unsigned blocks = (unsigned)((pa.n_items + 3) / 4);
-  prepare_kernel<real><<<blocks, 128, 0, st>>>(pa);
+  unsigned blocks = (unsigned)((pa.n_items + PREP_WARPS - 1) / PREP_WARPS);
+  prepare_kernel<real><<<blocks, 32 * PREP_WARPS, 0, st>>>(pa);
   LAUNCH_CHECK();
   return CG_OK;
 }
@@ -3044,7 +3134,7 @@ int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off, const CgSou
     }
   }
   const bool prof = prof_begin(st);
-  field_tile_kernel<<<g_sm_count * FT_MINB, FT_THREADS, 0, st>>>(fa);      // persistent: FT_MINB CTAs per SM (launch bounds)
+  field_tile_kernel<<<g_sm_count * FT_MINB, FT_LAUNCH_THREADS, 0, st>>>(fa);      // persistent: FT_MINB CTAs per SM (launch bounds)
   prof_end(prof, st);
   LAUNCH_CHECK();
   field_tile_final_kernel<<<n_img, 1024, 0, st>>>(fa);
@@ -3366,7 +3456,7 @@ int cg_pipe_probe(int which, double* ops_per_s, void* stream) {
   // which: 0 MUFU.EX2, 1 FFMA, 7 FFMA2 (packed; counted as 2 FMA per lane); 2..5 instruction-mix probes and 6 the row-recurrence loop at
   // 3 CTAs/SM (24 warps, the tile kernel's residency), 12..16 the same at 8 CTAs/SM (64 warps)
   const int var = which % 10;
-  const bool raw = var < 2 || which == 7;            // single-pipe probes: long chains, 8 CTAs/SM
+  const bool raw = var < 2 || (which >= 7 && which <= 9);   // single-pipe probes: long chains, 8 CTAs/SM
   const int iters = raw ? 4096 : 128, blocks = g_sm_count * ((which >= 2 && which < 10 && !raw) ? 3 : 8), threads = 256;
   float* d_out = nullptr;
   CUDA_TRY(cudaMalloc(&d_out, sizeof(float) * blocks * threads));
@@ -3379,6 +3469,8 @@ int cg_pipe_probe(int which, double* ops_per_s, void* stream) {
     if (which == 0) xu_probe_kernel<<<blocks, threads, 0, st>>>(d_out, iters);
     else if (which == 1) fma_probe_kernel<<<blocks, threads, 0, st>>>(d_out, iters);
     else if (which == 7) fma2_probe_kernel<<<blocks, threads, 0, st>>>(d_out, iters);
+    else if (which == 8) pk2_probe_kernel<0><<<blocks, threads, 0, st>>>(d_out, iters);
+    else if (which == 9) pk2_probe_kernel<1><<<blocks, threads, 0, st>>>(d_out, iters);
     else if (var == 2) mix_probe_kernel<2><<<blocks, threads, 0, st>>>(d_out, iters);
     else if (var == 3) mix_probe_kernel<3><<<blocks, threads, 0, st>>>(d_out, iters);
     else if (var == 4) mix_probe_kernel<4><<<blocks, threads, 0, st>>>(d_out, iters);
@@ -3394,7 +3486,7 @@ int cg_pipe_probe(int which, double* ops_per_s, void* stream) {
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   cudaFree(d_out);
-  if (ops_per_s) *ops_per_s = (double)blocks * threads * 8.0 * iters * (which == 7 ? 2.0 : (raw ? 1.0 : 32.0)) / (best * 1e-3);
+  if (ops_per_s) *ops_per_s = (double)blocks * threads * 8.0 * iters * ((which >= 7 && which <= 9) ? 2.0 : (raw ? 1.0 : 32.0)) / (best * 1e-3);
   return CG_OK;
 }
 

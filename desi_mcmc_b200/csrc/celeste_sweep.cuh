@@ -502,55 +502,81 @@ struct SliceArgs {
 };
 
 #define SLICE_WARP_BYTES (CG_MAX_COMP * TAB_W * 8 + (CG_MAX_COMP + 1) * 8 * 4)   /* float64-sized table + compacted table */
-__global__ void __launch_bounds__(32 * SLICE_MAX_IMG) slice_location_kernel(SliceArgs A) {
+// what one warp (one image of one source) carries from one likelihood evaluation to the next
+struct SliceCtx {
+  const DevImage* im;
+  CgSource src;
+  ItemHdr h;
+  unsigned char* my;           // this warp's SLICE_WARP_BYTES of shared memory
+  double* s_ll;                // [SLICE_MAX_IMG] the images' terms of the current evaluation
+  TileArgs ra;
+  const FilterTables* filters;
+  const double* flux_table;
+  long long flux_rows;
+  const LogTable* logtab;
+  unsigned long long issued;
+  int lane, b, n_img, wbox, hbox, cpr, hp, n_lu, n_strips, evals;
+  float r_band;
+};
+
+// Source.log_likelihood(u = x) summed over the images (sources.py:134-183); real = float: the fp32 path
+// of cg_items_loglik; real = double: its use_fp64 path (the guard band's evaluation).  Out of line: the
+// float64 instantiation is rare (a few comparisons per hundred sources) and must not set the kernel's
+// register count.
+template <typename real>
+__device__ __noinline__ double slice_loglik(SliceCtx& c, double x0, double x1) {
+  real* const s_tab = reinterpret_cast<real*>(c.my);
+  float* const s_wtab = reinterpret_cast<float*>(c.my + CG_MAX_COMP * TAB_W * 8);
+  const DevImage& im = *c.im;
+  c.src.u[0] = x0; c.src.u[1] = x1;
+  __syncthreads();                   // every warp is done with the previous evaluation's tables and s_ll
+  ItemGeom g = item_table<real>(im, c.src, c.h.flags, c.lane, s_tab);
+  const double flux = item_flux(im, c.src, c.h.flags, c.lane, g.star, c.filters, c.flux_table, c.flux_rows, g);
+  c.h.ox = g.ox; c.h.oy = g.oy; c.h.K = g.K; c.h.flux = flux; c.h.norm_term = flux * im.psf_wsum;
+  __syncwarp();
+  double t = 0.0;
+  for (int wt = 0; wt < c.n_strips; ++wt)         // the order items_finalize_kernel sums the strips in
+    t += render_warp_tile<real, MODE_COND>(c.ra, c.h, 0, s_tab, s_wtab, wt, c.lane, c.wbox, c.hbox, c.cpr, c.hp,
+                                           c.n_lu, c.r_band, c.im, (real)flux, c.logtab, c.issued);
+  if (c.lane == 0) c.s_ll[c.b] = t - c.h.norm_term;   // CG_LL_CONDITIONAL (sources.py:174)
+  __syncthreads();
+  double tot = 0.0;
+  for (int k = 0; k < c.n_img; ++k) tot += c.s_ll[k];  // image order: the lock-step driver's sum
+  ++c.evals;
+  return tot;
+}
+
+__global__ void __launch_bounds__(32 * SLICE_MAX_IMG, 2) slice_location_kernel(SliceArgs A) {
   extern __shared__ __align__(16) unsigned char s_dyn[];           // n_img x SLICE_WARP_BYTES
   __shared__ double s_ll[SLICE_MAX_IMG];
   const int s = blockIdx.x;
   if (s >= A.n_src) return;
-  const int lane = threadIdx.x & 31, b = threadIdx.x >> 5;       // warp b <-> image b
-  const DevImage& im = *A.imgs.p[b];
-  unsigned char* const my = s_dyn + (size_t)b * SLICE_WARP_BYTES;
-  float* const s_wtab = reinterpret_cast<float*>(my + CG_MAX_COMP * TAB_W * 8);
-  CgSource src = A.srcs[s];
-  const CgBox box0 = A.boxes[(long long)s * A.n_img + b];
+  SliceCtx c;
+  c.lane = threadIdx.x & 31; c.b = threadIdx.x >> 5;               // warp b <-> image b
+  c.im = A.imgs.p[c.b];
+  const DevImage& im = *c.im;
+  c.my = s_dyn + (size_t)c.b * SLICE_WARP_BYTES;
+  c.s_ll = s_ll;
+  c.src = A.srcs[s];
+  c.n_img = A.n_img;
+  const CgBox box0 = A.boxes[(long long)s * A.n_img + c.b];
   // the fixed box, clipped to the image as prepare_kernel clips CG_ITEM_FIXED_BOX
-  ItemHdr h;
+  ItemHdr& h = c.h;
   h.x0 = max(box0.x0, 0); h.y0 = max(box0.y0, 0); h.x1 = min(box0.x1, im.W); h.y1 = min(box0.y1, im.H);
   if (h.x1 <= h.x0 || h.y1 <= h.y0) { h.x1 = h.x0; h.y1 = h.y0; }
-  h.img = b; h.aux = s * A.n_img + b; h.flags = CG_ITEM_FLUX_BAND | CG_ITEM_FIXED_BOX; h.strip_start = 0;
-  const int wbox = h.x1 - h.x0, hbox = h.y1 - h.y0;
-  const int cpr = (wbox + PIX_PER_THREAD - 1) / PIX_PER_THREAD;
-  const int hp = (hbox / (2 * TILE_R)) * TILE_R + ((hbox % (2 * TILE_R)) + 1) / 2;
-  const int n_lu = cpr * hp;
-  const int n_strips = (int)(((long long)hp * cpr + 31) / 32);
-  const float r_band = __frcp_rn((float)max(cpr * TILE_R, 1));
-  TileArgs ra;
-  ra.cull = A.cull; ra.cond_sum = 0; ra.patches = nullptr; ra.max_patch_px = 0; ra.aux = A.aux; ra.aux_stride = A.aux_stride;
-  unsigned long long issued = 0;
-  int evals = 0, refined = 0;
-
-  // Source.log_likelihood(u = x) summed over the images (sources.py:134-183); tag = float: the fp32 path
-  // of cg_items_loglik; tag = double: its use_fp64 path (the guard band's evaluation)
-  auto loglik = [&](auto tag, double x0, double x1) -> double {
-    typedef decltype(tag) real;
-    real* const s_tab = reinterpret_cast<real*>(my);
-    src.u[0] = x0; src.u[1] = x1;
-    __syncthreads();                   // every warp is done with the previous evaluation's tables and s_ll
-    ItemGeom g = item_table<real>(im, src, h.flags, lane, s_tab);
-    const double flux = item_flux(im, src, h.flags, lane, g.star, A.filters, A.flux_table, A.flux_rows, g);
-    h.ox = g.ox; h.oy = g.oy; h.K = g.K; h.flux = flux; h.norm_term = flux * im.psf_wsum;
-    __syncwarp();
-    double t = 0.0;
-    for (int wt = 0; wt < n_strips; ++wt)         // the order items_finalize_kernel sums the strips in
-      t += render_warp_tile<real, MODE_COND>(ra, h, 0, s_tab, s_wtab, wt, lane, wbox, hbox, cpr, hp, n_lu, r_band,
-                                             &im, (real)flux, A.logtab, issued);
-    if (lane == 0) s_ll[b] = t - h.norm_term;         // CG_LL_CONDITIONAL (sources.py:174)
-    __syncthreads();
-    double tot = 0.0;
-    for (int k = 0; k < A.n_img; ++k) tot += s_ll[k];  // image order: the lock-step driver's sum
-    ++evals;
-    return tot;
-  };
+  h.img = c.b; h.aux = s * A.n_img + c.b; h.flags = CG_ITEM_FLUX_BAND | CG_ITEM_FIXED_BOX; h.strip_start = 0;
+  c.wbox = h.x1 - h.x0; c.hbox = h.y1 - h.y0;
+  c.cpr = (c.wbox + PIX_PER_THREAD - 1) / PIX_PER_THREAD;
+  c.hp = (c.hbox / (2 * TILE_R)) * TILE_R + ((c.hbox % (2 * TILE_R)) + 1) / 2;
+  c.n_lu = c.cpr * c.hp;
+  c.n_strips = (int)(((long long)c.hp * c.cpr + 31) / 32);
+  c.r_band = __frcp_rn((float)max(c.cpr * TILE_R, 1));
+  c.ra.cull = A.cull; c.ra.cond_sum = 0; c.ra.patches = nullptr; c.ra.max_patch_px = 0;
+  c.ra.aux = A.aux; c.ra.aux_stride = A.aux_stride;
+  c.filters = A.filters; c.flux_table = A.flux_table; c.flux_rows = A.flux_rows; c.logtab = A.logtab;
+  c.issued = 0; c.evals = 0;
+  int refined = 0;
+  const CgSource& src = c.src;
 
   const double* U = A.uni + (long long)s * A.B;
   const double* LU = A.log_uni + (long long)s * A.B;
@@ -563,20 +589,20 @@ __global__ void __launch_bounds__(32 * SLICE_MAX_IMG) slice_location_kernel(Slic
     double upper = A.sigma * U[idx++];                      // slicesample.py:155-156
     double lower = upper - A.sigma;
     const double log_u = LU[idx++];
-    const double llh_s = log_u + loglik(0.f, x[0], x[1]);   // :159
+    const double llh_s = log_u + slice_loglik<float>(c, x[0], x[1]);   // :159
     double level64 = 0.0;
     bool have64 = false;
     for (;;) {                                              // :181-198 (step_out = False)
       if (idx >= A.B) { st = 1; break; }
       const double z = (upper - lower) * U[idx++] + lower;
       const double xt0 = (d == 0 ? 1.0 : 0.0) * z + x[0], xt1 = (d == 1 ? 1.0 : 0.0) * z + x[1];
-      ll_new = loglik(0.f, xt0, xt1);
+      ll_new = slice_loglik<float>(c, xt0, xt1);
       if (ll_new != ll_new) { st = 3; break; }
       bool above = ll_new > llh_s;
       if (A.guard > 0. && fabs(ll_new - llh_s) < A.guard) {
         // inside the guard band: level and value again in float64 (compat.slicesample's `above`)
-        if (!have64) { level64 = log_u + loglik(0., x[0], x[1]); have64 = true; }
-        above = loglik(0., xt0, xt1) > level64;
+        if (!have64) { level64 = log_u + slice_loglik<double>(c, x[0], x[1]); have64 = true; }
+        above = slice_loglik<double>(c, xt0, xt1) > level64;
         ++refined;
       }
       if (above) { x[0] = xt0; x[1] = xt1; break; }
@@ -588,7 +614,7 @@ __global__ void __launch_bounds__(32 * SLICE_MAX_IMG) slice_location_kernel(Slic
   if (threadIdx.x == 0) {
     A.status[s] = st;
     A.n_used[s] = idx;
-    A.n_evals[s] = evals;
+    A.n_evals[s] = c.evals;
     A.ll_out[s] = ll_new;
     if (A.n_refined) A.n_refined[s] = refined;
     if (st == 0) { A.srcs[s].u[0] = x[0]; A.srcs[s].u[1] = x[1]; }
@@ -998,6 +1024,8 @@ int cg_slice_sample_locations(CgImage* const* imgs, int32_t n_img, CgSource* d_s
   const size_t smem = (size_t)n_img * SLICE_WARP_BYTES;
   if (smem > 48 * 1024)
     CUDA_TRY(cudaFuncSetAttribute(slice_location_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  CUDA_TRY(cudaFuncSetAttribute(slice_location_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                cudaSharedmemCarveoutMaxShared));
   slice_location_kernel<<<n_src, 32 * n_img, smem, (cudaStream_t)stream>>>(A);
   LAUNCH_CHECK();
   return CG_OK;
