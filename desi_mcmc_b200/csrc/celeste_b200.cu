@@ -2454,6 +2454,51 @@ __global__ void __launch_bounds__(256) pk2_probe_kernel(float* out, int iters) {
   if (s == 123.456f) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// which = 20 / 21 / 22: does a packed FP32x2 instruction hold the issue port for the two cycles it holds
+// the FMA pipe?  Per group: 2 FFMA2 (20), 2 FFMA (21) or 4 FFMA (22: the arithmetic of 20 unpacked), each
+// with ONE independent integer LOP3 (ALU pipe).  FMA-pipe cycles per group 4 / 2 / 4, issue slots 3 / 3 / 5
+// if a packed instruction takes one slot, 5 / 3 / 5 if it takes two.  Result: groups per second per lane
+// (scheduler clock / (result / 32 lanes / schedulers) = cycles per group).
+template <int VAR>
+__global__ void __launch_bounds__(256) issue_probe_kernel(float* out, int iters) {
+  f32x2 v[16];
+  float w[32];
+  unsigned n[8];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) v[j] = pk2(0.5f + 0.001f * (float)(threadIdx.x + j), 0.25f + 0.001f * (float)(threadIdx.x + j));
+#pragma unroll
+  for (int j = 0; j < 32; ++j) w[j] = 0.5f + 0.001f * (float)(threadIdx.x + j);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) n[j] = threadIdx.x * 2654435761u + j;
+  const f32x2 a = pk2(0.999f, 0.998f), b = pk2(0.0007f, 0.0005f);
+  const float fa = 0.999f, fb = 0.0007f;
+  const unsigned m = out ? 0x9e3779b9u : 0u;
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      // volatile: exactly these instructions, in these proportions
+      if (VAR == 0) {
+        asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(v[j]) : "l"(a), "l"(b));
+        asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(v[j + 8]) : "l"(a), "l"(b));
+      } else {
+        asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(w[j]) : "f"(fa), "f"(fb));
+        asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(w[j + 8]) : "f"(fa), "f"(fb));
+        if (VAR == 2) {
+          asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(w[j + 16]) : "f"(fa), "f"(fb));
+          asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(w[j + 24]) : "f"(fa), "f"(fb));
+        }
+      }
+      asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(n[j]) : "r"(m), "r"(i));   // n ^= m ^ i: not foldable across trips
+    }
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < 16; ++j) { float lo, hi; unpk2(v[j], lo, hi); s += lo + hi + w[j] + w[j + 16]; }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s += (float)n[j];
+  if (s == 123.456f) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 // Instruction-mix probes: the inner loop of field_tile_kernel / render_kernel in
 // isolation (no global memory, every lane busy), to measure what fraction of
 // the MUFU peak this MIX can reach on the device.  VAR 2: the full loop (table
@@ -3456,7 +3501,7 @@ int cg_pipe_probe(int which, double* ops_per_s, void* stream) {
   // which: 0 MUFU.EX2, 1 FFMA, 7 FFMA2 (packed; counted as 2 FMA per lane); 2..5 instruction-mix probes and 6 the row-recurrence loop at
   // 3 CTAs/SM (24 warps, the tile kernel's residency), 12..16 the same at 8 CTAs/SM (64 warps)
   const int var = which % 10;
-  const bool raw = var < 2 || (which >= 7 && which <= 9);   // single-pipe probes: long chains, 8 CTAs/SM
+  const bool raw = var < 2 || (which >= 7 && which <= 9) || which >= 20;   // single-pipe probes: long chains, 8 CTAs/SM
   const int iters = raw ? 4096 : 128, blocks = g_sm_count * ((which >= 2 && which < 10 && !raw) ? 3 : 8), threads = 256;
   float* d_out = nullptr;
   CUDA_TRY(cudaMalloc(&d_out, sizeof(float) * blocks * threads));
@@ -3471,6 +3516,9 @@ int cg_pipe_probe(int which, double* ops_per_s, void* stream) {
     else if (which == 7) fma2_probe_kernel<<<blocks, threads, 0, st>>>(d_out, iters);
     else if (which == 8) pk2_probe_kernel<0><<<blocks, threads, 0, st>>>(d_out, iters);
     else if (which == 9) pk2_probe_kernel<1><<<blocks, threads, 0, st>>>(d_out, iters);
+    else if (which == 20) issue_probe_kernel<0><<<blocks, threads, 0, st>>>(d_out, iters);
+    else if (which == 21) issue_probe_kernel<1><<<blocks, threads, 0, st>>>(d_out, iters);
+    else if (which == 22) issue_probe_kernel<2><<<blocks, threads, 0, st>>>(d_out, iters);
     else if (var == 2) mix_probe_kernel<2><<<blocks, threads, 0, st>>>(d_out, iters);
     else if (var == 3) mix_probe_kernel<3><<<blocks, threads, 0, st>>>(d_out, iters);
     else if (var == 4) mix_probe_kernel<4><<<blocks, threads, 0, st>>>(d_out, iters);
