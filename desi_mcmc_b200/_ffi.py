@@ -133,6 +133,8 @@ PROTOTYPES = {
     "cg_prior_stats": (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _vp]),
     "cg_slice_sample_locations": (C.c_int, [_vp, _i32, _vp, _i32, _vp, _vp, _i64, _vp, _vp, _vp, _i32, _dbl, _dbl,
                                             _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cg_hmc_galaxy_params": (C.c_int, [_vp, _i32, _vp, _i32, _vp, _i32, _vp, _vp, _i64, _vp, _vp, _vp, _dbl, _vp, _i32,
+                                       _vp, _vp, _vp, _vp, _vp]),
     "cg_flux_prior_scratch_bytes": (_sz, [_i64, _i32]),
     "cg_flux_prior_stats": (C.c_int, [_vp, _i64, _i32, _vp, _vp, _vp, _vp, _i32, _vp, _sz, _vp, _vp, _vp]),
     "cg_sweep_stats": (C.c_int, [_vp, _i32, _vp, _vp, _i32, _vp, _i64, _vp, _vp, _i32, _vp, _vp]),

@@ -196,6 +196,72 @@ def hmc_sample_galaxy_params(src, src_imgs, imgs, p_curr=None, step_sz=1e-5, ste
     return p_samp
 
 
+def hmc_sample_galaxy_params_on_device(srcs, src_imgs_list, imgs, p_curr=None, step_sz=1e-5,
+                                       steps_per_sample=50, random_state=None):
+    """hmc_sample_galaxy_params (:281-323) for EVERY galaxy of `srcs` in ONE launch
+    (cg_hmc_galaxy_params): the 50 leapfrog steps and their 51 x 11 + 2 float64
+    likelihoods run on the device, one thread block per galaxy.  src_imgs_list[s][n] is galaxy s's photon
+    image on imgs[n], shaped like the Cython-route footprint at the current parameters
+    (galaxy_source_like's contract; checked).  Randomness comes from `random_state` (default numpy.random)
+    in the order of the per-galaxy host loop: [the initial momentum if p_curr is None,] the refresh
+    normals, the acceptance uniform, galaxy after galaxy.  Where the reference would re-derive the
+    footprint at every evaluation (and raise once its shape differs from Z_s) the device keeps the
+    footprint of the start point.  Updates the sources in place; returns (p_samp [n, 11], accepted [n])."""
+    import torch
+    rs = np.random if random_state is None else random_state
+    srcs = list(srcs)
+    S, n_img = len(srcs), len(imgs)
+    if S == 0:
+        return np.zeros((0, 11)), np.zeros(0, dtype=bool)
+    mass = engine.HMC_GALAXY_MASS
+    th = np.array([np.concatenate(([s.theta, s.sigma, s.phi, s.rho], np.asarray(s.u, dtype=np.float64), fluxes_of(s)))
+                   for s in srcs])
+    rec = gal._cond_items(th, imgs, S)
+    flags = _ffi.CG_ITEM_TRUNC_BOX | _ffi.CG_ITEM_HEADER_CD
+    src_idx, img_idx = np.repeat(np.arange(S), n_img), np.tile(np.arange(n_img), S)
+    zmax = max(int(np.size(z)) for zs in src_imgs_list for z in zs)
+    _, boxes = engine.render_patches(imgs, rec, engine.make_items(src_idx, img_idx, flags=flags | _ffi.CG_ITEM_FLUX_UNIT),
+                                     max_patch_px=max(zmax, 1))     # the footprints at the start points
+    stride = 1
+    for k in range(S * n_img):
+        b = boxes[k]
+        shp = (int(b["y1"] - b["y0"]), int(b["x1"] - b["x0"]))
+        z = np.asarray(src_imgs_list[k // n_img][k % n_img])
+        if z.shape != shp:
+            raise ValueError("operands could not be broadcast together: Z_s[%d] of galaxy %d has shape %s, its "
+                             "footprint is %s" % (k % n_img, k // n_img, z.shape, shp))
+        stride = max(stride, shp[0] * shp[1])
+    host = np.zeros((S * n_img, stride), dtype=np.float32)
+    for k in range(S * n_img):
+        z = np.asarray(src_imgs_list[k // n_img][k % n_img], dtype=np.float32).ravel()
+        host[k, :z.size] = z
+    photons = torch.from_numpy(host).to(engine.device())
+    dbox = np.zeros(S * n_img, dtype=_ffi.BOX_DTYPE)
+    for k in range(S * n_img):
+        dbox[k] = (int(boxes[k]["x0"]), int(boxes[k]["x1"]), int(boxes[k]["y0"]), int(boxes[k]["y1"]))
+    # the host generator, in the order of hmc.py:62,67,73 for one galaxy after the other
+    P_old, P_new, log_u = np.zeros((S, 11)), np.zeros((S, 11)), np.zeros(S)
+    refresh_alpha = .9
+    for s in range(S):
+        P_old[s] = np.sqrt(mass) * rs.randn(11) if p_curr is None else np.asarray(p_curr[s], dtype=np.float64)
+        P_new[s] = refresh_alpha * P_old[s] + np.sqrt(1.0 - refresh_alpha ** 2) * np.sqrt(mass) * rs.randn(11)
+        log_u[s] = np.log(rs.rand())
+    ke = np.array([np.sum((1. / mass) * P_old[s] * P_old[s]) for s in range(S)])
+    d_srcs = engine.to_device(rec)
+    p_out, h, acc, status = engine.hmc_galaxy_params(imgs, d_srcs, S, engine.to_device(dbox), photons, stride,
+                                                     P_new, ke, log_u, step=step_sz, n_steps=steps_per_sample)
+    if np.any(status != 0):
+        raise FloatingPointError("non-finite energy on the HMC trajectory of galaxies %s" % np.nonzero(status)[0].tolist())
+    new = d_srcs.cpu().numpy().view(_ffi.SRC_DTYPE)
+    for s, src in enumerate(srcs):
+        src.theta, src.sigma, src.phi, src.rho = (float(new["theta"][s]), float(new["sigma"][s]),
+                                                  float(new["phi"][s]), float(new["rho"][s]))
+        src.u = np.array(new["u"][s], dtype=np.float64)
+        src.fluxes = dict(zip(BANDS, [float(v) for v in new["flux"][s]]))
+    hmc_sample_galaxy_params_on_device.last = dict(h=h, kernel_ms=engine.hmc_galaxy_params.last_kernel_ms)
+    return p_out, acc.astype(bool)
+
+
 def sample_source_params(src, src_imgs, imgs, verbose=False):
     """:153-164."""
     if src.a == 0:

@@ -622,6 +622,195 @@ __global__ void __launch_bounds__(32 * SLICE_MAX_IMG, 2) slice_location_kernel(S
 }
 
 // ---------------------------------------------------------------------------
+// N2: one HMC update of every galaxy's (shape, location, fluxes) in ONE launch
+// ---------------------------------------------------------------------------
+// celeste_mcmc.py:281-323 (hmc_sample_galaxy_params) around util/infer/hmc.py:16-98 with num_iter = 1:
+// x = [theta, sigma, phi, rho, u0, u1, b_u .. b_z]; energy = -galaxy_source_like
+// (celeste_galaxy_conditionals.py:15-42), gradient = galaxy_source_like_grad (:44-88): theta and the
+// fluxes analytically, sigma / phi / rho / u by central differences of 1e-5 -- ten more likelihoods per
+// gradient, num_steps + 1 gradients per trajectory.  One thread block per galaxy, one warp per image.
+// Every likelihood is evaluated in float64 straight from the float64 component table (item_table<double>,
+// the table prepare_kernel builds) on the FIXED footprint of the photon patch: no culling, no recurrence,
+// exp2 / log in float64 -- the differences are divided by 2e-5.  The momentum after the refresh and the
+// logarithm of the acceptance uniform come from the host generator (hmc.py:62,67,73 draw order).
+#define HMC_DIM 11
+struct HmcArgs {
+  ImgPtrs imgs;
+  int n_img, n_src, n_steps;
+  int item_flags;              // CG_ITEM_HEADER_CD (the Cython route of galaxy_source_like) or 0 (cd_at_pixel, the live route)
+  const int* sel;              // optional [n_src] indices into srcs / boxes / patches (the galaxies of a mixed list)
+  CgSource* srcs;              // in: current state; out: the accepted state
+  const CgBox* boxes;          // [.. * n_img] footprints of the photon patches
+  const float* aux;            // photon patches, item-major, stride aux_stride
+  long long aux_stride;
+  const double* p_in;          // [n_src][HMC_DIM] momentum after the refresh (hmc.py:67)
+  const double* ke_curr;       // [n_src] sum(P P / mass) of the momentum BEFORE the refresh (hmc.py:64 takes ll_curr there)
+  const double* log_u;         // [n_src] log of the acceptance uniform (hmc.py:73)
+  double eps;
+  double mass[HMC_DIM];
+  double* p_out;               // [n_src][HMC_DIM] momentum carried to the next call (hmc.py:79)
+  double* h_out;               // [n_src][2] -H at the start and at the proposal
+  int* accepted;               // [n_src]
+  int* status;                 // [n_src] 0 ok, 3 NaN / non-finite energy (state left unchanged)
+  const FilterTables* filters;
+  const double* flux_table;
+  long long flux_rows;
+};
+
+struct HmcCtx {
+  const DevImage* im;
+  CgSource src;
+  CgBox box;                   // clipped to the image
+  const float* z;              // this (source, image)'s photon patch
+  double* tab;                 // this warp's float64 table
+  double* s_part;              // [SLICE_MAX_IMG][4] per-image sums of the current evaluation
+  const FilterTables* filters;
+  const double* flux_table;
+  long long flux_rows;
+  int lane, b, n_img, item_flags;
+};
+
+// galaxy_source_like(th) (and, with parts, the sums the analytic part of the gradient needs) over the
+// images of the block; every thread returns the same values.  out[0] = ll; parts: out[1] = d ll / d theta,
+// the per-image flux terms stay in s_part[img * 4 + 2] for hmc_grad.
+__device__ __noinline__ void hmc_eval(HmcCtx& c, const double* th, bool parts, double* out) {
+  const DevImage& im = *c.im;
+  c.src.theta = th[0]; c.src.sigma = th[1]; c.src.phi = th[2]; c.src.rho = th[3];
+  c.src.u[0] = th[4]; c.src.u[1] = th[5];
+#pragma unroll
+  for (int k = 0; k < CG_NUM_BANDS; ++k) c.src.flux[k] = th[6 + k];
+  __syncthreads();                     // everybody is done with the previous tables and sums
+  const int flags = CG_ITEM_TRUNC_BOX | c.item_flags;
+  ItemGeom g = item_table<double>(im, c.src, flags, c.lane, c.tab);
+  const double flux = item_flux(im, c.src, flags, c.lane, false, c.filters, c.flux_table, c.flux_rows, g);
+  const double b_raw = th[6 + im.band];       // the gradient's "bs[img.band]" (:63,66) is the raw flux
+  __syncwarp();
+  const int K = g.K, Kexp = 6 * im.n_psf;
+  const int wbox = c.box.x1 - c.box.x0, npx = wbox * (c.box.y1 - c.box.y0);
+  double ll = 0., sf = 0., gt = 0., sz = 0.;
+  const double ith = 1. / th[0], ith1 = 1. / (1. - th[0]);
+  for (int p = c.lane; p < npx; p += 32) {
+    const int yy = p / wbox, xx = p - yy * wbox;
+    const double xl = (double)(c.box.x0 + xx - g.ox), yl = (double)(c.box.y0 + yy - g.oy);
+    double fe = 0., fd = 0.;
+    for (int k = 0; k < K; ++k) {
+      const double* t = c.tab + k * TAB_W;
+      const double e = exp2(fma(fma(t[0], xl, fma(t[1], yl, t[3])), xl, fma(fma(t[2], yl, t[4]), yl, t[5])));
+      if (k < Kexp) fe += e; else fd += e;
+    }
+    const double f = fe + fd, v = flux * f, z = (double)c.z[p];
+    if (v >= 1.17549435e-38) ll += log(v) * z;
+    ll -= v;
+    if (parts) {
+      sf += f; sz += z;
+      gt += (z / f - b_raw) * (fe * ith - fd * ith1);         // (Z / f_nms - b) (f_exp - f_dev), :63
+    }
+  }
+  ll = warp_sum(ll);
+  if (parts) { sf = warp_sum(sf); gt = warp_sum(gt); sz = warp_sum(sz); }
+  if (c.lane == 0) {
+    double* sp = c.s_part + c.b * 4;
+    sp[0] = ll; sp[1] = gt; sp[2] = sz / b_raw - sf; sp[3] = 0.;
+  }
+  __syncthreads();
+  double tot = 0., tg = 0.;
+  for (int k = 0; k < c.n_img; ++k) { tot += c.s_part[k * 4]; tg += c.s_part[k * 4 + 1]; }
+  out[0] = tot;
+  if (parts) out[1] = tg;
+}
+
+// galaxy_source_like_grad (:44-88) -> grad[HMC_DIM]; returns false on a non-finite value
+__device__ __noinline__ bool hmc_grad(HmcCtx& c, const ImgPtrs& imgs, const double* th, double* grad) {
+  double out[2];
+  hmc_eval(c, th, true, out);
+  grad[0] = out[1];
+#pragma unroll
+  for (int k = 0; k < CG_NUM_BANDS; ++k) grad[6 + k] = 0.;
+  for (int k = 0; k < c.n_img; ++k) grad[6 + imgs.p[k]->band] += c.s_part[k * 4 + 2];      // :66
+  bool ok = isfinite(out[0]);
+  double t2[HMC_DIM];
+  for (int i = 1; i <= 5; ++i) {                                                          // :69-78
+#pragma unroll
+    for (int k = 0; k < HMC_DIM; ++k) t2[k] = th[k];
+    double lp, lm;
+    t2[i] = th[i] + 1e-5;
+    hmc_eval(c, t2, false, &lp);
+    t2[i] = th[i] - 1e-5;
+    hmc_eval(c, t2, false, &lm);
+    grad[i] = (lp - lm) / (2. * 1e-5);
+    ok = ok && isfinite(lp) && isfinite(lm);
+  }
+  return ok;
+}
+
+#define HMC_WARP_BYTES (CG_MAX_COMP * TAB_W * 8)
+__global__ void __launch_bounds__(32 * SLICE_MAX_IMG) hmc_galaxy_kernel(HmcArgs A) {
+  extern __shared__ __align__(16) unsigned char s_dyn[];           // n_img x HMC_WARP_BYTES
+  __shared__ double s_part[SLICE_MAX_IMG * 4];
+  const int j = blockIdx.x;          // j: row of the per-call arrays; s: the source it updates
+  if (j >= A.n_src) return;
+  const int s = A.sel ? A.sel[j] : j;
+  HmcCtx c;
+  c.lane = threadIdx.x & 31; c.b = threadIdx.x >> 5; c.n_img = A.n_img; c.item_flags = A.item_flags;
+  c.im = A.imgs.p[c.b];
+  c.src = A.srcs[s];
+  c.tab = reinterpret_cast<double*>(s_dyn + (size_t)c.b * HMC_WARP_BYTES);
+  c.s_part = s_part;
+  c.filters = A.filters; c.flux_table = A.flux_table; c.flux_rows = A.flux_rows;
+  const CgBox b0 = A.boxes[(long long)s * A.n_img + c.b];
+  c.box.x0 = max(b0.x0, 0); c.box.y0 = max(b0.y0, 0); c.box.x1 = min(b0.x1, c.im->W); c.box.y1 = min(b0.y1, c.im->H);
+  if (c.box.x1 <= c.box.x0 || c.box.y1 <= c.box.y0) { c.box.x1 = c.box.x0; c.box.y1 = c.box.y0; }
+  c.z = A.aux + ((long long)s * A.n_img + c.b) * A.aux_stride;
+
+  double X[HMC_DIM], P[HMC_DIM], im_[HMC_DIM], grad[HMC_DIM];
+  X[0] = c.src.theta; X[1] = c.src.sigma; X[2] = c.src.phi; X[3] = c.src.rho; X[4] = c.src.u[0]; X[5] = c.src.u[1];
+#pragma unroll
+  for (int k = 0; k < CG_NUM_BANDS; ++k) X[6 + k] = c.src.flux[k];
+#pragma unroll
+  for (int k = 0; k < HMC_DIM; ++k) { P[k] = A.p_in[(long long)j * HMC_DIM + k]; im_[k] = 1. / A.mass[k]; }
+  const double eps = A.eps;
+  bool ok = true;
+  // ll_curr = -hamiltonian(X, P) is taken BEFORE the momentum refresh (hmc.py:64): the host passes that
+  // kinetic term
+  double ll0;
+  hmc_eval(c, X, false, &ll0);
+  const double h_curr = ll0 - .5 * A.ke_curr[j];
+  // leapstep (hmc.py:52-59); grad_energy = -grad
+  double xx[HMC_DIM], pp[HMC_DIM];
+#pragma unroll
+  for (int k = 0; k < HMC_DIM; ++k) { xx[k] = X[k]; pp[k] = P[k]; }
+  ok = hmc_grad(c, A.imgs, xx, grad) && ok;
+#pragma unroll
+  for (int k = 0; k < HMC_DIM; ++k) pp[k] = pp[k] - .5 * eps * (-grad[k]);
+  for (int l = 0; l < A.n_steps && ok; ++l) {
+#pragma unroll
+    for (int k = 0; k < HMC_DIM; ++k) xx[k] = xx[k] + eps * im_[k] * pp[k];
+    const double em = (l == A.n_steps - 1) ? .5 * eps : eps;
+    ok = hmc_grad(c, A.imgs, xx, grad) && ok;
+#pragma unroll
+    for (int k = 0; k < HMC_DIM; ++k) pp[k] = pp[k] - em * (-grad[k]);
+  }
+  double ll1 = 0., ke1 = 0.;
+  if (ok) hmc_eval(c, xx, false, &ll1);
+#pragma unroll
+  for (int k = 0; k < HMC_DIM; ++k) { pp[k] = -pp[k]; ke1 += im_[k] * pp[k] * pp[k]; }
+  const double h_prop = ll1 - .5 * ke1;
+  ok = ok && isfinite(h_prop) && isfinite(h_curr);
+  const bool acc = ok && (A.log_u[j] < h_prop - h_curr);              // hmc.py:73
+  if (threadIdx.x == 0) {
+    A.status[j] = ok ? 0 : 3;
+    A.accepted[j] = acc ? 1 : 0;
+    A.h_out[2 * j] = h_curr; A.h_out[2 * j + 1] = h_prop;
+    for (int k = 0; k < HMC_DIM; ++k) A.p_out[(long long)j * HMC_DIM + k] = -(acc ? pp[k] : P[k]);   // :74-79
+    if (acc) {
+      CgSource& o = A.srcs[s];
+      o.theta = xx[0]; o.sigma = xx[1]; o.phi = xx[2]; o.rho = xx[3]; o.u[0] = xx[4]; o.u[1] = xx[5];
+      for (int k = 0; k < CG_NUM_BANDS; ++k) o.flux[k] = xx[6 + k];
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
 // per-sweep statistics a rank contributes to the all-reduce
 // ---------------------------------------------------------------------------
 // colour-space coordinates of the sources of one type (FluxColorMoG, util/dists/flux_prior.py:4-40:
@@ -1027,6 +1216,40 @@ int cg_slice_sample_locations(CgImage* const* imgs, int32_t n_img, CgSource* d_s
   CUDA_TRY(cudaFuncSetAttribute(slice_location_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                                 cudaSharedmemCarveoutMaxShared));
   slice_location_kernel<<<n_src, 32 * n_img, smem, (cudaStream_t)stream>>>(A);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
+int cg_hmc_galaxy_params(CgImage* const* imgs, int32_t n_img, CgSource* d_srcs, int32_t n_src,
+                         const int32_t* d_sel, int32_t item_flags,
+                         const CgBox* d_boxes, const float* d_photons, int64_t max_patch_px,
+                         const double* d_p_in, const double* d_ke_curr, const double* d_log_u, double step,
+                         const double* mass, int32_t n_steps, double* d_p_out, double* d_h_out,
+                         int32_t* d_accepted, int32_t* d_status, void* stream) {
+  NEED_INIT();
+  HmcArgs A;
+  memset(&A, 0, sizeof A);
+  int rc = fill_imgs(imgs, n_img, &A.imgs);
+  if (rc) return rc;
+  if (n_img > SLICE_MAX_IMG) return fail(CG_EINVAL, "at most %d images per source in the on-device sampler", SLICE_MAX_IMG);
+  if (n_src <= 0) return CG_OK;
+  if (!d_srcs || !d_boxes || !d_photons || !d_p_in || !d_ke_curr || !d_log_u || !mass || !d_p_out || !d_h_out ||
+      !d_accepted || !d_status)
+    return fail(CG_EINVAL, "null argument");
+  if (n_steps < 1 || !(step > 0.)) return fail(CG_EINVAL, "n_steps >= 1 and step > 0");
+  for (int k = 0; k < HMC_DIM; ++k) {
+    if (!(mass[k] > 0.)) return fail(CG_EINVAL, "mass[%d] must be positive", k);
+    A.mass[k] = mass[k];
+  }
+  A.item_flags = item_flags & CG_ITEM_HEADER_CD; A.sel = d_sel;
+  A.n_img = n_img; A.n_src = n_src; A.n_steps = n_steps; A.srcs = d_srcs; A.boxes = d_boxes; A.aux = d_photons;
+  A.aux_stride = max_patch_px; A.p_in = d_p_in; A.ke_curr = d_ke_curr; A.log_u = d_log_u; A.eps = step;
+  A.p_out = d_p_out; A.h_out = d_h_out; A.accepted = d_accepted; A.status = d_status;
+  A.filters = g_d_filters; A.flux_table = g_flux_table; A.flux_rows = g_flux_rows;
+  const size_t smem = (size_t)n_img * HMC_WARP_BYTES;
+  if (smem > 48 * 1024)
+    CUDA_TRY(cudaFuncSetAttribute(hmc_galaxy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  hmc_galaxy_kernel<<<n_src, 32 * n_img, smem, (cudaStream_t)stream>>>(A);
   LAUNCH_CHECK();
   return CG_OK;
 }

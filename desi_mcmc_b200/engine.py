@@ -1235,6 +1235,26 @@ class GibbsSweep(object):
                                (int((status != 0).sum()), sorted(set(status[status != 0].tolist()))))
         return status, evals
 
+    def hmc_galaxies(self, seed: int, step: float = 1e-5, n_steps: int = 50, momentum: np.ndarray = None):
+        """hmc_sample_galaxy_params (celeste_mcmc.py:281-323) for every galaxy given the allocated photons, the
+        whole trajectory on the device in ONE launch (cg_hmc_galaxy_params) on the sweep's boxes.  Normals
+        and the acceptance uniform come from one host RandomState(seed).  momentum: [n_gal, 11] carried
+        from the previous call (None: drawn).  Returns (momentum, accepted)."""
+        rng = np.random.RandomState(int(seed) & 0x7fffffff)
+        types = self.sources()["type"]
+        gal = np.nonzero(types == 1)[0].astype(np.int32)
+        G = gal.size
+        sm = np.sqrt(HMC_GALAXY_MASS)
+        p_old = sm * rng.randn(G, 11) if momentum is None else np.asarray(momentum, dtype=np.float64)
+        p_new = .9 * p_old + np.sqrt(1. - .9 ** 2) * sm * rng.randn(G, 11)
+        log_u = np.log(rng.rand(G))
+        ke = np.sum(p_old * p_old / HMC_GALAXY_MASS, axis=1)
+        p_out, h, acc, status = hmc_galaxy_params(self.images, self.d_cur, G, self.d_boxes, self.samp, self.max_patch_px,
+                                                  p_new, ke, log_u, step=step, n_steps=n_steps, sel=gal, header_cd=False)
+        self.hmc_stats = dict(h=h, accepted=acc, status=status, kernel_ms=hmc_galaxy_params.last_kernel_ms,
+                              likelihoods=G * (11 * (n_steps + 1) + 2))
+        return p_out, acc
+
     def loglik(self):
         check(self.L.cg_field_loglik(self.harr, self.n_img, self.d_cur.data_ptr(), self.n_src, self.bound_cap,
                                      self.max_patch_px, self.ll.data_ptr(), None, self.ws_field.data_ptr(),
@@ -1340,6 +1360,49 @@ class SweepPayload(object):
                                     self.d_srcs.data_ptr(), self.n_src, self.blocks[0].data_ptr(),
                                     self.blocks[1].data_ptr(), self.block, self.vec[k].data_ptr(), stream_ptr()))
         return self.vec[k]
+
+
+HMC_GALAXY_MASS = np.array([.1, .1, 1., .1, .001, .001, 1., 1., 1., 1., 1.])    # celeste_mcmc.py:300-303
+
+
+def hmc_galaxy_params(images: Sequence[Image], d_srcs: torch.Tensor, n_src: int, d_boxes: torch.Tensor,
+                      photons: torch.Tensor, max_patch_px: int, p_in: np.ndarray, ke_curr: np.ndarray,
+                      log_u: np.ndarray, step: float = 1e-5, n_steps: int = 50, mass: np.ndarray = None,
+                      sel: np.ndarray = None, header_cd: bool = True):
+    """N2: cg_hmc_galaxy_params -- one HMC update (celeste_mcmc.py:281-323, util/infer/hmc.py with
+    num_iter = 1) of every galaxy in ONE launch.  d_srcs: device CgSource bytes (updated in place where the
+    proposal is accepted); d_boxes: device CgBox bytes [.. * n_img]; photons [.. * n_img, max_patch_px]
+    float32 device patches shaped like the boxes; p_in [n_src, 11] the momentum after the host's refresh,
+    ke_curr [n_src] sum(P P / mass) of the momentum before it, log_u [n_src].
+    sel: optional indices of the n_src galaxies inside d_srcs / d_boxes / photons (a mixed source list);
+    header_cd: the Cython route's header CD matrix (galaxy_source_like) or, False, cd_at_pixel (live route).
+    Returns host arrays (p_out [n_src, 11], h [n_src, 2] = -H before / proposed, accepted, status)."""
+    harr, n_img = _handles(images)
+    dev = device()
+    d_sel = None if sel is None else torch.from_numpy(np.ascontiguousarray(sel, dtype=np.int32)).to(dev)
+    mass = np.ascontiguousarray(HMC_GALAXY_MASS if mass is None else mass, dtype=np.float64)
+    p_in = np.ascontiguousarray(p_in, dtype=np.float64)
+    if p_in.shape != (n_src, 11) or mass.shape != (11,) or np.shape(ke_curr) != (n_src,) or np.shape(log_u) != (n_src,):
+        raise ValueError("p_in [n_src, 11], ke_curr [n_src], log_u [n_src], mass [11]")
+    d_p = torch.from_numpy(p_in).to(dev)
+    d_ke = torch.from_numpy(np.ascontiguousarray(ke_curr, dtype=np.float64)).to(dev)
+    d_lu = torch.from_numpy(np.ascontiguousarray(log_u, dtype=np.float64)).to(dev)
+    p_out = torch.zeros((n_src, 11), dtype=torch.float64, device=dev)
+    h = torch.zeros((n_src, 2), dtype=torch.float64, device=dev)
+    acc = torch.zeros(n_src, dtype=torch.int32, device=dev)
+    status = torch.zeros(n_src, dtype=torch.int32, device=dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    check(lib().cg_hmc_galaxy_params(harr, n_img, d_srcs.data_ptr(), int(n_src),
+                                     d_sel.data_ptr() if d_sel is not None else None,
+                                     _ffi.CG_ITEM_HEADER_CD if header_cd else 0, d_boxes.data_ptr(),
+                                     photons.data_ptr(), int(max_patch_px), d_p.data_ptr(), d_ke.data_ptr(),
+                                     d_lu.data_ptr(), float(step), mass.ctypes.data, int(n_steps),
+                                     p_out.data_ptr(), h.data_ptr(), acc.data_ptr(), status.data_ptr(), stream_ptr()))
+    e1.record()
+    out = p_out.cpu().numpy(), h.cpu().numpy(), acc.cpu().numpy(), status.cpu().numpy()
+    hmc_galaxy_params.last_kernel_ms = e0.elapsed_time(e1)
+    return out
 
 
 def slice_sample_locations(images: Sequence[Image], d_srcs: torch.Tensor, n_src: int, d_boxes: torch.Tensor,

@@ -419,6 +419,30 @@ int cg_slice_sample_locations(CgImage* const* imgs, int32_t n_img, CgSource* d_s
                               int32_t n_uniforms, double sigma, double guard, double* d_ll, int32_t* d_n_used,
                               int32_t* d_status, int32_t* d_n_evals, int32_t* d_n_refined, void* stream);
 
+/* One HMC update of (theta, sigma, phi, rho, u, fluxes) of EVERY galaxy in one launch
+ * (celeste_mcmc.py:281-323 hmc_sample_galaxy_params around util/infer/hmc.py:16-98, num_iter = 1): one
+ * thread block per galaxy runs the n_steps leapfrog steps and all 11 (n_steps + 1) + 2 float64
+ * likelihoods of the trajectory (galaxy_source_like / galaxy_source_like_grad,
+ * celeste_galaxy_conditionals.py:15-88: theta and the fluxes analytically, sigma / phi / rho / u by
+ * central differences of 1e-5) on the FIXED footprints d_boxes of the photon patches
+ * d_photons[(s * n_img + img) * max_patch_px] (the reference re-derives the footprint per evaluation and
+ * fails when its shape leaves that of Z_s).  Host-supplied randomness in the reference's draw order:
+ * d_p_in [n_src][11] the momentum after the refresh (hmc.py:67), d_ke_curr [n_src] = sum(P P / mass) of
+ * the momentum before it (hmc.py:64), d_log_u [n_src] the log of the acceptance uniform (hmc.py:73).
+ * mass: 11 host doubles.  Outputs: the accepted state written into d_srcs, d_p_out [n_src][11] the
+ * momentum to carry (hmc.py:79), d_h_out [n_src][2] = -H at the start / at the proposal, d_accepted,
+ * d_status (0 ok, 3 non-finite: state unchanged, rejected).
+ * d_sel (optional): n_src indices into d_srcs / d_boxes / d_photons -- the galaxies of a mixed source list;
+ * the per-call arrays (d_p_in ... d_status) have one row per selected galaxy.  item_flags:
+ * CG_ITEM_HEADER_CD for galaxy_source_like's Cython route (header CD matrix), 0 for the live route
+ * (FitsImage.cd_at_pixel), which is what the field path and the Gibbs sweep render with. */
+int cg_hmc_galaxy_params(CgImage* const* imgs, int32_t n_img, CgSource* d_srcs, int32_t n_src,
+                         const int32_t* d_sel, int32_t item_flags,
+                         const CgBox* d_boxes, const float* d_photons, int64_t max_patch_px,
+                         const double* d_p_in, const double* d_ke_curr, const double* d_log_u, double step,
+                         const double* mass, int32_t n_steps, double* d_p_out, double* d_h_out,
+                         int32_t* d_accepted, int32_t* d_status, void* stream);
+
 /* ---- per-sweep statistics for the all-reduce ------------------ */
 /* Sufficient statistics of the empirical colour prior over the sources of one type, straight from
  * the device source array: colours = FluxColorMoG.to_colors(log fluxes) (util/dists/flux_prior.py:4-40),

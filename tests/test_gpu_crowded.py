@@ -328,6 +328,55 @@ def test_batched_proposals_for_every_source_match_the_oracle(engine, oracle):
     assert worst < LL_RTOL, worst
 
 
+def test_hmc_of_every_galaxy_in_one_launch(engine, oracle):
+    """GibbsSweep.hmc_galaxies (cg_hmc_galaxy_params on the sweep's boxes and allocated photons, live
+    cd_at_pixel route): the start energy of every galaxy equals the oracle's conditional likelihood of its
+    photons (celeste_galaxy_conditionals.py:41 on the capped footprints) minus the kinetic term; stars and
+    rejected galaxies keep their state bit for bit, accepted ones move; seeded -> reproducible."""
+    from desi_mcmc_b200.engine import HMC_GALAXY_MASS
+    field, gimgs, oimgs, osrcs, packed, sw = _setup(engine, oracle, n_src=40, proposals=0, background_pass=False)
+    sw.eigen.project()
+    sw.allocate(seed=3)
+    before = sw.sources()
+    boxes, samp = sw.boxes(), sw.samp.cpu().numpy()
+    n_img = len(gimgs)
+    engine.launch_count(reset=True)
+    p, acc = sw.hmc_galaxies(seed=9, step=2e-9, n_steps=3)
+    assert engine.launch_count() == 1
+    after = sw.sources()
+    gal = np.nonzero(before["type"] == 1)[0]
+    st = sw.hmc_stats
+    assert gal.size > 20 and p.shape == (gal.size, 11) and np.all(st["status"] == 0) and np.all(np.isfinite(st["h"]))
+    # the generator of hmc_galaxies, replayed: kinetic term of the momentum before the refresh
+    rng = np.random.RandomState(9)
+    ke = np.sum((np.sqrt(HMC_GALAXY_MASS) * rng.randn(gal.size, 11)) ** 2 / HMC_GALAXY_MASS, axis=1)
+    for j in range(0, gal.size, 5):
+        s = int(gal[j])
+        ll = 0.
+        for b, oi in enumerate(oimgs):
+            bx = boxes[s, b]
+            pch, yl, xl = _capped_patch(oracle, osrcs[s], oi, 25.)
+            if pch is None:
+                continue
+            assert (xl[0], xl[1], yl[0], yl[1]) == (bx["x0"], bx["x1"], bx["y0"], bx["y1"])
+            z = samp[s * n_img + b, :pch.size].reshape(pch.shape).astype(np.float64)
+            ll += np.sum(z * np.log(pch) - pch)
+        want = ll - .5 * ke[j]
+        assert abs(st["h"][j, 0] - want) <= 1e-9 * max(abs(want), 1.), (s, st["h"][j, 0], want)
+    stars = np.nonzero(before["type"] != 1)[0]
+    assert before[stars].tobytes() == after[stars].tobytes()
+    for j, s in enumerate(gal):
+        same = before[s:s + 1].tobytes() == after[s:s + 1].tobytes()
+        assert same == (not acc[j])
+    assert acc.sum() > 0
+    # same seed, same state -> same trajectory
+    sw2 = _setup(engine, oracle, n_src=40, proposals=0, background_pass=False)[5]
+    sw2.eigen.project()
+    sw2.allocate(seed=3)
+    p2, acc2 = sw2.hmc_galaxies(seed=9, step=2e-9, n_steps=3)
+    assert np.array_equal(p, p2) and np.array_equal(acc, acc2) and sw2.sources().tobytes() == after.tobytes()
+
+
 def test_full_sweeps_are_reproducible_and_consistent(engine, oracle):
     """Three whole sweeps with no host hop in between: seeded -> bitwise reproducible; the
     log-likelihood a sweep reports is the field likelihood of the state it ends in; photons are

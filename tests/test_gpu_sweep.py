@@ -161,6 +161,45 @@ def test_hmc_galaxy_step_runs_on_device_gradients(engine, oracle):
     assert np.all(np.isfinite(th1)) and np.isfinite(gal.galaxy_source_like(th1, Z, gimgs)) and np.isfinite(ll0)
 
 
+def test_on_device_hmc_equals_oracle_driven_hmc(engine, oracle):
+    """N2: cg_hmc_galaxy_params (the whole trajectory of hmc_sample_galaxy_params, celeste_mcmc.py:281-323, in
+    one launch) against util/infer/hmc.py's control flow driven by the ORACLE's float64 galaxy_source_like /
+    galaxy_source_like_grad (celeste_galaxy_conditionals.py:15-88) from the same numpy.random stream: same
+    energies, same decision, same end state and momentum."""
+    from desi_mcmc_b200.compat import celeste_mcmc as cm
+    from desi_mcmc_b200.compat.hmc import hmc
+    m, field, nelec, gimgs = _model(engine, oracle, size=31)
+    oimgs = hp.oracle_images(oracle, field, nelec)
+    g = [s for s in m.srcs if s.is_galaxy()][0].params
+    th0 = np.concatenate(([g.theta, g.sigma, g.phi, g.rho], g.u, np.asarray(g.fluxes, dtype=float)))
+    Z, rng = [], np.random.RandomState(2)
+    for oi in oimgs:
+        R = oracle.gen_galaxy_transformation(g.sigma, g.rho, g.phi, oi.Ups_n)
+        f, _, _ = oracle.gen_galaxy_prof_psf_image('exp', R, g.u, oi)
+        Z.append(rng.poisson(50. * f / f.max()).astype(np.float64))
+    mass, step, n_steps = engine.HMC_GALAXY_MASS, 2e-9, 4
+    # the oracle-driven chain: initial momentum, refresh normals and the acceptance uniform from numpy.random
+    np.random.seed(11)
+    p0 = np.sqrt(mass) * np.random.randn(11)
+    x_o, p_o, _, _ = hmc(x_curr=th0.copy(), llhfunc=lambda t: oracle.galaxy_source_like(t, Z, oimgs),
+                         grad_llhfunc=lambda t: oracle.galaxy_source_like_grad(t, Z, oimgs), eps=step,
+                         num_steps=n_steps, mass=mass, p_curr=p0, refresh_alpha=.9)
+    np.random.seed(11)
+    p_d, acc = cm.hmc_sample_galaxy_params_on_device([g], [Z], gimgs, step_sz=step, steps_per_sample=n_steps)
+    x_d = np.concatenate(([g.theta, g.sigma, g.phi, g.rho], g.u, [g.fluxes[b] for b in "ugriz"]))
+    h = cm.hmc_sample_galaxy_params_on_device.last["h"][0]
+    want_h0 = oracle.galaxy_source_like(th0, Z, oimgs) - .5 * np.sum(p0 * p0 / mass)
+    assert abs(h[0] - want_h0) <= 1e-9 * abs(want_h0)
+    assert bool(acc[0]) == (not np.array_equal(x_o, th0))
+    moved_o, moved_d = x_o - th0, x_d - th0
+    scale = np.maximum(np.abs(moved_o), 1e-6 * np.max(np.abs(moved_o)))
+    assert np.any(moved_o != 0.) and np.all(np.abs(moved_d - moved_o) / scale < 1e-4), (moved_d, moved_o)
+    pscale = np.maximum(np.abs(p_o), 1e-6 * np.max(np.abs(p_o)))
+    assert np.all(np.abs(p_d[0] - p_o) / pscale < 1e-4), (p_d[0], p_o)
+    print("device HMC: %.2f ms for %d leapfrog steps, accepted %s" %
+          (cm.hmc_sample_galaxy_params_on_device.last["kernel_ms"], n_steps, bool(acc[0])))
+
+
 def test_batched_resample_equals_per_source_resample(engine, oracle):
     """All sources advanced in lock-step (one launch per slice round) end in the
     state the reference's per-source loop reaches with the same per-source RNG."""
