@@ -112,6 +112,7 @@ PROTOTYPES = {
     "cg_score_proposals": (C.c_int, [_vp, _i32, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _dbl,
                                      _vp, _vp, _vp, _vp, _sz, _vp]),
     "cg_poisson_loglike": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _vp]),
+    "cg_poisson_loglike_static": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _vp]),
     "cg_alloc_workspace_bytes": (_sz, [_i32, _i64]),
     "cg_sample_source_counts": (C.c_int, [_vp, _i32, _i32, _vp, _vp, _i64, C.c_uint64, _vp, _vp, _vp, _sz, _vp]),
     "cg_binomial_draws": (C.c_int, [_i64, _dbl, C.c_uint64, _i64, _vp, _vp]),

@@ -2690,6 +2690,23 @@ static int stream_scratch(int kind, cudaStream_t st, size_t n_doubles, double** 
   return CG_OK;
 }
 
+// ---- scratch of cg_poisson_loglike_static: no allocation at call time -------------------------
+// The block partials of the Poisson reduction live in a file-scope device array (8 KB that every GPU
+// which loads this library holds until the process exits).  In HOST code the name g_static_partials is
+// a host-side stand-in, not a device address: its device address is taken once per device at set-up
+// (cg_init, with that device current) by cudaGetSymbolAddress and only that pointer is handed to kernels.
+static __device__ __align__(256) double g_static_partials[CG_POISSON_STATIC_MAX_BLOCKS];
+#define STATIC_MAX_DEVICES 64
+static double* g_static_partials_ptr[STATIC_MAX_DEVICES] = {nullptr};
+static int static_scratch_setup(int device) {
+  if (device < 0 || device >= STATIC_MAX_DEVICES) return CG_OK;   // cg_poisson_loglike_static reports it
+  if (g_static_partials_ptr[device]) return CG_OK;
+  double* p = nullptr;
+  CUDA_TRY(cudaGetSymbolAddress((void**)&p, g_static_partials));
+  g_static_partials_ptr[device] = p;
+  return CG_OK;
+}
+
 extern "C" {
 
 int cg_abi_version(void) { return CG_ABI_VERSION; }
@@ -2733,6 +2750,7 @@ int cg_init(int device) {
     CUDA_TRY(cudaMalloc(&g_d_filters, sizeof(FilterTables)));
     CUDA_TRY(cudaMemset(g_d_filters, 0, sizeof(FilterTables)));
   }
+  { int rc = static_scratch_setup(device); if (rc) return rc; }   // device address of g_static_partials
   g_device = device;
   return CG_OK;
 }
@@ -3355,6 +3373,29 @@ int cg_poisson_loglike(const double* d_data, const double* d_model, const double
   poisson_partial_kernel<<<blocks, 256, 0, st>>>(d_data, d_model, d_mask, n, g_scratch);
   LAUNCH_CHECK();
   sum_partials_kernel<<<1, 256, 0, st>>>(g_scratch, blocks, d_out);
+  LAUNCH_CHECK();
+  return CG_OK;
+}
+
+// the same reduction with its scratch in g_static_partials: no cudaMalloc / cudaFree, no allocating
+// library call, no lock, no map look-up -- callable under CUDA graph capture
+int cg_poisson_loglike_static(const double* d_data, const double* d_model, const double* d_mask, int64_t n,
+                              double* d_out, void* stream) {
+  NEED_INIT();
+  if (n < 0) return fail(CG_EINVAL, "negative size");
+  if (n > (int64_t)CG_POISSON_STATIC_MAX_N)
+    return fail(CG_EINVAL, "cg_poisson_loglike_static: n = %lld exceeds the static scratch's limit of %lld elements "
+                "(CG_POISSON_STATIC_MAX_N); use cg_poisson_loglike", (long long)n, (long long)CG_POISSON_STATIC_MAX_N);
+  if (!d_data || !d_model || !d_out) return fail(CG_EINVAL, "null argument");
+  double* scratch = (g_device >= 0 && g_device < STATIC_MAX_DEVICES) ? g_static_partials_ptr[g_device] : nullptr;
+  if (!scratch) return fail(CG_ECUDA, "the static scratch of device %d was not resolved at cg_init", g_device);
+  cudaStream_t st = (cudaStream_t)stream;
+  // the launch shape of cg_poisson_loglike: the two entry points return the same bits
+  int blocks = (int)std::min<long long>(CG_POISSON_STATIC_MAX_BLOCKS, std::max<long long>(1, (n + 255) / 256));
+  // nothing has to start at zero: every one of the `blocks` slots read below is written by its block first
+  poisson_partial_kernel<<<blocks, 256, 0, st>>>(d_data, d_model, d_mask, n, scratch);
+  LAUNCH_CHECK();
+  sum_partials_kernel<<<1, 256, 0, st>>>(scratch, blocks, d_out);
   LAUNCH_CHECK();
   return CG_OK;
 }

@@ -270,6 +270,23 @@ int cg_score_proposals(CgImage* const* imgs, int32_t n_img,
 int cg_poisson_loglike(const double* d_data, const double* d_model, const double* d_mask,
                        int64_t n, double* d_out, void* stream);
 
+/* cg_poisson_loglike without any allocation at call time.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  Same arguments, same result bits as
+ * cg_poisson_loglike (same kernels, same launch shape); the block partials live in a file-scope
+ * __device__ array of CG_POISSON_STATIC_MAX_BLOCKS doubles (8 KB per GPU that loads the library, held
+ * until exit) whose device address cg_init resolves once per device (cudaGetSymbolAddress).  The entry
+ * point calls no cudaMalloc / cudaFree / allocating routine, takes no lock and touches no host map.
+ * Limit: n <= CG_POISSON_STATIC_MAX_N elements (a whole 2048 x 1489 frame is 3.05e6); larger n returns
+ * CG_EINVAL with a message.  EVERY call shares the one array, which keeps the last call's partials
+ * (nothing needs clearing: each slot is written before it is read): two calls that overlap on the GPU
+ * (different streams, or graph branches without an edge between them) RACE -- serialise them, or use
+ * cg_poisson_loglike, whose scratch is per stream. */
+#define CG_POISSON_STATIC_MAX_BLOCKS 1024
+#define CG_POISSON_STATIC_MAX_N (1024LL * 256LL * 64LL)   /* 16 777 216: at most 64 grid-stride trips per thread */
+int cg_poisson_loglike_static(const double* d_data, const double* d_model, const double* d_mask,
+                              int64_t n, double* d_out, void* stream);
+
 /* ---- N1: celeste_sample_sources.pyx:61-156 ------------------------------- */
 /* sample_source_counts for n_img images at once.  Item = src*n_img + img (the
  * layout cg_render_patches produces with d_items = NULL): d_boxes[item] is the
