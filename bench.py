@@ -373,6 +373,7 @@ def bench_crowded(engine, synth, steps, pk, with_cpu):
                 render_evals += evals[name]
     # N2: the location slice samplers of all 5000 sources in one launch (not part of the sweep above)
     sw.allocate(7)
+    sw.slice_locations(seed=10)            # warm-up (first launch sets the kernel's shared-memory attributes)
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     status, sl_evals = sw.slice_locations(seed=11)
@@ -386,6 +387,17 @@ def bench_crowded(engine, synth, steps, pk, with_cpu):
                  "uniforms_per_source": {"block": 256, "max_used": int(sw.slice_stats["used"].max())},
                  "sources_finished_on_device": int((status == 0).sum()),
                  "comparisons_decided_in_float64": int(sw.slice_stats["refined"].sum())}
+    # HMC of every galaxy (celeste_mcmc.py:281-323) in one launch, a SHORT trajectory (2 leapfrog steps = 35 float64
+    # likelihoods per galaxy instead of the reference's 50 steps = 563); the state is restored afterwards
+    keep = sw.d_cur.clone()
+    _, hmc_acc = sw.hmc_galaxies(seed=12, step=1e-9, n_steps=2)
+    sw.d_cur.copy_(keep)
+    hmc_leg = {"what": "hmc_sample_galaxy_params for all galaxies in ONE launch (cg_hmc_galaxy_params), 2 leapfrog steps; "
+                       "a likelihood = the galaxy's 5 capped footprints x 42 components in float64, no culling",
+               "galaxies": int(hmc_acc.size), "leapfrog_steps": 2, "kernel_ms": sw.hmc_stats["kernel_ms"],
+               "float64_likelihoods": int(sw.hmc_stats["likelihoods"]),
+               "likelihoods_per_s": float(sw.hmc_stats["likelihoods"] / (sw.hmc_stats["kernel_ms"] * 1e-3)),
+               "accepted": int(hmc_acc.sum())}
     # backgrounds: every active neighbour rendered on the target's box (sources.py:481)
     offs, idx = sw.h_nbr
     st = sw.h_static
@@ -412,7 +424,7 @@ def bench_crowded(engine, synth, steps, pk, with_cpu):
            "sweep_ms": ms, "sweep_ms_host_clock": wall * 1e3, "value": evals_sweep / (ms * 1e-3), "unit": "evals/s",
            "proposals_per_s": 2 * S * P / (ms * 1e-3), "evals_per_sweep": evals_sweep, "evals_by_phase": evals,
            "phase_ms": {k: round(v, 3) for k, v in ph.items()}, "workspace_bytes": int(sw.workspace_bytes),
-           "slice_sampler_on_device": slice_leg,
+           "slice_sampler_on_device": slice_leg, "hmc_on_device": hmc_leg,
            "h2d_bytes_per_sweep": 2 * S * P * 8, "accepted_last_sweep": res["accepted"].tolist(),
            "guard_rescored_last_sweep": res["guard"].tolist(),
            "roofline": _roofline("render_kernel<float, COND | POISSON> (the two scoring passes: %.0f%% of the sweep)" %

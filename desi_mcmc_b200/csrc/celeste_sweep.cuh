@@ -744,7 +744,10 @@ __device__ __noinline__ bool hmc_grad(HmcCtx& c, const ImgPtrs& imgs, const doub
 }
 
 #define HMC_WARP_BYTES (CG_MAX_COMP * TAB_W * 8)
-__global__ void __launch_bounds__(32 * SLICE_MAX_IMG) hmc_galaxy_kernel(HmcArgs A) {
+#ifndef HMC_MINB
+#define HMC_MINB 3
+#endif
+__global__ void __launch_bounds__(32 * SLICE_MAX_IMG, HMC_MINB) hmc_galaxy_kernel(HmcArgs A) {
   extern __shared__ __align__(16) unsigned char s_dyn[];           // n_img x HMC_WARP_BYTES
   __shared__ double s_part[SLICE_MAX_IMG * 4];
   const int j = blockIdx.x;          // j: row of the per-call arrays; s: the source it updates

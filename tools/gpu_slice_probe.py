@@ -13,3 +13,9 @@ if __name__ == "__main__":
         st = sw.slice_stats
         print(json.dumps({"kernel_ms": round(st["kernel_ms"], 3), "evals": int(st["evals"].sum()),
                           "refined": int(st["refined"].sum()), "max_used": int(st["used"].max())}))
+    for rep in range(2):
+        keep = sw.d_cur.clone()
+        _, acc = sw.hmc_galaxies(seed=12, step=1e-9, n_steps=2)
+        sw.d_cur.copy_(keep)
+        print(json.dumps({"variant": os.environ.get("CG_LIB_VARIANT", "base"), "hmc_kernel_ms": round(sw.hmc_stats["kernel_ms"], 2),
+                          "likelihoods": int(sw.hmc_stats["likelihoods"]), "accepted": int(acc.sum())}))
