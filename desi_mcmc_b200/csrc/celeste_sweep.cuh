@@ -1216,8 +1216,6 @@ int cg_slice_sample_locations(CgImage* const* imgs, int32_t n_img, CgSource* d_s
   const size_t smem = (size_t)n_img * SLICE_WARP_BYTES;
   if (smem > 48 * 1024)
     CUDA_TRY(cudaFuncSetAttribute(slice_location_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  CUDA_TRY(cudaFuncSetAttribute(slice_location_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                cudaSharedmemCarveoutMaxShared));
   slice_location_kernel<<<n_src, 32 * n_img, smem, (cudaStream_t)stream>>>(A);
   LAUNCH_CHECK();
   return CG_OK;
