@@ -475,7 +475,7 @@ def main():
                     help="weak scaling instead: this many fields on every rank")
     ap.add_argument("--fields-per-call", type=int, default=8,
                     help="fields batched into one cg_fields_loglik call")
-    ap.add_argument("--streams", type=int, default=3,
+    ap.add_argument("--streams", type=int, default=4,
                     help="side streams the field sets of a step are spread over (the set-up kernels of one set run in the tail of "
                          "the previous set's tile kernel; the roofline leg always times the kernel alone on one stream)")
     ap.add_argument("--no-graph", action="store_true", help="launch every step kernel by kernel")

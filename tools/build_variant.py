@@ -12,6 +12,6 @@ if r.returncode:
     sys.exit(r.stdout + r.stderr)
 L = (r.stdout + r.stderr).splitlines()
 for i, l in enumerate(L):
-    if "Compiling entry function '_Z17field_tile_kernel" in l or "Compiling entry function '_Z17hmc_galaxy_kernel" in l:
+    if "Compiling entry function '_Z17field_tile_kernel" in l or "Compiling entry function '_Z17hmc_galaxy_kernel" in l or "Compiling entry function '_Z14prepare_kernelIf" in l:
         print(L[i + 1].strip()); print(L[i + 2].strip()); print(L[i + 3].strip())
 print(out)
