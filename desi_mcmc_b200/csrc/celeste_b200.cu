@@ -1221,8 +1221,11 @@ __device__ __forceinline__ int bins_of(const DevImage& im, int* bins_x) {
   return *bins_x * ((im.H + BIN_H - 1) / BIN_H);
 }
 
-__global__ void __launch_bounds__(256) bin_order_kernel(FieldArgs a) {
-  const int g = blockIdx.x * 256 + threadIdx.x;
+#ifndef BO_THREADS
+#define BO_THREADS 256
+#endif
+__global__ void __launch_bounds__(BO_THREADS) bin_order_kernel(FieldArgs a) {
+  const int g = blockIdx.x * BO_THREADS + threadIdx.x;
   int b = -1, cnt = 0;
   if (g < a.tiles_total) {
     const int img = g / a.max_tiles, t = g - img * a.max_tiles;
@@ -1776,19 +1779,24 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
 }
 
 // one block per image: fixed-shape tree over its bin sums
-__global__ void __launch_bounds__(1024) field_tile_final_kernel(FieldArgs a) {
+#ifndef FIN_THREADS
+#define FIN_THREADS 1024
+#endif
+__global__ void __launch_bounds__(FIN_THREADS) field_tile_final_kernel(FieldArgs a) {
   const int img = blockIdx.x;
   int bx;
   const int n_bins = bins_of(*a.imgs.p[img], &bx);
-  __shared__ double s_fin[1024];
+  __shared__ double s_fin[FIN_THREADS];
   double t0 = 0, t1 = 0, t2 = 0, t3 = 0;
   const double* bp = a.block_partials + (long long)img * a.max_tiles;
   int i = threadIdx.x;
-  for (; i + 3072 < n_bins; i += 4096) { t0 += bp[i]; t1 += bp[i + 1024]; t2 += bp[i + 2048]; t3 += bp[i + 3072]; }
-  for (; i < n_bins; i += 1024) t0 += bp[i];
+  for (; i + 3 * FIN_THREADS < n_bins; i += 4 * FIN_THREADS) {
+    t0 += bp[i]; t1 += bp[i + FIN_THREADS]; t2 += bp[i + 2 * FIN_THREADS]; t3 += bp[i + 3 * FIN_THREADS];
+  }
+  for (; i < n_bins; i += FIN_THREADS) t0 += bp[i];
   s_fin[threadIdx.x] = (t0 + t1) + (t2 + t3);
   __syncthreads();
-  for (int o = 512; o > 0; o >>= 1) {
+  for (int o = FIN_THREADS / 2; o > 0; o >>= 1) {
     if (threadIdx.x < o) s_fin[threadIdx.x] += s_fin[threadIdx.x + o];
     __syncthreads();
   }
@@ -3173,7 +3181,7 @@ static int field_setup(CgImage* const* imgs, const int32_t* h_img_off, const CgS
   if ((long long)max_bins * n_img >= (1LL << 25))
     return fail(CG_EINVAL, "%lld image bins in one call exceed the bin descriptor's 25-bit index", (long long)max_bins * n_img);
   fa.logtab = g_d_logtab; fa.cnt = cnt; fa.cull = g_cull | (g_recur ? 0 : 2);
-  bin_order_kernel<<<(fa.tiles_total + 255) / 256, 256, 0, st>>>(fa);
+  bin_order_kernel<<<(fa.tiles_total + BO_THREADS - 1) / BO_THREADS, BO_THREADS, 0, st>>>(fa);
   LAUNCH_CHECK();
   return CG_OK;
 }
@@ -3207,7 +3215,7 @@ int cg_fields_loglik(CgImage* const* imgs, const int32_t* h_img_off, const CgSou
   field_tile_kernel<<<g_sm_count * FT_MINB, FT_LAUNCH_THREADS, 0, st>>>(fa);      // persistent: FT_MINB CTAs per SM (launch bounds)
   prof_end(prof, st);
   LAUNCH_CHECK();
-  field_tile_final_kernel<<<n_img, 1024, 0, st>>>(fa);
+  field_tile_final_kernel<<<n_img, FIN_THREADS, 0, st>>>(fa);
   LAUNCH_CHECK();
   g_last_counters = pa.cnt;
   return CG_OK;

@@ -941,7 +941,7 @@ int cg_field_sample_photons(CgImage* const* imgs, int32_t n_img, const CgSource*
   alloc_tile_kernel<<<g_sm_count * per_sm, 256, 0, st>>>(A);
   LAUNCH_CHECK();
   A.f.ll = d_noise_sum;                       // per-image sum of the per-bin noise photons, fixed order
-  field_tile_final_kernel<<<n_img, 1024, 0, st>>>(A.f);
+  field_tile_final_kernel<<<n_img, FIN_THREADS, 0, st>>>(A.f);
   LAUNCH_CHECK();
   if (d_unit_sums && n_items > 0) {
     unit_sums_kernel<<<(unsigned)((n_items + 255) / 256), 256, 0, st>>>(A.item_unit_fx, n_items, d_unit_sums);
