@@ -511,3 +511,65 @@ def test_planck_without_filter_curves_fails_loudly(engine):
         engine.field_loglik(gimgs, d_srcs)
     ll = engine.field_loglik(gimgs, packed).cpu().numpy()       # a host array: the curves are loaded first
     assert np.all(np.isfinite(ll))
+
+
+def _four_component_psf(field):
+    """every image's PSF gets a fourth, wide component (CG_MAX_PSF = 4: a galaxy then has
+    (6 + 8) x 4 = 56 = CG_MAX_COMP components; the reference's PSFs have 3)"""
+    for m in field["images"]:
+        w = np.concatenate([np.asarray(m["psf_weights"], dtype=np.float64) * .9, [.1]])
+        means = np.concatenate([np.asarray(m["psf_means"], dtype=np.float64), [[.3, -.2]]])
+        covs = np.concatenate([np.asarray(m["psf_covars"], dtype=np.float64), [[[9., 1.], [1., 7.]]]])
+        m["psf_weights"], m["psf_means"], m["psf_covars"] = w, means, covs
+    return field
+
+
+def test_galaxy_on_four_component_psf(engine, oracle):
+    """K = 56: the component table, the per-warp shared tables and the bin-list packing (item * 64 + K) at
+    their maximum -- patches, model image and log-likelihood against the oracle."""
+    from desi_mcmc_b200 import _ffi
+    field = _four_component_psf(synth.make_field(79, H=120, W=140, n_src=8, star_frac=.4))
+    assert _check_patches(engine, oracle, field, _ffi.CG_ITEM_FLUX_BAND, False) < RATE_RTOL
+    nelec = hp.simulate_nelec(oracle, field, 6)
+    gimgs = hp.gpu_images(engine, field, nelec)
+    oimgs = hp.oracle_images(oracle, field, nelec)
+    ll, models = engine.field_loglik(gimgs, hp.gpu_sources(engine, field), return_model=True)
+    ll = ll.cpu().numpy()
+    osrcs = hp.oracle_sources(oracle, field)
+    for i, img in enumerate(oimgs):
+        assert hp.rel_err(models[i].cpu().numpy(), oracle.gen_model_image(osrcs, img), 1.0) < RATE_RTOL
+        want = oracle.celeste_likelihood(osrcs, img)
+        assert abs(ll[i] - want) <= LL_RTOL * abs(want)
+
+
+def test_score_proposals_more_near_ties_than_the_old_guard_list(engine, oracle):
+    """2048 proposals ALL inside the guard band (round 1 capped the re-score list at 1024 and kept the
+    fp32 decision beyond it): every one is re-scored in float64 and its decision is the float64 one."""
+    P, size = 2048, 24
+    field, gimgs, oimgs, cur, other, props, _ = _stamp_problem(engine, oracle, 1005, size, P, with_mask=False)
+    ocur = hp.oracle_sources(oracle, [cur])[0]
+    oother = hp.oracle_sources(oracle, [other])
+    boxes, bgs, gboxes = [], [], []
+    for img in oimgs:
+        xlim, ylim = oracle.make_bbox(ocur, img, pixel_radius=9)
+        boxes.append((xlim, ylim))
+        bgs.append(oracle.generate_background_patch(ocur, oother, img, xlim, ylim))
+        gboxes.append((xlim[0], xlim[1], ylim[0], ylim[1]))
+    packed = engine.pack_sources(hp.gpu_sources(engine, [cur] + props))
+    raw = engine.ProposalScorer(gimgs, gboxes, bgs, max_proposals=P, guard=0.0)
+    d32, _, n0 = raw.score(packed, np.zeros(P))
+    assert n0 == 0
+    # thresholds a hair away from the fp32 scores: near-ties, every one of them
+    log_u = d32 + np.random.RandomState(4).uniform(-2e-3, 2e-3, size=P)
+    scorer = engine.ProposalScorer(gimgs, gboxes, bgs, max_proposals=P, guard=1e-2)
+    delta, accept, n_guard = scorer.score(packed, log_u)
+    assert n_guard == P
+    assert np.array_equal(accept, log_u < delta)
+    pick = np.random.RandomState(5).choice(P, 48, replace=False)      # the oracle takes ~10 ms per proposal
+    oprops = hp.oracle_sources(oracle, [props[k] for k in pick])
+    want = np.array([oracle.calculate_acceptance_logprob(ocur, p, oimgs, boxes, bgs) for p in oprops])
+    # float64 tables / exp / log on the device; what is left is the float32 rounding of the background patches
+    assert np.max(np.abs(delta[pick] - want)) < 5e-5
+    clear = np.abs(log_u[pick] - want) > 5e-5
+    assert np.array_equal(accept[pick][clear], (log_u[pick] < want)[clear])
+    assert np.max(np.abs(d32 - delta)) > 1e-6                          # the fp32 scores did differ
