@@ -929,6 +929,12 @@ struct TileArgs {
 };
 __device__ __forceinline__ long long aux_offset_of(const TileArgs& a, int idx) { return (long long)idx * a.aux_stride; }
 
+#ifndef RW_ROWPAIR
+#define RW_ROWPAIR 1        // warp tiles whose lanes' rows are 8 apart take the field kernel's packed loop (ft_eval2r)
+#endif
+__device__ __forceinline__ void ft_eval2r(const float* tb, int n, float y0l, float y1l,
+                                          float x0, float (&acc0)[4], float (&acc1)[4]);
+
 template <typename real, int MODE, typename Args>
 __device__ __forceinline__ double render_warp_tile(const Args& a, const ItemHdr& h, long long item,
                                                    const real* s_tab, float* s_wtab, int wt, int lane, int wbox,
@@ -970,6 +976,19 @@ __device__ __forceinline__ double render_warp_tile(const Args& a, const ItemHdr&
     real xl[PIX_PER_THREAD];
 #pragma unroll
     for (int p = 0; p < PIX_PER_THREAD; ++p) xl[p] = xl0 + (real)p;
+#if RW_ROWPAIR
+    if constexpr (sizeof(real) == 4) {
+      // a full band of a footprint: every lane's rows are TILE_R = 8 apart, the geometry of the field
+      // kernel's bins -- its loop (3 exp2 and 22 issue slots per component and lane instead of 4 and 36;
+      // the second row's ratio is the first's times k8 = 2^(8B), which cull_components already tabulated
+      // and range-checked)
+      if (recur && __all_sync(0xffffffffu, !active || row1 - row0 == 8)) {
+        ft_eval2r(tb, n, y0l, y1l, xl0, acc0, acc1);
+        n = 0;
+        recur = false;
+      }
+    }
+#endif
     if (sizeof(real) == 4 && recur) {
       // row recurrence: 2 exp2 per row of 4 pixels (the rows of a lane are not a fixed
       // distance apart here, so each row takes its own neighbour ratio)
@@ -1071,11 +1090,11 @@ template <typename real, int MODE>
 __global__ void __launch_bounds__(STRIP_THREADS) render_kernel(RenderArgs a) {
   // per-warp staging: the item's component table and the culled, compacted table
   __shared__ __align__(16) real s_tab_all[(STRIP_THREADS / 32) * TAB_STRIDE];
-  __shared__ __align__(16) float s_wtab_all[(sizeof(real) == 4) ? (STRIP_THREADS / 32) * CG_MAX_COMP * 8 : 4];
+  __shared__ __align__(16) float s_wtab_all[(sizeof(real) == 4) ? (STRIP_THREADS / 32) * (CG_MAX_COMP + 1) * 8 : 4];   // + ft_eval2r's prefetch row
   const LogTable* const logt = a.logtab;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   real* const s_tab = s_tab_all + warp * TAB_STRIDE;
-  float* const s_wtab = s_wtab_all + ((sizeof(real) == 4) ? warp * CG_MAX_COMP * 8 : 0);
+  float* const s_wtab = s_wtab_all + ((sizeof(real) == 4) ? warp * (CG_MAX_COMP + 1) * 8 : 0);
   const int n_heavy = *((volatile int*)&a.cnt->heavy_strips);
   const int total = n_heavy + *((volatile int*)&a.cnt->light_strips);
   unsigned long long issued = 0;
