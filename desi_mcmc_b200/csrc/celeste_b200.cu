@@ -1452,6 +1452,18 @@ __device__ __forceinline__ bool ft_source_rates(const FieldArgs& a, int item, in
     }
     recur = !__any_sync(0xffffffffu, !(dmx <= FT_RECUR_DMAX)) && FT_RECUR && !(a.cull & 2);
     __syncwarp();
+#ifdef FT_ABLATE_CULL       // timing experiment: galaxies evaluate a fixed number of components, no culling
+  } else if ((a.cull & 1) && n > 1) {
+    for (int k = lane; k < n; k += 32) {
+      const float4* t4 = reinterpret_cast<const float4*>(gtab + k * TAB_W);
+      const float4 e0 = __ldg(t4), e1 = __ldg(t4 + 1);
+      *reinterpret_cast<float4*>(wtab + k * 8) = e0;
+      *reinterpret_cast<float4*>(wtab + k * 8 + 4) = make_float4(e1.x, e1.y, 1.f, 1.f);
+    }
+    n = min(n, FT_ABLATE_CULL);
+    recur = true;
+    __syncwarp();
+#endif
   } else if ((a.cull & 1) && n > 1) {
     n = cull_components<true>(gtab, n, lane, (float)(ix0 - o.x), (float)(ix1 - 1 - o.x), (float)(iy0 - o.y),
                               (float)(iy1 - 1 - o.y), 3.f, wtab, &recur);
@@ -1473,6 +1485,9 @@ __device__ __forceinline__ bool ft_source_rates(const FieldArgs& a, int item, in
   const bool doA = iy0 < q.Y0 + 8, doB = iy1 > q.Y0 + 8;         // which row halves the footprint reaches
 #pragma unroll
   for (int p = 0; p < 4; ++p) { acc0[p] = 0.f; acc1[p] = 0.f; }
+#ifdef FT_ABLATE_EVAL       // timing experiment (tools/build_variant.py): everything but the evaluation loops
+  if (n >= 0) { acc0[0] = (float)n * 1e-12f + fabsf(tb[0]) * 1e-30f; if (lane == 0) issued += recur; return true; }
+#endif
   if (doA && doB) {
     if (recur) ft_eval2r(tb, n, (float)(q.yA - o.y), (float)(q.yB - o.y), xl[0], acc0, acc1);
     else ft_eval2(tb, n, (float)(q.yA - o.y), (float)(q.yB - o.y), xl, acc0, acc1);
