@@ -1669,7 +1669,11 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
         if (y < H && q.x < W) {
           const float* rp = im.nelec + (long long)y * W + q.x;
           if (vec) {
+#ifdef FT_ABLATE_LOAD       // timing experiment: no pixel traffic
+            const float4 v = make_float4((float)y, (float)q.x, 1.f, 2.f);
+#else
             const float4 v = __ldcs(reinterpret_cast<const float4*>(rp));     // read once: streaming
+#endif
             d[r][0] = v.x; d[r][1] = v.y; d[r][2] = v.z; d[r][3] = v.w;
           } else {
 #pragma unroll
@@ -1743,7 +1747,11 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
         const unsigned vm = __ballot_sync(0xffffffffu, valid);
         const int nv = __popc(vm);
         const int rk = __popc(vm & ((1u << lane) - 1u));         // lane order = source order (sorted list / scan)
+#ifdef FT_ABLATE_PAIRS      // timing experiment: the per-(bin, source) work removed
+        for (int r = 0; r < 0; ++r) {
+#else
         for (int r = 0; r < nv; ++r) {
+#endif
           const unsigned m = __ballot_sync(0xffffffffu, valid && rk == r);
           const int sl = __ffs(m) - 1;
           const int ee = __shfl_sync(0xffffffffu, e, sl);
@@ -1762,6 +1770,12 @@ __global__ void __launch_bounds__(FT_THREADS, FT_MINB) field_tile_kernel(FieldAr
       FT_LOAD_D()
       float sres = 0.f;
       double slam = 0.0;
+#ifdef FT_ABLATE_EPI        // timing experiment: no per-pixel logarithm
+      if (q.x >= 0) {
+#pragma unroll
+        for (int r = 0; r < 2; ++r) slam += (double)(((lam[r][0] + lam[r][1]) + (lam[r][2] + lam[r][3])) * ((d[r][0] + d[r][1]) + (d[r][2] + d[r][3])));
+      } else
+#endif
       if (q.x + 3 < W && q.yB < H) {                          // interior lane: no bounds tests
 #pragma unroll
         for (int r = 0; r < 2; ++r) {
