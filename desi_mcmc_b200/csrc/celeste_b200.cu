@@ -1510,6 +1510,9 @@ __device__ __forceinline__ void ft_source(const FieldArgs& a, int item, int K, i
                                           float (&lam)[2][4], unsigned long long& issued) {
   float acc0[4], acc1[4];
   if (!ft_source_rates(a, item, K, bx, o, q, lane, wtab, acc0, acc1, issued)) return;
+#ifdef FT_ABLATE_LAM        // timing experiment: no masks, no lambda update
+  lam[0][0] += acc0[0]; return;
+#endif
   if (min(q.X0 + BIN_W, bx.y) - max(q.X0, bx.x) == BIN_W &&
       min(q.Y0 + BIN_H, bx.w) - max(q.Y0, bx.z) == BIN_H) {       // the footprint covers the bin: no masks
 #pragma unroll
